@@ -1,0 +1,24 @@
+"""bottleneck_guided_rrt_b200 — B200-native hot paths of the bottleneck-guided RRT* planner.
+
+The product is the C-ABI shared library ``libbgrrt.so`` (include/bgrrt.h): hand-written
+sm_100a CUDA kernels behind the planner's own call surface (libnabo-style NNSearch and
+isStateValid / isLineValid).  This package is the thin Python binding used by the tests,
+the benchmark and the multi-GPU launcher; importing it FAILS LOUDLY if the CUDA library
+has not been built — there is no CPU fallback anywhere in the product path.
+"""
+from .capi import (  # noqa: F401
+    ALLOW_SELF_MATCH,
+    SORT_RESULTS,
+    TOUCH_STATISTICS,
+    METHOD_AUTO,
+    METHOD_BRUTE,
+    METHOD_GRID,
+    SHAPE_CYLINDER,
+    SHAPE_CAPSULE,
+    BgrError,
+    NNSearchF,
+    OccupancyMap,
+    lib,
+    library_path,
+    knn_merge_dev,
+)

@@ -1,0 +1,330 @@
+"""ctypes binding of libbgrrt.so + host-side mirror of the reference call surface.
+
+``NNSearchF`` mirrors libnabo's ``Nabo::NNSearchF`` as the reference uses it
+(rrt_star_milestones.cpp:1306-1315): ``createKDTreeLinearHeap(cloud)`` / ``knn(query,
+indices, dists2, k, eps, flags, maxRadius)`` with libnabo's argument meaning and error
+behaviour (``RuntimeError`` where libnabo throws ``std::runtime_error``).
+``OccupancyMap`` mirrors ``isStateValid`` (:310-351) / ``isLineValid`` (:385-471): True means
+IN COLLISION, as in the reference.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+ALLOW_SELF_MATCH = 1
+SORT_RESULTS = 2
+TOUCH_STATISTICS = 1
+METHOD_AUTO, METHOD_BRUTE, METHOD_GRID = 0, 1, 2
+SHAPE_CYLINDER, SHAPE_CAPSULE = 0, 1
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class BgrError(RuntimeError):
+    def __init__(self, rc, msg):
+        super().__init__("libbgrrt rc=%d: %s" % (rc, msg))
+        self.rc = rc
+
+
+def library_path():
+    return os.path.join(_HERE, "libbgrrt.so")
+
+
+def lib():
+    """Load libbgrrt.so.  Raises if the CUDA extension is missing (no fallback)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise ImportError(
+            "libbgrrt.so not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C bottleneck_guided_rrt_b200/csrc` (there is no CPU fallback)")
+    L = C.CDLL(path)
+    vp, i64, i32, f32, f64, u32 = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_double, C.c_uint
+    L.bgr_last_error.restype = C.c_char_p
+    L.bgr_version.restype = i32
+    L.bgr_device_count.argtypes = [vp]
+    L.bgr_device_info.argtypes = [vp, vp, vp]
+    L.bgr_nns_create.argtypes = [vp, i64, i32, u32, vp]
+    L.bgr_nns_create_dev.argtypes = [vp, i64, i32, u32, vp, vp]
+    L.bgr_nns_append.argtypes = [vp, vp, i64]
+    L.bgr_nns_append_dev.argtypes = [vp, vp, i64]
+    L.bgr_nns_size.restype = i64
+    L.bgr_nns_size.argtypes = [vp]
+    L.bgr_nns_set_stream.argtypes = [vp, vp]
+    L.bgr_nns_set_method.argtypes = [vp, i32]
+    L.bgr_nns_set_index_base.argtypes = [vp, i64]
+    L.bgr_nns_build_index.argtypes = [vp]
+    L.bgr_nns_knn.argtypes = [vp, vp, i64, i32, f32, u32, f32, vp, vp, vp, vp]
+    L.bgr_nns_knn_dev.argtypes = [vp, vp, i64, i32, f32, u32, f32, vp, vp, vp, vp]
+    L.bgr_nns_nearest.argtypes = [vp, vp, i64, vp, vp]
+    L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
+    L.bgr_nns_destroy.argtypes = [vp]
+    L.bgr_knn_merge_dev.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
+    L.bgr_map_create.argtypes = [f64, vp, vp, vp]
+    L.bgr_map_set_stream.argtypes = [vp, vp]
+    L.bgr_map_set_boxes.argtypes = [vp, vp, i64]
+    L.bgr_map_update_boxes.argtypes = [vp, vp, i64, vp, i64]
+    L.bgr_map_occupied_cells.argtypes = [vp, vp]
+    L.bgr_map_download_bitmap.argtypes = [vp, vp, vp]
+    L.bgr_map_collide_spheres.argtypes = [vp, vp, i64, f64, vp, vp]
+    L.bgr_map_collide_spheres_dev.argtypes = [vp, vp, i64, f64, vp, vp]
+    L.bgr_map_collide_edges.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
+    L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
+    L.bgr_map_last_stats.argtypes = [vp, vp]
+    L.bgr_map_destroy.argtypes = [vp]
+    _LIB = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise BgrError(rc, lib().bgr_last_error().decode("utf-8", "replace"))
+
+
+def _ptr(a):
+    """host numpy array / raw int device pointer / torch tensor -> void*"""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    if hasattr(a, "data_ptr"):
+        return C.c_void_p(a.data_ptr())
+    raise TypeError(type(a))
+
+
+def _host_f32(a, cols=3):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if a.ndim == 1:
+        a = a.reshape(-1, cols)
+    return a
+
+
+def _is_dev(a):
+    return hasattr(a, "data_ptr") and getattr(a, "is_cuda", False)
+
+
+class NNSearchF:
+    """libnabo-shaped search object over the append-only HBM node store.
+
+    Points are passed as (N, 3) float32 arrays — the memory image of libnabo's 3xN
+    column-major ``Eigen::MatrixXf`` (one point per column).
+    """
+
+    ALLOW_SELF_MATCH = ALLOW_SELF_MATCH
+    SORT_RESULTS = SORT_RESULTS
+    TOUCH_STATISTICS = TOUCH_STATISTICS
+
+    def __init__(self, handle):
+        self._h = handle
+
+    # Nabo::NNSearchF::createKDTreeLinearHeap(cloud, dim, creationOptionFlags)
+    @classmethod
+    def createKDTreeLinearHeap(cls, cloud, dim=None, creationOptionFlags=0, stream=None):
+        h = C.c_void_p()
+        if _is_dev(cloud):
+            n = cloud.shape[0]
+            _check(lib().bgr_nns_create_dev(_ptr(cloud), n, dim or 3, creationOptionFlags,
+                                            C.c_void_p(stream or 0), C.byref(h)))
+        else:
+            cloud = _host_f32(cloud)
+            _check(lib().bgr_nns_create(_ptr(cloud), cloud.shape[0], dim or cloud.shape[1],
+                                        creationOptionFlags, C.byref(h)))
+            if stream:
+                _check(lib().bgr_nns_set_stream(h, C.c_void_p(stream)))
+        return cls(h)
+
+    create = createKDTreeLinearHeap
+
+    def __del__(self):
+        self.close()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgr_nns_destroy(self._h)
+            self._h = None
+
+    def __len__(self):
+        return int(lib().bgr_nns_size(self._h))
+
+    def append(self, pts):
+        if _is_dev(pts):
+            _check(lib().bgr_nns_append_dev(self._h, _ptr(pts), pts.shape[0]))
+        else:
+            pts = _host_f32(pts)
+            _check(lib().bgr_nns_append(self._h, _ptr(pts), pts.shape[0]))
+
+    def set_stream(self, stream):
+        _check(lib().bgr_nns_set_stream(self._h, C.c_void_p(stream or 0)))
+
+    def set_method(self, method):
+        _check(lib().bgr_nns_set_method(self._h, method))
+
+    def set_index_base(self, base):
+        _check(lib().bgr_nns_set_index_base(self._h, base))
+
+    def build_index(self):
+        _check(lib().bgr_nns_build_index(self._h))
+
+    def knn(self, query, k=1, epsilon=0.0, optionFlags=0, maxRadius=float("inf"), maxRadii=None,
+            indices=None, dists2=None):
+        """Returns (indices (Q,k) int32, dists2 (Q,k) float32, touched).  Host arrays in,
+        host arrays out; CUDA tensors in, CUDA tensors out (asynchronous on the stream)."""
+        touched = C.c_uint64(0)
+        if _is_dev(query):
+            import torch
+            nq = query.shape[0]
+            if indices is None:
+                indices = torch.empty((nq, k), dtype=torch.int32, device=query.device)
+            if dists2 is None:
+                dists2 = torch.empty((nq, k), dtype=torch.float32, device=query.device)
+            _check(lib().bgr_nns_knn_dev(self._h, _ptr(query), nq, k, epsilon, optionFlags, maxRadius,
+                                         _ptr(maxRadii), _ptr(indices), _ptr(dists2), C.byref(touched)))
+            return indices, dists2, touched.value
+        q = _host_f32(query)
+        nq = q.shape[0]
+        if indices is None:
+            indices = np.empty((nq, k), dtype=np.int32)
+        if dists2 is None:
+            dists2 = np.empty((nq, k), dtype=np.float32)
+        # libnabo checkSizesKnn: result matrices must be k x Q
+        if indices.shape != (nq, k) or dists2.shape != (nq, k):
+            raise RuntimeError("Index/distance matrix has wrong shape: expected %dx%d" % (k, nq))
+        mr = None
+        if maxRadii is not None:
+            mr = np.ascontiguousarray(maxRadii, dtype=np.float32)
+            if mr.shape[0] != nq:
+                raise RuntimeError("Maximum radii vector has %d rows != %d queries" % (mr.shape[0], nq))
+        _check(lib().bgr_nns_knn(self._h, _ptr(q), nq, k, epsilon, optionFlags, maxRadius, _ptr(mr),
+                                 _ptr(indices), _ptr(dists2), C.byref(touched)))
+        return indices, dists2, touched.value
+
+    def nearest(self, query, idx=None, dist=None):
+        """Batched reference Nearest(): returns (index (Q,) int32, Norm (Q,) float32)."""
+        if _is_dev(query):
+            import torch
+            nq = query.shape[0]
+            if idx is None:
+                idx = torch.empty(nq, dtype=torch.int32, device=query.device)
+            if dist is None:
+                dist = torch.empty(nq, dtype=torch.float32, device=query.device)
+            _check(lib().bgr_nns_nearest_dev(self._h, _ptr(query), nq, _ptr(idx), _ptr(dist)))
+            return idx, dist
+        q = _host_f32(query)
+        nq = q.shape[0]
+        idx = np.empty(nq, dtype=np.int32) if idx is None else idx
+        dist = np.empty(nq, dtype=np.float32) if dist is None else dist
+        _check(lib().bgr_nns_nearest(self._h, _ptr(q), nq, _ptr(idx), _ptr(dist)))
+        return idx, dist
+
+
+def knn_merge_dev(idx_slabs, d2_slabs, idx_out, d2_out, stream=0):
+    """Merge G per-shard (Q,k) top-k slabs (CUDA tensors (G,Q,k)) into one, by (d2, index)."""
+    g, nq, k = idx_slabs.shape
+    _check(lib().bgr_knn_merge_dev(_ptr(idx_slabs), _ptr(d2_slabs), g, nq, k, _ptr(idx_out), _ptr(d2_out),
+                                   C.c_void_p(stream or 0)))
+    return idx_out, d2_out
+
+
+class OccupancyMap:
+    """Octomap occupied leaves flattened to HBM bit grids; isStateValid / isLineValid batched."""
+
+    def __init__(self, res, origin, dims, stream=None):
+        o = np.ascontiguousarray(origin, dtype=np.float64)
+        d = np.ascontiguousarray(dims, dtype=np.int32)
+        h = C.c_void_p()
+        _check(lib().bgr_map_create(res, _ptr(o), _ptr(d), C.byref(h)))
+        self._h = h
+        self.res, self.origin, self.dims = res, o, d
+        if stream:
+            self.set_stream(stream)
+
+    def __del__(self):
+        self.close()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgr_map_destroy(self._h)
+            self._h = None
+
+    def set_stream(self, stream):
+        _check(lib().bgr_map_set_stream(self._h, C.c_void_p(stream or 0)))
+
+    def set_boxes(self, boxes):
+        b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 6)
+        _check(lib().bgr_map_set_boxes(self._h, _ptr(b), b.shape[0]))
+
+    def update_boxes(self, add=None, remove=None):
+        a = np.ascontiguousarray(add if add is not None else np.zeros((0, 6)), dtype=np.float64).reshape(-1, 6)
+        r = np.ascontiguousarray(remove if remove is not None else np.zeros((0, 6)), dtype=np.float64).reshape(-1, 6)
+        _check(lib().bgr_map_update_boxes(self._h, _ptr(a), a.shape[0], _ptr(r), r.shape[0]))
+
+    def occupied_cells(self):
+        c = C.c_int64(0)
+        _check(lib().bgr_map_occupied_cells(self._h, C.byref(c)))
+        return c.value
+
+    def download_bitmap(self):
+        n = C.c_int64(0)
+        _check(lib().bgr_map_download_bitmap(self._h, None, C.byref(n)))
+        out = np.empty(n.value, dtype=np.uint64)
+        _check(lib().bgr_map_download_bitmap(self._h, _ptr(out), C.byref(n)))
+        return out
+
+    def collide_spheres(self, centers, radius=0.1, want_band=True, hit=None, band=None):
+        if _is_dev(centers):
+            import torch
+            n = centers.shape[0]
+            hit = torch.empty(n, dtype=torch.uint8, device=centers.device) if hit is None else hit
+            if want_band and band is None:
+                band = torch.empty(n, dtype=torch.uint8, device=centers.device)
+            _check(lib().bgr_map_collide_spheres_dev(self._h, _ptr(centers), n, radius, _ptr(hit),
+                                                     _ptr(band) if want_band else None))
+            return hit, band
+        c = _host_f32(centers)
+        n = c.shape[0]
+        hit = np.empty(n, dtype=np.uint8) if hit is None else hit
+        if want_band and band is None:
+            band = np.empty(n, dtype=np.uint8)
+        _check(lib().bgr_map_collide_spheres(self._h, _ptr(c), n, radius, _ptr(hit), _ptr(band) if want_band else None))
+        return hit, band
+
+    def collide_edges(self, p1, p2, radius=0.03, shape=SHAPE_CYLINDER, want_band=True, hit=None, band=None):
+        if _is_dev(p1):
+            import torch
+            n = p1.shape[0]
+            hit = torch.empty(n, dtype=torch.uint8, device=p1.device) if hit is None else hit
+            if want_band and band is None:
+                band = torch.empty(n, dtype=torch.uint8, device=p1.device)
+            _check(lib().bgr_map_collide_edges_dev(self._h, _ptr(p1), _ptr(p2), n, radius, shape, _ptr(hit),
+                                                   _ptr(band) if want_band else None))
+            return hit, band
+        a, b = _host_f32(p1), _host_f32(p2)
+        n = a.shape[0]
+        hit = np.empty(n, dtype=np.uint8) if hit is None else hit
+        if want_band and band is None:
+            band = np.empty(n, dtype=np.uint8)
+        _check(lib().bgr_map_collide_edges(self._h, _ptr(a), _ptr(b), n, radius, shape, _ptr(hit),
+                                           _ptr(band) if want_band else None))
+        return hit, band
+
+    def last_stats(self):
+        s = np.zeros(4, dtype=np.uint64)
+        _check(lib().bgr_map_last_stats(self._h, _ptr(s)))
+        return {"work_items": int(s[0]), "candidates": int(s[1]), "narrow_tests": int(s[2]), "iter_cap": int(s[3])}
+
+    # reference-shaped single queries (True = in collision)
+    def isStateValid(self, point):
+        hit, _ = self.collide_spheres(np.asarray(point, dtype=np.float32).reshape(1, 3), 0.1, want_band=False)
+        return bool(hit[0])
+
+    def isLineValid(self, point1, point2):
+        hit, _ = self.collide_edges(np.asarray(point1, dtype=np.float32).reshape(1, 3),
+                                    np.asarray(point2, dtype=np.float32).reshape(1, 3), 0.03, SHAPE_CYLINDER,
+                                    want_band=False)
+        return bool(hit[0])

@@ -1,0 +1,97 @@
+// Shared host/device helpers for libbgrrt (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <cstdio>
+#include <cstdarg>
+#include <string>
+#include "../../include/bgrrt.h"
+
+namespace bgr {
+
+void set_error(const char* fmt, ...);
+const char* get_error();
+
+#define BGR_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            bgr::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call,                 \
+                           cudaGetErrorString(e__));                                     \
+            return BGR_ERR_CUDA;                                                         \
+        }                                                                                \
+    } while (0)
+
+#define BGR_CHECK(rc_expr)                                                               \
+    do {                                                                                 \
+        int rc__ = (rc_expr);                                                            \
+        if (rc__ != BGR_OK) return rc__;                                                 \
+    } while (0)
+
+#define BGR_ARG(cond, ...)                                                               \
+    do {                                                                                 \
+        if (!(cond)) {                                                                   \
+            bgr::set_error(__VA_ARGS__);                                                 \
+            return BGR_ERR_ARG;                                                          \
+        }                                                                                \
+    } while (0)
+
+constexpr int kNumSMsB200 = 148;
+constexpr unsigned kFull = 0xffffffffu;
+
+inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+int num_sms();  // of the current device (cached)
+
+// growable device buffer (append-only stores double their capacity)
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    int64_t cap = 0;
+    int reserve(int64_t n, cudaStream_t st, bool keep, int64_t keep_n = 0) {
+        if (n <= cap) return BGR_OK;
+        int64_t nc = cap ? cap : 1024;
+        while (nc < n) nc *= 2;
+        T* np = nullptr;
+        BGR_CUDA(cudaMalloc(&np, (size_t)nc * sizeof(T)));
+        if (keep && p && keep_n > 0)
+            BGR_CUDA(cudaMemcpyAsync(np, p, (size_t)keep_n * sizeof(T), cudaMemcpyDeviceToDevice, st));
+        if (p) {
+            BGR_CUDA(cudaStreamSynchronize(st));
+            BGR_CUDA(cudaFree(p));
+        }
+        p = np;
+        cap = nc;
+        return BGR_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// pinned host staging buffer
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return BGR_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        size_t nc = 1 << 16;
+        while (nc < bytes) nc *= 2;
+        BGR_CUDA(cudaMallocHost(&p, nc));
+        cap = nc;
+        return BGR_OK;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace bgr

@@ -1,0 +1,415 @@
+// Exact grid-bucketed kNN (reference surface nns->knn, MS:1309-1312).
+//
+// Index: the indexed prefix [0, n_indexed) of the append-only store is bucketed into a
+// uniform grid (about kPtsPerCell nodes per cell, <= 1024 cells per axis) and stored as
+// one float4 {x,y,z,index} per node, sorted by cell with x fastest — so the cells of one
+// x-row of a query's neighbourhood are ONE contiguous, 16-byte-aligned range that a warp
+// reads with coalesced float4 loads.  Nodes appended after the last build form an unsorted
+// tail that every query scans linearly; the index is rebuilt when the tail exceeds a
+// quarter of the indexed part (nns.cu).
+//
+// Query: one warp per query.  Ring 1 (3x3x3 cells) is scanned first, then cubic shells;
+// after each ring the search stops once the k-th key is closer than the nearest unscanned
+// cell face (minus a slack that covers the float rounding of the cell computation), which
+// makes the result identical to the brute-force scan: same f32 d2, same (d2,index) order.
+#pragma once
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <vector>
+#include "warp_topk.cuh"
+
+namespace bgr {
+
+constexpr int kPtsPerCell = 8;
+constexpr int kMaxCellsPerAxis = 1024;
+
+struct GridGeom {
+    float mn[3];
+    float cs;      // cell size
+    float inv_cs;
+    int g[3];
+};
+
+struct GridIndex {
+    int64_t n_indexed = 0;
+    GridGeom geom{};
+    DevBuf<float4> pts;
+    DevBuf<int32_t> cell_start;   // ncells + 1
+    DevBuf<int32_t> cell_id;      // per node (build scratch)
+    DevBuf<int32_t> cursor;       // per cell (build scratch)
+    DevBuf<int32_t> block_sums;
+    DevBuf<float> partial;        // bbox partials
+};
+
+__device__ __forceinline__ int cell_coord(float v, float mn, float inv_cs, int g) {
+    const float t = __fmul_rn(__fsub_rn(v, mn), inv_cs);
+    int c = (int)floorf(t);
+    // NaN / out-of-range queries clamp into the grid
+    if (!(t >= 0.f)) c = 0;
+    return min(c, g - 1);
+}
+
+// ---------------------------------------------------------------- build kernels
+__global__ void bbox_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                            const float* __restrict__ z, int64_t n, float* __restrict__ partial) {
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float v[3] = {x[i], y[i], z[i]};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            mn[a] = fminf(mn[a], v[a]);
+            mx[a] = fmaxf(mx[a], v[a]);
+        }
+    }
+    __shared__ float sm[6][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[a] = fminf(mn[a], __shfl_xor_sync(kFull, mn[a], o));
+            mx[a] = fmaxf(mx[a], __shfl_xor_sync(kFull, mx[a], o));
+        }
+        if (lane == 0) {
+            sm[a][warp] = mn[a];
+            sm[3 + a][warp] = mx[a];
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            float m0 = lane < nw ? sm[a][lane] : FLT_MAX, m1 = lane < nw ? sm[3 + a][lane] : -FLT_MAX;
+            for (int o = 16; o > 0; o >>= 1) {
+                m0 = fminf(m0, __shfl_xor_sync(kFull, m0, o));
+                m1 = fmaxf(m1, __shfl_xor_sync(kFull, m1, o));
+            }
+            if (lane == 0) {
+                partial[blockIdx.x * 6 + a] = m0;
+                partial[blockIdx.x * 6 + 3 + a] = m1;
+            }
+        }
+    }
+}
+
+__global__ void cell_count_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                  const float* __restrict__ z, int64_t n, GridGeom gm,
+                                  int32_t* __restrict__ cell_id, int32_t* __restrict__ counts) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cx = cell_coord(x[i], gm.mn[0], gm.inv_cs, gm.g[0]);
+    const int cy = cell_coord(y[i], gm.mn[1], gm.inv_cs, gm.g[1]);
+    const int cz = cell_coord(z[i], gm.mn[2], gm.inv_cs, gm.g[2]);
+    const int32_t c = (cz * gm.g[1] + cy) * gm.g[0] + cx;
+    cell_id[i] = c;
+    atomicAdd(&counts[c], 1);
+}
+
+// exclusive scan, 3 phases over 1024-element blocks
+__global__ void scan_block_kernel(int32_t* __restrict__ data, int64_t n, int32_t* __restrict__ sums) {
+    __shared__ int32_t warp_tot[32];
+    const int64_t i = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int32_t v = i < n ? data[i] : 0;
+    int32_t inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int32_t t = __shfl_up_sync(kFull, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int32_t w = warp_tot[lane];
+        for (int o = 1; o < 32; o <<= 1) {
+            const int32_t t = __shfl_up_sync(kFull, w, o);
+            if (lane >= o) w += t;
+        }
+        warp_tot[lane] = w;
+    }
+    __syncthreads();
+    const int32_t off = warp ? warp_tot[warp - 1] : 0;
+    if (i < n) data[i] = off + inc - v;
+    if (threadIdx.x == 1023) sums[blockIdx.x] = off + inc;
+}
+__global__ void scan_add_kernel(int32_t* __restrict__ data, int64_t n, const int32_t* __restrict__ sums) {
+    const int64_t i = (int64_t)blockIdx.x * 1024 + threadIdx.x;
+    if (i < n) data[i] += sums[blockIdx.x];
+}
+
+__global__ void scatter_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                               const float* __restrict__ z, int64_t n,
+                               const int32_t* __restrict__ cell_id, const int32_t* __restrict__ cell_start,
+                               int32_t* __restrict__ cursor, float4* __restrict__ pts) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t c = cell_id[i];
+    const int32_t pos = cell_start[c] + atomicAdd(&cursor[c], 1);
+    pts[pos] = make_float4(x[i], y[i], z[i], __int_as_float((int)i));
+}
+
+inline int exclusive_scan(int32_t* d, int64_t n, DevBuf<int32_t>& sums, cudaStream_t st) {
+    // recursive over levels; the sums of level L live at offset in `sums`
+    std::vector<int64_t> sizes;
+    int64_t m = n, total = 0;
+    while (m > 1024) {
+        m = div_up(m, 1024);
+        sizes.push_back(m);
+        total += round_up(m, 4);
+    }
+    sizes.push_back(1);
+    total += 4;
+    BGR_CHECK(sums.reserve(total, st, false));
+    std::vector<int32_t*> lv;
+    int32_t* p = sums.p;
+    for (int64_t s : sizes) {
+        lv.push_back(p);
+        p += round_up(s, 4);
+    }
+    std::vector<int32_t*> data{d};
+    std::vector<int64_t> ns{n};
+    for (size_t l = 0; l + 1 < sizes.size() + 1 && ns.back() > 0; ++l) {
+        const int64_t cur = ns.back();
+        scan_block_kernel<<<(unsigned)div_up(cur, 1024), 1024, 0, st>>>(data.back(), cur, lv[l]);
+        BGR_CUDA(cudaGetLastError());
+        if (cur <= 1024) break;
+        data.push_back(lv[l]);
+        ns.push_back(div_up(cur, 1024));
+    }
+    for (int l = (int)data.size() - 2; l >= 0; --l) {
+        scan_add_kernel<<<(unsigned)div_up(ns[l], 1024), 1024, 0, st>>>(data[l], ns[l], data[l + 1]);
+        BGR_CUDA(cudaGetLastError());
+    }
+    return BGR_OK;
+}
+
+inline int grid_build(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,
+                      cudaStream_t st) {
+    if (n <= 0) {
+        G.n_indexed = 0;
+        return BGR_OK;
+    }
+    // 1. bounding box
+    const int nb = 512;
+    BGR_CHECK(G.partial.reserve(nb * 6, st, false));
+    bbox_kernel<<<nb, 256, 0, st>>>(x, y, z, n, G.partial.p);
+    BGR_CUDA(cudaGetLastError());
+    std::vector<float> hp((size_t)nb * 6);
+    BGR_CUDA(cudaMemcpyAsync(hp.data(), G.partial.p, hp.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
+    BGR_CUDA(cudaStreamSynchronize(st));
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int b = 0; b < nb; ++b)
+        for (int a = 0; a < 3; ++a) {
+            mn[a] = std::min(mn[a], hp[(size_t)b * 6 + a]);
+            mx[a] = std::max(mx[a], hp[(size_t)b * 6 + 3 + a]);
+        }
+    for (int a = 0; a < 3; ++a)
+        BGR_ARG(std::isfinite(mn[a]) && std::isfinite(mx[a]), "non-finite node coordinates");
+    // 2. cell size: smallest cs with prod(ceil(ext/cs)) <= n / kPtsPerCell (bisection)
+    double ext[3], emax = 0;
+    for (int a = 0; a < 3; ++a) {
+        ext[a] = (double)mx[a] - (double)mn[a];
+        emax = std::max(emax, ext[a]);
+    }
+    const double target = std::max<double>(1.0, (double)n / kPtsPerCell);
+    auto cells = [&](double cs) {
+        double c = 1;
+        for (int a = 0; a < 3; ++a) c *= std::max(1.0, std::ceil(ext[a] / cs));
+        return c;
+    };
+    double lo = std::max(emax / kMaxCellsPerAxis, 1e-30), hi = std::max(emax, 1e-30) * 1.0001;
+    if (cells(lo) <= target) hi = lo;
+    else
+        for (int it = 0; it < 60; ++it) {
+            const double mid = 0.5 * (lo + hi);
+            if (cells(mid) <= target) hi = mid; else lo = mid;
+        }
+    GridGeom gm;
+    gm.cs = (float)(hi * 1.000001);
+    gm.inv_cs = 1.0f / gm.cs;
+    int64_t ncells = 1;
+    for (int a = 0; a < 3; ++a) {
+        gm.mn[a] = mn[a];
+        gm.g[a] = (int)std::min<double>(kMaxCellsPerAxis, std::max(1.0, std::floor(ext[a] / (double)gm.cs) + 1.0));
+        ncells *= gm.g[a];
+    }
+    // 3. count, scan, scatter
+    BGR_CHECK(G.cell_id.reserve(n, st, false));
+    BGR_CHECK(G.cell_start.reserve(ncells + 1, st, false));
+    BGR_CHECK(G.cursor.reserve(ncells, st, false));
+    BGR_CHECK(G.pts.reserve(n, st, false));
+    BGR_CUDA(cudaMemsetAsync(G.cell_start.p, 0, (size_t)(ncells + 1) * sizeof(int32_t), st));
+    BGR_CUDA(cudaMemsetAsync(G.cursor.p, 0, (size_t)ncells * sizeof(int32_t), st));
+    cell_count_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(x, y, z, n, gm, G.cell_id.p, G.cell_start.p);
+    BGR_CUDA(cudaGetLastError());
+    BGR_CHECK(exclusive_scan(G.cell_start.p, ncells + 1, G.block_sums, st));
+    scatter_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(x, y, z, n, G.cell_id.p, G.cell_start.p, G.cursor.p, G.pts.p);
+    BGR_CUDA(cudaGetLastError());
+    G.geom = gm;
+    G.n_indexed = n;
+    return BGR_OK;
+}
+
+inline void grid_release(GridIndex& G) {
+    G.pts.release(); G.cell_start.release(); G.cell_id.release(); G.cursor.release();
+    G.block_sums.release(); G.partial.release();
+    G.n_indexed = 0;
+}
+
+// ---------------------------------------------------------------- query kernel
+struct GridKnnArgs {
+    GridGeom gm;
+    const float4* pts;
+    const int32_t* cell_start;
+    int64_t n_indexed;
+    const float* x;  // raw store (tail scan)
+    const float* y;
+    const float* z;
+    int64_t n;
+    const float* q;
+    int64_t nq;
+    int k;
+    unsigned flags;
+    float max_radius;
+    const float* max_radii;
+    int32_t* idx;
+    float* d2;
+    int64_t index_base;
+    unsigned long long* counter;
+};
+
+__device__ __forceinline__ uint32_t radius_sentinel_g(float mr) {
+    float mr2 = __fmul_rn(mr, mr);
+    if (!(mr2 <= FLT_MAX)) mr2 = FLT_MAX;
+    return __float_as_uint(mr2) + 1u;
+}
+
+__global__ void __launch_bounds__(256) grid_knn_kernel(GridKnnArgs a) {
+    const int lane = threadIdx.x & 31;
+    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (qi >= a.nq) return;
+    const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
+    const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
+    const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
+    const float lim = __uint_as_float(sent - 1u);
+    WarpList L;
+    L.init(sent);
+    uint32_t tau_d = sent, tau_i = 0u;
+    float tau_f = __uint_as_float(sent);
+    unsigned long long touched = 0;
+
+    auto offer = [&](float px, float py, float pz, uint32_t pidx, bool valid) {
+        const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
+        const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        const bool pass = valid && (d <= tau_f) && (self || d > FLT_EPSILON);
+        if (__any_sync(kFull, pass)) {
+            warp_offer(L, pass, __float_as_uint(d), pidx, tau_d, tau_i, a.k, lane);
+            tau_f = __uint_as_float(tau_d);
+        }
+    };
+
+    // ---- unsorted tail [n_indexed, n)
+    for (int64_t base = a.n_indexed; base < a.n; base += 32) {
+        const int64_t j = base + lane;
+        const bool valid = j < a.n;
+        const float px = valid ? a.x[j] : 0.f, py = valid ? a.y[j] : 0.f, pz = valid ? a.z[j] : 0.f;
+        offer(px, py, pz, (uint32_t)j, valid);
+    }
+    touched += (unsigned long long)(a.n - a.n_indexed);
+
+    if (a.n_indexed > 0) {
+        const GridGeom& gm = a.gm;
+        const int cx = cell_coord(qx, gm.mn[0], gm.inv_cs, gm.g[0]);
+        const int cy = cell_coord(qy, gm.mn[1], gm.inv_cs, gm.g[1]);
+        const int cz = cell_coord(qz, gm.mn[2], gm.inv_cs, gm.g[2]);
+        const int gmax = max(gm.g[0], max(gm.g[1], gm.g[2]));
+        for (int ring = 1; ring <= gmax; ++ring) {
+            // items of this ring: every (y,z) row of the block contributes two items;
+            // ring 1 scans the full 3x3x3 block, later rings only the cubic shell.
+            const int side = 2 * ring + 1;
+            const int nitems = 2 * side * side;
+            for (int t0 = 0; t0 < nitems; t0 += 32) {
+                const int t = t0 + lane;
+                int s = 0, e = 0;
+                if (t < nitems) {
+                    const int row = t >> 1, which = t & 1;
+                    const int dy = row % side - ring, dz = row / side - ring;
+                    const int yy = cy + dy, zz = cz + dz;
+                    if (yy >= 0 && yy < gm.g[1] && zz >= 0 && zz < gm.g[2]) {
+                        const bool shell_row = (ring == 1) || abs(dy) == ring || abs(dz) == ring;
+                        int x0, x1;   // inclusive cell range
+                        if (shell_row) {
+                            x0 = which == 0 ? cx - ring : 1;
+                            x1 = which == 0 ? cx + ring : 0;
+                        } else {
+                            x0 = x1 = which == 0 ? cx - ring : cx + ring;
+                            if (x0 < 0 || x0 >= gm.g[0]) { x0 = 1; x1 = 0; }
+                        }
+                        x0 = max(x0, 0);
+                        x1 = min(x1, gm.g[0] - 1);
+                        if (x0 <= x1) {
+                            const int64_t rb = ((int64_t)zz * gm.g[1] + yy) * gm.g[0];
+                            s = __ldg(a.cell_start + rb + x0);
+                            e = __ldg(a.cell_start + rb + x1 + 1);
+                        }
+                    }
+                }
+                unsigned nonempty = __ballot_sync(kFull, e > s);
+                while (nonempty) {
+                    const int src = __ffs(nonempty) - 1;
+                    nonempty &= nonempty - 1;
+                    const int rs = __shfl_sync(kFull, s, src), re = __shfl_sync(kFull, e, src);
+                    touched += (unsigned long long)(re - rs);
+                    for (int b = rs; b < re; b += 32) {
+                        const int j = b + lane;
+                        const bool valid = j < re;
+                        float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid) p = __ldg(a.pts + j);
+                        offer(p.x, p.y, p.z, (uint32_t)__float_as_int(p.w), valid);
+                    }
+                }
+            }
+            // ---- termination: nearest unscanned face (inf when the block reaches the border)
+            float b = __uint_as_float(kInfBits);
+            const float qv[3] = {qx, qy, qz};
+            const int cc[3] = {cx, cy, cz};
+#pragma unroll
+            for (int ax = 0; ax < 3; ++ax) {
+                if (cc[ax] - ring > 0) b = fminf(b, qv[ax] - (gm.mn[ax] + (float)(cc[ax] - ring) * gm.cs));
+                if (cc[ax] + ring + 1 < gm.g[ax]) b = fminf(b, (gm.mn[ax] + (float)(cc[ax] + ring + 1) * gm.cs) - qv[ax]);
+            }
+            if (b == __uint_as_float(kInfBits)) break;               // whole grid scanned
+            const float bs = fmaxf(0.f, b - 2e-3f * gm.cs);
+            const float b2 = bs * bs * (1.f - 2e-6f);
+            if (b2 > lim) break;                                      // nothing farther is admissible
+            if (tau_d != sent && tau_f < b2) break;                   // k found, all closer than the rest
+        }
+    }
+
+    if (lane < a.k) {
+        const bool empty = (L.d == sent);
+        a.idx[qi * a.k + lane] = empty ? -1 : (int32_t)((int64_t)L.i + a.index_base);
+        a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
+    }
+    if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+}
+
+inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,
+                    const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
+                    const float* d_radii, int32_t* d_idx, float* d_d2, int64_t index_base,
+                    unsigned long long* counter, cudaStream_t st) {
+    GridKnnArgs a;
+    a.gm = G.geom;
+    a.pts = G.pts.p;
+    a.cell_start = G.cell_start.p;
+    a.n_indexed = G.n_indexed;
+    a.x = x; a.y = y; a.z = z; a.n = n;
+    a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
+    a.max_radius = max_radius; a.max_radii = d_radii;
+    a.idx = d_idx; a.d2 = d_d2; a.index_base = index_base; a.counter = counter;
+    grid_knn_kernel<<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+}  // namespace bgr

@@ -1,0 +1,696 @@
+// bgr_map_* — Octomap occupied leaves flattened to bit grids in HBM + batched collision
+// queries.  Reference surface: octomap_Callback/generateBoxesFromOctomap MS:273-306,
+// isStateValid MS:310-351, isLineValid MS:385-471.
+//
+// Data layout in HBM
+//   level 0 : one bit per finest cell, 4x4x4 cells per 64-bit brick word
+//             word = (bz*nby + by)*nbx + bx,  bit = (z&3)<<4 | (y&3)<<2 | (x&3)
+//             (512^3 cells -> 128^3 words = 16 MiB, L2 resident on B200)
+//   level L : same brick format over the grid of aligned 2^L-cell blocks; a set bit says
+//             "one pruned Octomap leaf of size res*2^L covers exactly this block".
+//             Together they are the sparse leaf-box list in implicit form: an occupied cell
+//             finds its leaf with at most kMaxLevel extra bit probes, and the narrow phase
+//             tests the SAME boxes the reference gets from fcl::OcTree::toBoxes().
+//
+// Edge query = major-axis DDA sweep (supercover): an edge is cut into slabs one cell thick
+// along its dominant axis; each (edge, slab) work item covers a <= few-cell rectangle in the
+// other two axes (conservative interval bounds around the capsule hull of the shape), so the
+// items are independent and are spread over the lanes of a CTA by a prefix sum instead of
+// being walked serially per edge (Amanatides-Woo's tMax stepping is inherently sequential).
+// Occupied candidate cells are classified by two closed-form ball tests (deep hit / clear
+// miss, margin 1e-5 m >> MPR tolerance); only ambiguous ones run the exact MPR narrow phase.
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "mpr.cuh"
+
+using namespace bgr;
+
+namespace {
+
+constexpr int kMaxLevel = 5;            // largest pruned leaf kept as one box: 32^3 cells
+constexpr double kBandTol = 1e-6;       // FCL collision_tolerance (libccd mpr_tolerance)
+constexpr double kBandFlag = 2.5e-6;    // inflation used to flag tolerance-determined results
+constexpr double kCertMargin = 1e-5;    // closed-form certificates decide only beyond this
+constexpr double kSweepMargin = 1e-4;   // broadphase hull inflation
+
+struct LevelGrid {
+    uint64_t* bits;
+    int nb[3];   // bricks per axis
+};
+
+struct MapView {
+    double res, inv_res;
+    double origin[3];
+    int dims[3];
+    LevelGrid lv[kMaxLevel + 1];
+    unsigned level_mask;   // bit L set: level L has at least one leaf marker
+};
+
+__device__ __forceinline__ bool test_bit(const LevelGrid& g, int x, int y, int z) {
+    const int64_t w = ((int64_t)(z >> 2) * g.nb[1] + (y >> 2)) * g.nb[0] + (x >> 2);
+    const int b = ((z & 3) << 4) | ((y & 3) << 2) | (x & 3);
+    return (__ldg(g.bits + w) >> b) & 1ull;
+}
+
+// leaf containing occupied finest cell (x,y,z): level and min-corner finest coordinates
+__device__ __forceinline__ int find_leaf(const MapView& m, int x, int y, int z, int& lx, int& ly, int& lz) {
+    for (int L = kMaxLevel; L >= 1; --L) {
+        if (!((m.level_mask >> L) & 1u)) continue;
+        if (test_bit(m.lv[L], x >> L, y >> L, z >> L)) {
+            lx = (x >> L) << L;
+            ly = (y >> L) << L;
+            lz = (z >> L) << L;
+            return L;
+        }
+    }
+    lx = x; ly = y; lz = z;
+    return 0;
+}
+
+__device__ __forceinline__ void leaf_box(const MapView& m, int L, int lx, int ly, int lz, D3& c, double& e) {
+    const double half_cells = 0.5 * (double)(1 << L);
+    c.x = m.origin[0] + ((double)lx + half_cells) * m.res;
+    c.y = m.origin[1] + ((double)ly + half_cells) * m.res;
+    c.z = m.origin[2] + ((double)lz + half_cells) * m.res;
+    e = (m.res * (double)(1 << L)) / 2;
+}
+
+// ------------------------------------------------------------------ rasterisation
+struct LeafRec {
+    int32_t x, y, z, level;   // min corner (finest cells), level
+};
+
+__global__ void raster_kernel(MapView m, const LeafRec* __restrict__ recs, int64_t n, int set) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const LeafRec r = recs[i];
+    const int L = r.level;
+    if (L >= 1) {
+        const LevelGrid& g = m.lv[L];
+        const int X = r.x >> L, Y = r.y >> L, Z = r.z >> L;
+        const int64_t w = ((int64_t)(Z >> 2) * g.nb[1] + (Y >> 2)) * g.nb[0] + (X >> 2);
+        const unsigned long long bit = 1ull << (((Z & 3) << 4) | ((Y & 3) << 2) | (X & 3));
+        if (set) atomicOr((unsigned long long*)g.bits + w, bit);
+        else atomicAnd((unsigned long long*)g.bits + w, ~bit);
+    }
+    const LevelGrid& g0 = m.lv[0];
+    if (L >= 2) {
+        const int nbk = 1 << (L - 2);
+        const int bx0 = r.x >> 2, by0 = r.y >> 2, bz0 = r.z >> 2;
+        for (int bz = 0; bz < nbk; ++bz)
+            for (int by = 0; by < nbk; ++by)
+                for (int bx = 0; bx < nbk; ++bx) {
+                    const int64_t w = ((int64_t)(bz0 + bz) * g0.nb[1] + (by0 + by)) * g0.nb[0] + (bx0 + bx);
+                    g0.bits[w] = set ? ~0ull : 0ull;
+                }
+    } else {
+        unsigned long long mask = 0;
+        const int s = 1 << L;
+        for (int dz = 0; dz < s; ++dz)
+            for (int dy = 0; dy < s; ++dy)
+                for (int dx = 0; dx < s; ++dx)
+                    mask |= 1ull << ((((r.z + dz) & 3) << 4) | (((r.y + dy) & 3) << 2) | ((r.x + dx) & 3));
+        const int64_t w = ((int64_t)(r.z >> 2) * g0.nb[1] + (r.y >> 2)) * g0.nb[0] + (r.x >> 2);
+        if (set) atomicOr((unsigned long long*)g0.bits + w, mask);
+        else atomicAnd((unsigned long long*)g0.bits + w, ~mask);
+    }
+}
+
+__global__ void popcount_kernel(const uint64_t* __restrict__ bits, int64_t n, unsigned long long* out) {
+    unsigned long long c = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        c += __popcll(bits[i]);
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(kFull, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// ------------------------------------------------------------------ spheres (isStateValid)
+// Exact closed form: gap = dist(centre, leaf box) - r in double; hit = gap < 0.
+__global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const float* __restrict__ c3,
+                                                              int64_t n, double radius,
+                                                              uint8_t* __restrict__ hit,
+                                                              uint8_t* __restrict__ band) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
+    int lo[3], hi[3];
+    bool empty = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const double r = radius + kSweepMargin;
+        lo[a] = max(0, (int)floor((c[a] - r - m.origin[a]) * m.inv_res) - 1);
+        hi[a] = min(m.dims[a] - 1, (int)floor((c[a] + r - m.origin[a]) * m.inv_res) + 1);
+        empty |= lo[a] > hi[a];
+    }
+    double gmin = 1e300;
+    if (!empty)
+        for (int z = lo[2]; z <= hi[2]; ++z)
+            for (int y = lo[1]; y <= hi[1]; ++y)
+                for (int x = lo[0]; x <= hi[0]; ++x) {
+                    if (!test_bit(m.lv[0], x, y, z)) continue;
+                    int lx, ly, lz;
+                    const int L = find_leaf(m, x, y, z, lx, ly, lz);
+                    D3 bc;
+                    double e;
+                    leaf_box(m, L, lx, ly, lz, bc, e);
+                    const double tx = fmax(0.0, fabs(c[0] - bc.x) - e), ty = fmax(0.0, fabs(c[1] - bc.y) - e),
+                                 tz = fmax(0.0, fabs(c[2] - bc.z) - e);
+                    double d2 = tx * tx;
+                    d2 += ty * ty;
+                    d2 += tz * tz;
+                    gmin = fmin(gmin, sqrt(d2) - radius);
+                }
+    hit[i] = gmin < 0.0 ? 1 : 0;
+    if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
+}
+
+// ------------------------------------------------------------------ edges (isLineValid)
+constexpr int kEdgeThreads = 256;
+constexpr int kEdgesPerCta = 256;
+constexpr int kQueueCap = 2048;
+
+struct EdgeSetup {       // per-edge broadphase frame, shared memory
+    double c[3], u[3], a0[3];   // centre, unit axis, endpoint A = c - h*u
+    double h;
+    int ax, i_lo, nslab;
+};
+
+enum { F_HIT = 1, F_DEEP = 2, F_INFL = 4, F_DEFL = 8, F_CAP = 16 };
+
+struct EdgeArgs {
+    MapView m;
+    const float* p1;
+    const float* p2;
+    int64_t n;
+    double radius;
+    int shape;
+    uint8_t* hit;
+    uint8_t* band;
+    unsigned long long* stats;   // [4]
+};
+
+__device__ __forceinline__ double gap_center_ball(const EdgeSetup& s, double radius, int shape, const D3& bc,
+                                                  double dr) {
+    // signed "uniform inflation" distance from the shape inflated by dr to the point bc
+    const double wx = bc.x - s.c[0], wy = bc.y - s.c[1], wz = bc.z - s.c[2];
+    const double a = wx * s.u[0] + wy * s.u[1] + wz * s.u[2];
+    if (shape == BGR_SHAPE_CAPSULE) {
+        const double t = fmax(-s.h, fmin(s.h, a));
+        const double ex = wx - t * s.u[0], ey = wy - t * s.u[1], ez = wz - t * s.u[2];
+        return sqrt(ex * ex + ey * ey + ez * ez) - (radius + dr);
+    }
+    const double ex = wx - a * s.u[0], ey = wy - a * s.u[1], ez = wz - a * s.u[2];
+    const double rho = sqrt(ex * ex + ey * ey + ez * ez);
+    const double da = fmax(0.0, fabs(a) - (s.h + dr)), dq = fmax(0.0, rho - (radius + dr));
+    return sqrt(da * da + dq * dq);   // Euclidean distance to the (inflated) cylinder, 0 inside
+}
+
+__global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a) {
+    __shared__ EdgeSetup es[kEdgesPerCta];
+    __shared__ int prefix[kEdgesPerCta + 1];
+    __shared__ unsigned flags[kEdgesPerCta];
+    __shared__ unsigned long long queue[kQueueCap];
+    __shared__ int qcount;
+    __shared__ int warp_sums[kEdgeThreads / 32];
+    __shared__ unsigned long long st_items, st_cand, st_mpr, st_cap;
+
+    const MapView& m = a.m;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t e0 = (int64_t)blockIdx.x * kEdgesPerCta;
+    const int ne = (int)min((int64_t)kEdgesPerCta, a.n - e0);
+    if (tid == 0) { qcount = 0; st_items = st_cand = st_mpr = st_cap = 0; }
+
+    // ---- phase 0: per-edge setup (thread per edge)
+    int myslabs = 0;
+    if (tid < ne) {
+        const int64_t e = e0 + tid;
+        const float p1[3] = {a.p1[3 * e], a.p1[3 * e + 1], a.p1[3 * e + 2]};
+        const float p2[3] = {a.p2[3 * e], a.p2[3 * e + 1], a.p2[3 * e + 2]};
+        const ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+        D3 u = {0, 0, 1};
+        quat_rot(u, o.rot);
+        d3_scale(u, 1.0 / sqrt(d3_dot(u, u)));
+        EdgeSetup s;
+        s.c[0] = o.pos.x; s.c[1] = o.pos.y; s.c[2] = o.pos.z;
+        s.u[0] = u.x; s.u[1] = u.y; s.u[2] = u.z;
+        s.h = o.height;
+        for (int k = 0; k < 3; ++k) s.a0[k] = s.c[k] - s.h * s.u[k];
+        s.ax = 0;
+        if (fabs(s.u[1]) > fabs(s.u[s.ax])) s.ax = 1;
+        if (fabs(s.u[2]) > fabs(s.u[s.ax])) s.ax = 2;
+        const double rm = a.radius + kSweepMargin;
+        const double pa = s.a0[s.ax], pb = s.c[s.ax] + s.h * s.u[s.ax];
+        int lo = (int)floor((fmin(pa, pb) - rm - m.origin[s.ax]) * m.inv_res);
+        int hi = (int)floor((fmax(pa, pb) + rm - m.origin[s.ax]) * m.inv_res);
+        lo = max(lo, 0);
+        hi = min(hi, m.dims[s.ax] - 1);
+        s.i_lo = lo;
+        s.nslab = max(0, hi - lo + 1);
+        const bool finite = isfinite(s.c[0] + s.c[1] + s.c[2] + s.h);
+        if (!finite) s.nslab = 0;
+        es[tid] = s;
+        flags[tid] = 0;
+        myslabs = s.nslab;
+    }
+    // block exclusive prefix sum of slab counts
+    {
+        int inc = myslabs;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < kEdgeThreads / 32 ? warp_sums[lane] : 0;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(kFull, w, o);
+                if (lane >= o) w += t;
+            }
+            if (lane < kEdgeThreads / 32) warp_sums[lane] = w;
+        }
+        __syncthreads();
+        const int off = warp ? warp_sums[warp - 1] : 0;
+        prefix[tid + 1] = off + inc;
+        if (tid == 0) prefix[0] = 0;
+    }
+    __syncthreads();
+    const int total = prefix[kEdgesPerCta];
+
+    // ---- phase 1: sweep.  work item = (edge, slab)
+    unsigned long long n_cand = 0, n_mpr = 0, n_cap = 0;
+    const double rm = a.radius + kSweepMargin;
+    const double sqrt3 = 1.7320508075688772;
+    for (int w = tid; w < total; w += kEdgeThreads) {
+        int lo = 0, hi = kEdgesPerCta;   // largest el with prefix[el] <= w
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (prefix[mid] <= w) lo = mid; else hi = mid;
+        }
+        const int el = lo;
+        const EdgeSetup& s = es[el];
+        const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
+        const int i = s.i_lo + (w - prefix[el]);
+        const double x0 = m.origin[ax] + (double)i * m.res - rm, x1 = m.origin[ax] + (double)(i + 1) * m.res + rm;
+        // parameter range of the axis segment A + t*(2h u), t in [0,1], inside [x0,x1] on ax
+        const double dax = 2.0 * s.h * s.u[ax];
+        double t0 = 0.0, t1 = 1.0;
+        if (fabs(dax) > 1e-12) {
+            const double ta = (x0 - s.a0[ax]) / dax, tb = (x1 - s.a0[ax]) / dax;
+            t0 = fmax(0.0, fmin(ta, tb));
+            t1 = fmin(1.0, fmax(ta, tb));
+        }
+        if (t0 > t1) continue;   // slab only touched by the hull's end caps: covered below by margins
+        int r0[3], r1[3];
+        r0[ax] = r1[ax] = i;
+        bool none = false;
+        for (int k = 0; k < 2; ++k) {
+            const int b = k ? cx : bx;
+            const double pa = s.a0[b] + t0 * 2.0 * s.h * s.u[b], pb = s.a0[b] + t1 * 2.0 * s.h * s.u[b];
+            int lo_b = (int)floor((fmin(pa, pb) - rm - m.origin[b]) * m.inv_res);
+            int hi_b = (int)floor((fmax(pa, pb) + rm - m.origin[b]) * m.inv_res);
+            lo_b = max(lo_b, 0);
+            hi_b = min(hi_b, m.dims[b] - 1);
+            r0[b] = lo_b;
+            r1[b] = hi_b;
+            none |= lo_b > hi_b;
+        }
+        if (none) continue;
+        for (int jc = r0[cx]; jc <= r1[cx]; ++jc)
+            for (int jb = r0[bx]; jb <= r1[bx]; ++jb) {
+                int v[3];
+                v[ax] = i; v[bx] = jb; v[cx] = jc;
+                if (!test_bit(m.lv[0], v[0], v[1], v[2])) continue;
+                int l[3];
+                const int L = find_leaf(m, v[0], v[1], v[2], l[0], l[1], l[2]);
+                // one representative cell per (item, leaf)
+                if (jb != max(r0[bx], l[bx]) || jc != max(r0[cx], l[cx])) continue;
+                ++n_cand;
+                D3 bc;
+                double e;
+                leaf_box(m, L, l[0], l[1], l[2], bc, e);
+                // certificates from the leaf's circumscribed / inscribed balls
+                const double g_out = gap_center_ball(s, a.radius, a.shape, bc, kCertMargin);
+                if (g_out > e * sqrt3 * (1.0 + 1e-9)) continue;                 // clear miss
+                bool deep = false;
+                if (a.shape == BGR_SHAPE_CAPSULE || s.h > kCertMargin) {
+                    const double g_in = gap_center_ball(s, a.radius, a.shape, bc, -kCertMargin);
+                    deep = a.shape == BGR_SHAPE_CAPSULE ? (g_in < e) : (g_in < e && a.radius > kCertMargin);
+                }
+                if (deep) {
+                    atomicOr(&flags[el], F_HIT | F_DEEP);
+                    continue;
+                }
+                const unsigned long long rec = ((unsigned long long)el << 40) | ((unsigned long long)L << 36) |
+                                               ((unsigned long long)l[0] << 24) | ((unsigned long long)l[1] << 12) |
+                                               (unsigned long long)l[2];
+                const int slot = atomicAdd(&qcount, 1);
+                if (slot < kQueueCap) queue[slot] = rec;
+                else {
+                    // queue overflow: run the narrow phase inline (rare)
+                    const int64_t eg = e0 + el;
+                    const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
+                    const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
+                    ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+                    int capped = 0;
+                    unsigned f = 0;
+                    if (mpr_shape_box(o, bc, e, kBandTol, &capped)) f |= F_HIT;
+                    ++n_mpr;
+                    if (a.band) {
+                        ShapeObj oi = o, od = o;
+                        oi.radius += kBandFlag; od.radius = fmax(0.0, od.radius - kBandFlag);
+                        if (o.type == kShapeCyl) { oi.height += kBandFlag; od.height = fmax(0.0, od.height - kBandFlag); }
+                        if (mpr_shape_box(oi, bc, e, kBandTol, &capped)) f |= F_INFL;
+                        if (mpr_shape_box(od, bc, e, kBandTol, &capped)) f |= F_DEFL;
+                        n_mpr += 2;
+                    }
+                    if (capped) { f |= F_CAP; ++n_cap; }
+                    if (f) atomicOr(&flags[el], f);
+                }
+            }
+    }
+    __syncthreads();
+
+    // ---- phase 2: exact narrow phase on the queued (edge, leaf) pairs
+    const int nq = min(qcount, kQueueCap);
+    for (int ci = tid; ci < nq; ci += kEdgeThreads) {
+        const unsigned long long rec = queue[ci];
+        const int el = (int)(rec >> 40);
+        if (flags[el] & F_DEEP) continue;
+        const int L = (int)((rec >> 36) & 15), lx = (int)((rec >> 24) & 4095), ly = (int)((rec >> 12) & 4095),
+                  lz = (int)(rec & 4095);
+        D3 bc;
+        double e;
+        leaf_box(m, L, lx, ly, lz, bc, e);
+        const int64_t eg = e0 + el;
+        const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
+        const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
+        ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+        int capped = 0;
+        unsigned f = 0;
+        const bool h = mpr_shape_box(o, bc, e, kBandTol, &capped) != 0;
+        ++n_mpr;
+        if (h) f |= F_HIT;
+        if (a.band) {
+            // flag results that flip under a +-2.5e-6 m inflation (covers MPR's 1e-6 band)
+            ShapeObj o2 = o;
+            if (h) {
+                o2.radius = fmax(0.0, o2.radius - kBandFlag);
+                if (o.type == kShapeCyl) o2.height = fmax(0.0, o2.height - kBandFlag);
+                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_DEFL;
+            } else {
+                o2.radius += kBandFlag;
+                if (o.type == kShapeCyl) o2.height += kBandFlag;
+                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_INFL;
+            }
+            ++n_mpr;
+        }
+        if (capped) { f |= F_CAP; ++n_cap; }
+        if (f) atomicOr(&flags[el], f);
+    }
+    __syncthreads();
+
+    if (tid < ne) {
+        const unsigned f = flags[tid];
+        const bool h = (f & F_HIT) != 0;
+        a.hit[e0 + tid] = h ? 1 : 0;
+        if (a.band) {
+            const bool b = !(f & F_DEEP) && ((h && !(f & F_DEFL)) || (!h && (f & F_INFL)) || (f & F_CAP));
+            a.band[e0 + tid] = b ? 1 : 0;
+        }
+    }
+    if (a.stats) {
+        atomicAdd(&st_cand, n_cand);
+        atomicAdd(&st_mpr, n_mpr);
+        atomicAdd(&st_cap, n_cap);
+        __syncthreads();
+        if (tid == 0) {
+            atomicAdd(a.stats + 0, (unsigned long long)total);
+            atomicAdd(a.stats + 1, st_cand);
+            atomicAdd(a.stats + 2, st_mpr);
+            atomicAdd(a.stats + 3, st_cap);
+        }
+    }
+}
+
+}  // namespace
+
+// ====================================================================== host side
+struct bgr_map {
+    cudaStream_t stream = nullptr;
+    double res = 0;
+    double origin[3] = {0, 0, 0};
+    int dims[3] = {0, 0, 0};
+    DevBuf<uint64_t> bits[kMaxLevel + 1];
+    int64_t words[kMaxLevel + 1] = {0};
+    int nb[kMaxLevel + 1][3];
+    unsigned level_mask = 0;
+    int64_t level_count[kMaxLevel + 1] = {0};
+    DevBuf<LeafRec> recs;
+    DevBuf<float> p1_dev, p2_dev;
+    DevBuf<uint8_t> hit_dev, band_dev;
+    DevBuf<unsigned long long> stats;
+    uint64_t last_stats[4] = {0, 0, 0, 0};
+
+    MapView view() const {
+        MapView v;
+        v.res = res;
+        v.inv_res = 1.0 / res;
+        for (int a = 0; a < 3; ++a) { v.origin[a] = origin[a]; v.dims[a] = dims[a]; }
+        for (int L = 0; L <= kMaxLevel; ++L) {
+            v.lv[L].bits = bits[L].p;
+            for (int a = 0; a < 3; ++a) v.lv[L].nb[a] = nb[L][a];
+        }
+        v.level_mask = level_mask;
+        return v;
+    }
+};
+
+namespace {
+
+// toBoxes() rows -> validated integer leaf records (leaves larger than 2^kMaxLevel cells are
+// split into 2^kMaxLevel blocks: the union is identical, only MPR's sub-tolerance behaviour
+// on the interior faces can differ)
+int boxes_to_recs(const bgr_map* h, const double* boxes, int64_t nb, std::vector<LeafRec>& out, int64_t counts[kMaxLevel + 1]) {
+    out.clear();
+    out.reserve((size_t)nb);
+    for (int64_t i = 0; i < nb; ++i) {
+        const double* b = boxes + 6 * i;
+        if (!(b[4] >= b[5])) continue;   // toBoxes keeps occupancy >= threshold; be safe on raw lists
+        const double cells = b[3] / h->res;
+        const int L = (int)std::lround(std::log2(cells));
+        BGR_ARG(L >= 0 && L <= 16 && std::fabs(cells - (double)(1 << L)) < 1e-6 * cells,
+                "box %lld: size %g is not res*2^L", (long long)i, b[3]);
+        int32_t c[3];
+        for (int a = 0; a < 3; ++a) {
+            const double v = (b[a] - h->origin[a]) / h->res - 0.5 * (double)(1 << L);
+            const double r = std::round(v);
+            BGR_ARG(std::fabs(v - r) < 1e-4, "box %lld: centre not aligned to the grid on axis %d", (long long)i, a);
+            c[a] = (int32_t)r;
+            BGR_ARG(c[a] >= 0 && (int64_t)c[a] + (1 << L) <= h->dims[a] && (c[a] & ((1 << L) - 1)) == 0,
+                    "box %lld: outside the map or not octree-aligned on axis %d", (long long)i, a);
+        }
+        if (L <= kMaxLevel) {
+            out.push_back({c[0], c[1], c[2], L});
+            counts[L]++;
+        } else {
+            const int s = 1 << kMaxLevel, n = 1 << (L - kMaxLevel);
+            for (int z = 0; z < n; ++z)
+                for (int y = 0; y < n; ++y)
+                    for (int x = 0; x < n; ++x) {
+                        out.push_back({c[0] + x * s, c[1] + y * s, c[2] + z * s, kMaxLevel});
+                        counts[kMaxLevel]++;
+                    }
+        }
+    }
+    return BGR_OK;
+}
+
+int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
+    if (recs.empty()) return BGR_OK;
+    BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
+    raster_kernel<<<(unsigned)div_up((int64_t)recs.size(), 256), 256, 0, h->stream>>>(h->view(), h->recs.p, (int64_t)recs.size(), set);
+    BGR_CUDA(cudaGetLastError());
+    BGR_CUDA(cudaStreamSynchronize(h->stream));   // recs is a host temporary
+    return BGR_OK;
+}
+
+void refresh_mask(bgr_map* h) {
+    h->level_mask = 0;
+    for (int L = 1; L <= kMaxLevel; ++L)
+        if (h->level_count[L] > 0) h->level_mask |= 1u << L;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bgr_map_create(double res, const double origin[3], const int dims[3], bgr_map** out) {
+    BGR_ARG(out != nullptr, "out is null");
+    *out = nullptr;
+    BGR_ARG(res > 0 && origin && dims, "bad map geometry");
+    for (int a = 0; a < 3; ++a) BGR_ARG(dims[a] >= 1 && dims[a] <= 4096, "dims[%d]=%d out of range [1,4096]", a, dims[a]);
+    bgr_map* h = new bgr_map;
+    h->res = res;
+    for (int a = 0; a < 3; ++a) { h->origin[a] = origin[a]; h->dims[a] = dims[a]; }
+    for (int L = 0; L <= kMaxLevel; ++L) {
+        int64_t w = 1;
+        for (int a = 0; a < 3; ++a) {
+            const int cells = (dims[a] + (1 << L) - 1) >> L;
+            h->nb[L][a] = (cells + 3) >> 2;
+            w *= h->nb[L][a];
+        }
+        h->words[L] = w;
+        int rc = h->bits[L].reserve(w, h->stream, false);
+        if (rc == BGR_OK && cudaMemsetAsync(h->bits[L].p, 0, (size_t)w * 8, h->stream) != cudaSuccess) {
+            set_error("cudaMemset failed");
+            rc = BGR_ERR_CUDA;
+        }
+        if (rc != BGR_OK) { bgr_map_destroy(h); return rc; }
+    }
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) { set_error("sync failed"); bgr_map_destroy(h); return BGR_ERR_CUDA; }
+    *out = h;
+    return BGR_OK;
+}
+
+int bgr_map_set_stream(bgr_map* h, void* stream) {
+    BGR_ARG(h != nullptr, "null handle");
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    h->stream = (cudaStream_t)stream;
+    return BGR_OK;
+}
+
+int bgr_map_set_boxes(bgr_map* h, const double* boxes, int64_t nb) {
+    BGR_ARG(h != nullptr && nb >= 0 && (nb == 0 || boxes), "bad set_boxes arguments");
+    std::vector<LeafRec> recs;
+    int64_t counts[kMaxLevel + 1] = {0};
+    BGR_CHECK(boxes_to_recs(h, boxes, nb, recs, counts));
+    for (int L = 0; L <= kMaxLevel; ++L) {
+        BGR_CUDA(cudaMemsetAsync(h->bits[L].p, 0, (size_t)h->words[L] * 8, h->stream));
+        h->level_count[L] = counts[L];
+    }
+    refresh_mask(h);
+    return raster(h, recs, 1);
+}
+
+int bgr_map_update_boxes(bgr_map* h, const double* add, int64_t n_add, const double* rem, int64_t n_rem) {
+    BGR_ARG(h != nullptr && n_add >= 0 && n_rem >= 0, "bad update arguments");
+    std::vector<LeafRec> recs;
+    int64_t counts[kMaxLevel + 1] = {0};
+    if (n_rem > 0) {
+        BGR_CHECK(boxes_to_recs(h, rem, n_rem, recs, counts));
+        for (int L = 0; L <= kMaxLevel; ++L) h->level_count[L] = std::max<int64_t>(0, h->level_count[L] - counts[L]);
+        BGR_CHECK(raster(h, recs, 0));
+    }
+    if (n_add > 0) {
+        std::memset(counts, 0, sizeof(counts));
+        BGR_CHECK(boxes_to_recs(h, add, n_add, recs, counts));
+        for (int L = 0; L <= kMaxLevel; ++L) h->level_count[L] += counts[L];
+        BGR_CHECK(raster(h, recs, 1));
+    }
+    refresh_mask(h);
+    return BGR_OK;
+}
+
+int bgr_map_occupied_cells(bgr_map* h, int64_t* cells) {
+    BGR_ARG(h != nullptr && cells, "bad arguments");
+    BGR_CHECK(h->stats.reserve(4, h->stream, false));
+    BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 8, h->stream));
+    popcount_kernel<<<256, 256, 0, h->stream>>>(h->bits[0].p, h->words[0], h->stats.p);
+    BGR_CUDA(cudaGetLastError());
+    unsigned long long c = 0;
+    BGR_CUDA(cudaMemcpyAsync(&c, h->stats.p, 8, cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    *cells = (int64_t)c;
+    return BGR_OK;
+}
+
+int bgr_map_download_bitmap(bgr_map* h, uint64_t* out, int64_t* n_words) {
+    BGR_ARG(h != nullptr && n_words, "bad arguments");
+    *n_words = h->words[0];
+    if (!out) return BGR_OK;
+    BGR_CUDA(cudaMemcpyAsync(out, h->bits[0].p, (size_t)h->words[0] * 8, cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double radius, uint8_t* d_hit, uint8_t* d_band) {
+    BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_spheres arguments");
+    if (n == 0) return BGR_OK;
+    collide_spheres_kernel<<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+int bgr_map_collide_spheres(bgr_map* h, const float* c, int64_t n, double radius, uint8_t* hit, uint8_t* band) {
+    BGR_ARG(h != nullptr && n >= 0 && (n == 0 || (c && hit)), "bad collide_spheres arguments");
+    if (n == 0) return BGR_OK;
+    BGR_CHECK(h->p1_dev.reserve(3 * n, h->stream, false));
+    BGR_CHECK(h->hit_dev.reserve(n, h->stream, false));
+    BGR_CHECK(h->band_dev.reserve(n, h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, c, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    BGR_CHECK(bgr_map_collide_spheres_dev(h, h->p1_dev.p, n, radius, h->hit_dev.p, band ? h->band_dev.p : nullptr));
+    BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, int64_t n, double radius,
+                              int shape, uint8_t* d_hit, uint8_t* d_band) {
+    BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_edges arguments");
+    BGR_ARG(shape == BGR_SHAPE_CYLINDER || shape == BGR_SHAPE_CAPSULE, "unknown shape %d", shape);
+    BGR_ARG(radius + kSweepMargin < 64 * h->res, "radius too large for the sweep (>= 64 cells)");
+    if (n == 0) return BGR_OK;
+    BGR_CHECK(h->stats.reserve(4, h->stream, false));
+    BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 4 * sizeof(unsigned long long), h->stream));
+    EdgeArgs a;
+    a.m = h->view();
+    a.p1 = d_p1; a.p2 = d_p2; a.n = n; a.radius = radius; a.shape = shape;
+    a.hit = d_hit; a.band = d_band; a.stats = h->stats.p;
+    collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(a);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t n, double radius, int shape,
+                          uint8_t* hit, uint8_t* band) {
+    BGR_ARG(h != nullptr && n >= 0 && (n == 0 || (p1 && p2 && hit)), "bad collide_edges arguments");
+    if (n == 0) return BGR_OK;
+    BGR_CHECK(h->p1_dev.reserve(3 * n, h->stream, false));
+    BGR_CHECK(h->p2_dev.reserve(3 * n, h->stream, false));
+    BGR_CHECK(h->hit_dev.reserve(n, h->stream, false));
+    BGR_CHECK(h->band_dev.reserve(n, h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, p1, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p, p2, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    BGR_CHECK(bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
+                                        band ? h->band_dev.p : nullptr));
+    BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_map_last_stats(bgr_map* h, uint64_t out[4]) {
+    BGR_ARG(h != nullptr && out, "bad arguments");
+    if (!h->stats.p) { out[0] = out[1] = out[2] = out[3] = 0; return BGR_OK; }
+    unsigned long long s[4];
+    BGR_CUDA(cudaMemcpyAsync(s, h->stats.p, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < 4; ++i) out[i] = s[i];
+    return BGR_OK;
+}
+
+int bgr_map_destroy(bgr_map* h) {
+    if (!h) return BGR_OK;
+    cudaStreamSynchronize(h->stream);
+    for (int L = 0; L <= kMaxLevel; ++L) h->bits[L].release();
+    h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
+    h->stats.release();
+    delete h;
+    return BGR_OK;
+}
+
+}  // extern "C"

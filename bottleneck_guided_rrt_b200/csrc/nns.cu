@@ -1,0 +1,376 @@
+// bgr_nns_* — libnabo-shaped nearest-neighbour object over an append-only SoA node store
+// in HBM.  Host side of the C ABI declared in include/bgrrt.h (reference surface:
+// MS:138-154 Nearest, MS:1277-1315 libnabo create/knn/delete).
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "grid.cuh"
+#include "knn_brute.cuh"
+#include "nearest.cuh"
+
+using namespace bgr;
+
+struct bgr_nns {
+    int device = 0;
+    cudaStream_t stream = nullptr;   // borrowed (set_stream) or the legacy default stream
+    unsigned create_flags = 0;
+    int method = BGR_METHOD_AUTO;
+    int64_t index_base = 0;
+    // append-only SoA store, NaN padded to a multiple of kTile
+    DevBuf<float> x, y, z;
+    int64_t n = 0;
+    // scratch
+    DevBuf<float> stage_f;       // interleaved staging for host API / appends
+    DevBuf<float> q_dev, radii_dev, d2_dev, part_d2;
+    DevBuf<int32_t> idx_dev, part_idx;
+    DevBuf<unsigned long long> counter;
+    GridIndex grid;
+};
+
+namespace {
+
+__global__ void deinterleave_kernel(const float* __restrict__ src, int64_t m, float* __restrict__ x,
+                                    float* __restrict__ y, float* __restrict__ z) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < m) {
+        x[i] = src[3 * i];
+        y[i] = src[3 * i + 1];
+        z[i] = src[3 * i + 2];
+    }
+}
+
+int grow_store(bgr_nns* h, int64_t need) {
+    need = round_up(need > 0 ? need : 1, kTile);
+    if (need <= h->x.cap) return BGR_OK;
+    const int64_t old_cap = h->x.cap;
+    BGR_CHECK(h->x.reserve(need, h->stream, true, h->n));
+    BGR_CHECK(h->y.reserve(need, h->stream, true, h->n));
+    BGR_CHECK(h->z.reserve(need, h->stream, true, h->n));
+    (void)old_cap;
+    // 0xFF bytes = NaN: padded nodes can never be admitted by any comparison
+    const int64_t cap = h->x.cap;
+    BGR_CUDA(cudaMemsetAsync(h->x.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
+    BGR_CUDA(cudaMemsetAsync(h->y.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
+    BGR_CUDA(cudaMemsetAsync(h->z.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
+    return BGR_OK;
+}
+
+int append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
+    if (m == 0) return BGR_OK;
+    BGR_ARG(h->n + m < (int64_t)1 << 31, "node count exceeds int32 index range");
+    BGR_CHECK(grow_store(h, h->n + m));
+    deinterleave_kernel<<<(unsigned)div_up(m, 256), 256, 0, h->stream>>>(d_pts, m, h->x.p + h->n,
+                                                                          h->y.p + h->n, h->z.p + h->n);
+    BGR_CUDA(cudaGetLastError());
+    h->n += m;
+    return BGR_OK;
+}
+
+constexpr size_t kBruteSmem = (size_t)kStages * 3 * kTile * sizeof(float) + 2 * kStages * sizeof(uint64_t);
+
+template <int R>
+int launch_brute(bgr_nns* h, BruteArgs a, int chunks) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        BGR_CUDA(cudaFuncSetAttribute(knn_brute_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBruteSmem));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
+    knn_brute_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+template <int R>
+int launch_nearest(bgr_nns* h, NearestArgs a, int chunks) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        BGR_CUDA(cudaFuncSetAttribute(nearest_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBruteSmem));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
+    nearest_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+// queries per warp and node chunks so that the grid fills the machine for >= ~2 waves
+void plan_scan(int64_t nq, int64_t n, int* R, int* chunks, int64_t* chunk_nodes) {
+    const int sms = num_sms();
+    int r = 8;
+    while (r > 1 && div_up(nq, (int64_t)kConsumerWarps * r) < 2 * sms) r >>= 1;
+    const int64_t qblocks = div_up(nq, (int64_t)kConsumerWarps * r);
+    const int64_t tiles = div_up(n > 0 ? n : 1, kTile);
+    int64_t c = 1;
+    const int64_t resident = 3LL * sms;
+    if (qblocks < 2 * resident) c = div_up(2 * resident, qblocks);
+    c = std::min<int64_t>(c, std::max<int64_t>(1, tiles / 4));
+    c = std::min<int64_t>(c, 64);
+    int64_t per = div_up(tiles, c) * kTile;
+    c = div_up(tiles * kTile, per);
+    *R = r;
+    *chunks = (int)c;
+    *chunk_nodes = per;
+}
+
+int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
+                  const float* d_radii, int32_t* d_idx, float* d_d2) {
+    int R, chunks;
+    int64_t per;
+    plan_scan(nq, h->n, &R, &chunks, &per);
+    BruteArgs a;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = h->n;
+    a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
+    a.max_radius = max_radius; a.max_radii = d_radii;
+    a.chunk_nodes = per;
+    a.index_base = h->index_base;
+    if (chunks == 1) {
+        a.idx = d_idx; a.d2 = d_d2;
+    } else {
+        BGR_CHECK(h->part_idx.reserve((int64_t)chunks * nq * k, h->stream, false));
+        BGR_CHECK(h->part_d2.reserve((int64_t)chunks * nq * k, h->stream, false));
+        a.idx = h->part_idx.p; a.d2 = h->part_d2.p;
+    }
+    switch (R) {
+        case 8: BGR_CHECK(launch_brute<8>(h, a, chunks)); break;
+        case 4: BGR_CHECK(launch_brute<4>(h, a, chunks)); break;
+        case 2: BGR_CHECK(launch_brute<2>(h, a, chunks)); break;
+        default: BGR_CHECK(launch_brute<1>(h, a, chunks)); break;
+    }
+    if (chunks > 1) {
+        knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
+                                                                         nq, k, d_idx, d_d2);
+        BGR_CUDA(cudaGetLastError());
+    }
+    return BGR_OK;
+}
+
+int check_knn_args(const bgr_nns* h, int64_t nq, int k, float eps, unsigned flags, float max_radius) {
+    BGR_ARG(h != nullptr, "null nns handle");
+    BGR_ARG(nq >= 0, "negative query count");
+    BGR_ARG((flags & ~(BGR_ALLOW_SELF_MATCH | BGR_SORT_RESULTS)) == 0,
+            "OR-ed value of option flags (%u) is larger than maximal valid value (3)", flags);
+    BGR_ARG(k >= 1, "k must be >= 1");
+    if (flags & BGR_ALLOW_SELF_MATCH)
+        BGR_ARG(k <= h->n, "Requesting more points (%d) than available in cloud (%lld)", k, (long long)h->n);
+    else
+        BGR_ARG(k <= h->n - 1,
+                "Requesting more points (%d) than available in cloud minus 1 (%lld) (as self match is forbidden)",
+                k, (long long)(h->n - 1));
+    if (eps != 0.f) {
+        set_error("approximate search (epsilon=%g) is not offered: exact search only", (double)eps);
+        return BGR_ERR_UNSUPPORTED;
+    }
+    BGR_ARG(!(max_radius < 0.f) && max_radius == max_radius, "maxRadius must be >= 0");
+    if (k > 32) {
+        set_error("k=%d > 32 is not supported by the warp top-k in this build", k);
+        return BGR_ERR_UNSUPPORTED;
+    }
+    return BGR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bgr_nns_create_dev(const float* d_cloud, int64_t n, int dim, unsigned create_flags, void* stream,
+                       bgr_nns** out) {
+    BGR_ARG(out != nullptr, "out is null");
+    *out = nullptr;
+    BGR_ARG(n >= 0, "negative point count");
+    if (dim != 3) {
+        set_error("dim=%d: only 3-D clouds are supported (the planner's state space)", dim);
+        return BGR_ERR_UNSUPPORTED;
+    }
+    BGR_ARG((create_flags & ~BGR_TOUCH_STATISTICS) == 0, "unknown creation flags %u", create_flags);
+    int dev = 0;
+    BGR_CUDA(cudaGetDevice(&dev));
+    bgr_nns* h = new bgr_nns;
+    h->device = dev;
+    h->stream = (cudaStream_t)stream;
+    h->create_flags = create_flags;
+    int rc = grow_store(h, n);
+    if (rc == BGR_OK && n > 0) rc = append_dev(h, d_cloud, n);
+    if (rc != BGR_OK) {
+        bgr_nns_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return BGR_OK;
+}
+
+int bgr_nns_create(const float* cloud, int64_t n, int dim, unsigned create_flags, bgr_nns** out) {
+    BGR_ARG(out != nullptr, "out is null");
+    *out = nullptr;
+    BGR_ARG(n == 0 || cloud != nullptr, "cloud is null");
+    bgr_nns* h = nullptr;
+    BGR_CHECK(bgr_nns_create_dev(nullptr, 0, dim, create_flags, nullptr, &h));
+    int rc = bgr_nns_append(h, cloud, n);
+    if (rc != BGR_OK) {
+        bgr_nns_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return BGR_OK;
+}
+
+int bgr_nns_append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
+    BGR_ARG(h != nullptr && m >= 0, "bad append arguments");
+    return append_dev(h, d_pts, m);
+}
+
+int bgr_nns_append(bgr_nns* h, const float* pts, int64_t m) {
+    BGR_ARG(h != nullptr && m >= 0 && (m == 0 || pts != nullptr), "bad append arguments");
+    if (m == 0) return BGR_OK;
+    BGR_CHECK(h->stage_f.reserve(3 * m, h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->stage_f.p, pts, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    BGR_CHECK(append_dev(h, h->stage_f.p, m));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int64_t bgr_nns_size(const bgr_nns* h) { return h ? h->n : -1; }
+
+int bgr_nns_set_stream(bgr_nns* h, void* stream) {
+    BGR_ARG(h != nullptr, "null handle");
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    h->stream = (cudaStream_t)stream;
+    return BGR_OK;
+}
+
+int bgr_nns_set_method(bgr_nns* h, int method) {
+    BGR_ARG(h != nullptr && method >= 0 && method <= 2, "bad method");
+    h->method = method;
+    return BGR_OK;
+}
+
+int bgr_nns_set_index_base(bgr_nns* h, int64_t base) {
+    BGR_ARG(h != nullptr && base >= 0 && base + h->n < ((int64_t)1 << 31), "bad index base");
+    h->index_base = base;
+    return BGR_OK;
+}
+
+int bgr_nns_build_index(bgr_nns* h) {
+    BGR_ARG(h != nullptr, "null handle");
+    if (h->n == 0) return BGR_OK;
+    return grid_build(h->grid, h->x.p, h->y.p, h->z.p, h->n, h->stream);
+}
+
+int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, unsigned flags,
+                    float max_radius, const float* d_radii, int32_t* d_idx, float* d_d2,
+                    uint64_t* touched) {
+    BGR_CHECK(check_knn_args(h, nq, k, eps, flags, max_radius));
+    if (touched) *touched = 0;
+    if (nq == 0) return BGR_OK;
+    int method = h->method;
+    if (method == BGR_METHOD_AUTO) method = (h->n >= 16384) ? BGR_METHOD_GRID : BGR_METHOD_BRUTE;
+    if (method == BGR_METHOD_GRID) {
+        // re-bucket when the unsorted tail grew past a quarter of the indexed part
+        if (h->grid.n_indexed == 0 || (h->n - h->grid.n_indexed) > std::max<int64_t>(4096, h->grid.n_indexed / 4))
+            BGR_CHECK(grid_build(h->grid, h->x.p, h->y.p, h->z.p, h->n, h->stream));
+        const bool stats = (h->create_flags & BGR_TOUCH_STATISTICS) && touched;
+        if (stats) {
+            BGR_CHECK(h->counter.reserve(1, h->stream, false));
+            BGR_CUDA(cudaMemsetAsync(h->counter.p, 0, sizeof(unsigned long long), h->stream));
+        }
+        BGR_CHECK(grid_knn(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, k, flags, max_radius, d_radii,
+                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, h->stream));
+        if (stats) {
+            unsigned long long c = 0;
+            BGR_CUDA(cudaMemcpyAsync(&c, h->counter.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+            BGR_CUDA(cudaStreamSynchronize(h->stream));
+            *touched = c;
+        }
+        return BGR_OK;
+    }
+    BGR_CHECK(knn_brute_dev(h, d_q, nq, k, flags, max_radius, d_radii, d_idx, d_d2));
+    if (touched) *touched = (uint64_t)nq * (uint64_t)h->n;
+    return BGR_OK;
+}
+
+int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsigned flags,
+                float max_radius, const float* max_radii, int32_t* idx, float* d2, uint64_t* touched) {
+    BGR_CHECK(check_knn_args(h, nq, k, eps, flags, max_radius));
+    BGR_ARG(nq == 0 || (q && idx && d2), "null query/result buffer");
+    if (touched) *touched = 0;
+    if (nq == 0) return BGR_OK;
+    BGR_CHECK(h->q_dev.reserve(3 * nq, h->stream, false));
+    BGR_CHECK(h->idx_dev.reserve(nq * k, h->stream, false));
+    BGR_CHECK(h->d2_dev.reserve(nq * k, h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->q_dev.p, q, (size_t)3 * nq * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    const float* d_radii = nullptr;
+    if (max_radii) {
+        BGR_CHECK(h->radii_dev.reserve(nq, h->stream, false));
+        BGR_CUDA(cudaMemcpyAsync(h->radii_dev.p, max_radii, (size_t)nq * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        d_radii = h->radii_dev.p;
+    }
+    BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
+                              h->d2_dev.p, touched));
+    BGR_CUDA(cudaMemcpyAsync(idx, h->idx_dev.p, (size_t)nq * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaMemcpyAsync(d2, h->d2_dev.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, float* d_dist) {
+    BGR_ARG(h != nullptr && nq >= 0, "bad nearest arguments");
+    BGR_ARG(h->n >= 1, "Nearest on an empty tree");
+    if (nq == 0) return BGR_OK;
+    int R, chunks;
+    int64_t per;
+    plan_scan(nq, h->n, &R, &chunks, &per);
+    if (R > 4) R = 4;   // double-precision state: keep registers in check
+    NearestArgs a;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = h->n;
+    a.q = d_q; a.nq = nq; a.chunk_nodes = per; a.index_base = h->index_base;
+    BGR_CHECK(h->part_idx.reserve((int64_t)chunks * nq, h->stream, false));
+    BGR_CHECK(h->part_d2.reserve((int64_t)chunks * nq, h->stream, false));
+    a.idx = h->part_idx.p; a.dist = h->part_d2.p;
+    switch (R) {
+        case 4: BGR_CHECK(launch_nearest<4>(h, a, chunks)); break;
+        case 2: BGR_CHECK(launch_nearest<2>(h, a, chunks)); break;
+        default: BGR_CHECK(launch_nearest<1>(h, a, chunks)); break;
+    }
+    nearest_reduce_kernel<<<(unsigned)div_up(nq, 256), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
+                                                                            nq, d_idx, d_dist);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+int bgr_nns_nearest(bgr_nns* h, const float* q, int64_t nq, int32_t* idx, float* dist) {
+    BGR_ARG(h != nullptr && nq >= 0 && (nq == 0 || (q && idx)), "bad nearest arguments");
+    BGR_ARG(h->n >= 1, "Nearest on an empty tree");
+    if (nq == 0) return BGR_OK;
+    BGR_CHECK(h->q_dev.reserve(3 * nq, h->stream, false));
+    BGR_CHECK(h->idx_dev.reserve(nq, h->stream, false));
+    BGR_CHECK(h->d2_dev.reserve(nq, h->stream, false));
+    BGR_CUDA(cudaMemcpyAsync(h->q_dev.p, q, (size_t)3 * nq * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    BGR_CHECK(bgr_nns_nearest_dev(h, h->q_dev.p, nq, h->idx_dev.p, h->d2_dev.p));
+    BGR_CUDA(cudaMemcpyAsync(idx, h->idx_dev.p, (size_t)nq * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (dist)
+        BGR_CUDA(cudaMemcpyAsync(dist, h->d2_dev.p, (size_t)nq * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_nns_destroy(bgr_nns* h) {
+    if (!h) return BGR_OK;
+    cudaStreamSynchronize(h->stream);
+    h->x.release(); h->y.release(); h->z.release();
+    h->stage_f.release(); h->q_dev.release(); h->radii_dev.release(); h->d2_dev.release();
+    h->part_d2.release(); h->idx_dev.release(); h->part_idx.release(); h->counter.release();
+    grid_release(h->grid);
+    delete h;
+    return BGR_OK;
+}
+
+int bgr_knn_merge_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int64_t nq, int k,
+                      int32_t* d_idx, float* d_d2, void* stream) {
+    BGR_ARG(g >= 1 && nq >= 0 && k >= 1 && k <= 32, "bad merge arguments (k<=32)");
+    if (nq == 0) return BGR_OK;
+    knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, (cudaStream_t)stream>>>(d_idx_in, d_d2_in, g, nq, k, d_idx, d_d2);
+    BGR_CUDA(cudaGetLastError());
+    return BGR_OK;
+}
+
+}  // extern "C"

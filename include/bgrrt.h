@@ -1,0 +1,150 @@
+/*
+ * bgrrt.h — C ABI of the B200-native hot paths of the bottleneck-guided RRT* planner.
+ *
+ * Drop-in boundary for the two data-parallel paths of
+ * indraneelpatil/bottleneck_guided_rrt, abb_manipulator/src/rrt_star_milestones.cpp ("MS"):
+ *   (1) nearest-neighbour search  — Nearest() MS:138-154 and the libnabo object built at
+ *       MS:1306 (Nabo::NNSearchF::createKDTreeLinearHeap) and queried at MS:1312 (knn);
+ *   (2) collision queries          — isStateValid() MS:310-351 (FCL Sphere vs every Octomap
+ *       leaf box) and isLineValid() MS:385-471 (FCL Cylinder vs every leaf box), fed by
+ *       generateBoxesFromOctomap() MS:288-306 / fcl::OcTree::toBoxes().
+ * The reference has no FFI; these entry points are what a cgo/ctypes/C++ binding for that
+ * call surface binds (INTEGRATION.md shows the planner-side stub).  Plain pointers and
+ * sizes only; no C++ or torch types.  Every function returns 0 on success or a negative
+ * bgr_status; bgr_last_error() gives the message (thread-local).  There is NO CPU
+ * fallback: without a CUDA device every compute call fails with BGR_ERR_CUDA.
+ *
+ * Layout conventions (libnabo's): a point set is dim x N column-major float, i.e.
+ * x0,y0,z0,x1,y1,z1,...; knn results are k x Q column-major (query c owns [c*k, c*k+k)).
+ * "_dev" variants take DEVICE pointers and are asynchronous on the handle's stream;
+ * the others take HOST pointers, copy through pinned staging and return synchronised.
+ * Handles are not thread-safe (the reference caller is single-threaded).
+ */
+#ifndef BGRRT_H
+#define BGRRT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BGR_VERSION 100
+
+typedef enum bgr_status {
+    BGR_OK = 0,
+    BGR_ERR_ARG = -1,      /* bad argument (libnabo would throw std::runtime_error) */
+    BGR_ERR_CUDA = -2,     /* CUDA runtime error / no device */
+    BGR_ERR_ALLOC = -3,
+    BGR_ERR_UNSUPPORTED = -4,
+    BGR_ERR_STATE = -5
+} bgr_status;
+
+const char* bgr_last_error(void);
+int bgr_version(void);
+int bgr_device_count(int* count);
+/* SM count, SM clock (kHz), L2 bytes of the current device */
+int bgr_device_info(int* sms, int* sm_clock_khz, int64_t* l2_bytes);
+
+/* ------------------------------------------------------------------ nearest neighbours */
+typedef struct bgr_nns bgr_nns;
+
+/* libnabo search option flags (nabo.h SearchOptionFlags) and creation flags */
+#define BGR_ALLOW_SELF_MATCH 1u
+#define BGR_SORT_RESULTS 2u      /* accepted; results are always ascending by (d2, index) */
+#define BGR_TOUCH_STATISTICS 1u  /* creation flag: knn reports evaluated (query,node) pairs */
+
+/* search methods for bgr_nns_set_method */
+#define BGR_METHOD_AUTO 0
+#define BGR_METHOD_BRUTE 1   /* exact brute-force scan (FP32-pipe bound) */
+#define BGR_METHOD_GRID 2    /* exact grid-bucketed scan with ring expansion */
+
+/* Replaces Nabo::NNSearchF::createKDTreeLinearHeap(cloud) (MS:1306).  cloud is copied to
+ * an append-only SoA buffer in HBM (libnabo keeps a reference instead).  n may be 0. */
+int bgr_nns_create(const float* cloud_3xN, int64_t n, int dim, unsigned create_flags,
+                   bgr_nns** out);
+int bgr_nns_create_dev(const float* d_cloud_3xN, int64_t n, int dim, unsigned create_flags,
+                       void* cuda_stream, bgr_nns** out);
+/* Replaces the per-iteration rebuild MS:1277-1306: appends m points (indices continue). */
+int bgr_nns_append(bgr_nns* nns, const float* pts_3xM, int64_t m);
+int bgr_nns_append_dev(bgr_nns* nns, const float* d_pts_3xM, int64_t m);
+int64_t bgr_nns_size(const bgr_nns* nns);
+int bgr_nns_set_stream(bgr_nns* nns, void* cuda_stream);
+int bgr_nns_set_method(bgr_nns* nns, int method);
+/* indices returned by knn/nearest are local index + base (index-range shards, §8e) */
+int bgr_nns_set_index_base(bgr_nns* nns, int64_t base);
+/* (re)build the grid index now instead of lazily at the next query */
+int bgr_nns_build_index(bgr_nns* nns);
+
+/* Replaces nns->knn(q, indices, dists2, k, eps, flags, maxRadius) (MS:1309-1312) and its
+ * matrix / per-query-maxRadii overloads.  Exact search only: eps must be 0.
+ * d2 = ((dx*dx)+dy*dy)+dz*dz in f32, every operation rounded, no FMA; admission
+ * d2<=maxRadius^2 && (ALLOW_SELF_MATCH || d2>FLT_EPSILON); output ascending by (d2,index);
+ * unfilled slots idx=-1, d2=+inf.  Errors like libnabo's checkSizesKnn: k > N (or N-1
+ * without self match), unknown flag bits.  max_radii (Q floats) may be NULL.
+ * touched (may be NULL) receives the number of (query,node) pairs evaluated. */
+int bgr_nns_knn(bgr_nns* nns, const float* q_3xQ, int64_t nq, int k, float eps,
+                unsigned flags, float max_radius, const float* max_radii,
+                int32_t* idx_kxQ, float* d2_kxQ, uint64_t* touched);
+int bgr_nns_knn_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, float eps,
+                    unsigned flags, float max_radius, const float* d_max_radii,
+                    int32_t* d_idx_kxQ, float* d_d2_kxQ, uint64_t* touched);
+
+/* Replaces Nearest(V, x) (MS:138-154) for a batch of x: Norm in the reference's mixed
+ * precision (f32 differences, f64 squares/sum/sqrt, f32 result), `<=` so the LAST index
+ * among float-equal minima wins.  dist may be NULL. */
+int bgr_nns_nearest(bgr_nns* nns, const float* q_3xQ, int64_t nq, int32_t* idx, float* dist);
+int bgr_nns_nearest_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int32_t* d_idx,
+                        float* d_dist);
+int bgr_nns_destroy(bgr_nns* nns);
+
+/* Merge G per-shard top-k slabs (each k x Q, ascending, global indices) into one top-k by
+ * (d2, index) — the exchange step after the all-gather of an index-range-sharded search. */
+int bgr_knn_merge_dev(const int32_t* d_idx_GxkxQ, const float* d_d2_GxkxQ, int g,
+                      int64_t nq, int k, int32_t* d_idx_kxQ, float* d_d2_kxQ,
+                      void* cuda_stream);
+
+/* ------------------------------------------------------------------ occupancy map */
+typedef struct bgr_map bgr_map;
+
+#define BGR_SHAPE_CYLINDER 0 /* fcl::Cylinder(radius, |p2-p1|): the reference, MS:437 */
+#define BGR_SHAPE_CAPSULE 1  /* fcl::Capsule on the same frame (conservative superset) */
+
+/* Octomap view: finest resolution res, grid origin (min corner), dims in finest cells. */
+int bgr_map_create(double res, const double origin[3], const int dims[3], bgr_map** out);
+int bgr_map_set_stream(bgr_map* map, void* cuda_stream);
+/* Replaces octomap_Callback + generateBoxesFromOctomap (MS:273-306): boxes is B x 6
+ * row-major {x,y,z,size,occupancy,threshold} = fcl::OcTree::toBoxes(); kept if
+ * occupancy >= threshold.  Boxes must be octree-aligned cubes of res*2^L.  Clears first. */
+int bgr_map_set_boxes(bgr_map* map, const double* boxes_Bx6, int64_t nb);
+/* incremental refresh: remove then add leaf boxes (same layout) */
+int bgr_map_update_boxes(bgr_map* map, const double* add_Bx6, int64_t n_add,
+                         const double* remove_Bx6, int64_t n_remove);
+int bgr_map_occupied_cells(bgr_map* map, int64_t* cells);
+/* copy the occupancy bitmap (one bit per finest cell, 4x4x4 bricks) to host; bytes may be
+ * queried with out==NULL */
+int bgr_map_download_bitmap(bgr_map* map, uint64_t* out, int64_t* n_words);
+
+/* Replaces isStateValid(point) (MS:310-351) for a batch: hit[i]=1 means IN COLLISION
+ * (reference polarity).  in_band[i]=1 when the closest contact lies within the 1e-6 m
+ * tolerance band of FCL's MPR solver (result tolerance-determined).  in_band may be NULL.
+ * An empty map reports free (the reference returns a stale flag there). */
+int bgr_map_collide_spheres(bgr_map* map, const float* c_3xM, int64_t m, double radius,
+                            uint8_t* hit, uint8_t* in_band);
+int bgr_map_collide_spheres_dev(bgr_map* map, const float* d_c_3xM, int64_t m, double radius,
+                                uint8_t* d_hit, uint8_t* d_in_band);
+/* Replaces isLineValid(p1,p2) (MS:385-471) for a batch of edges. */
+int bgr_map_collide_edges(bgr_map* map, const float* p1_3xM, const float* p2_3xM, int64_t m,
+                          double radius, int shape, uint8_t* hit, uint8_t* in_band);
+int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* d_p2_3xM,
+                              int64_t m, double radius, int shape, uint8_t* d_hit,
+                              uint8_t* d_in_band);
+/* counters of the last collide_edges call: [0] work items (edge,slab), [1] occupied
+ * candidate voxels, [2] exact narrow-phase tests, [3] narrow-phase iteration-cap events */
+int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
+int bgr_map_destroy(bgr_map* map);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BGRRT_H */

@@ -1,0 +1,215 @@
+"""GPU parity: bgr_map_* (through the C ABI) vs the CPU oracle's FCL/libccd-MPR restatement.
+
+Reference surface: generateBoxesFromOctomap (rrt_star_milestones.cpp:288-306),
+isStateValid (:310-351), isLineValid (:385-471).  Booleans must be identical except inside
+the 1e-6 m MPR tolerance band, which the library flags (in_band) and the test counts."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _map(B, O, n=64, seed=1, max_level=2, **kw):
+    occ = O.make_map(n, seed=seed, **kw)
+    boxes = O.grid_to_boxes(occ, 0.05, (0, 0, 0), max_level)
+    m = B.OccupancyMap(0.05, (0, 0, 0), (n, n, n))
+    m.set_boxes(boxes)
+    return occ, boxes, m
+
+
+def _bits_to_occ(words, n):
+    nb = (n + 3) // 4
+    w = words.reshape(nb, nb, nb)  # [bz][by][bx]
+    occ = np.zeros((n, n, n), dtype=np.uint8)
+    for z in range(4):
+        for y in range(4):
+            for x in range(4):
+                bit = (z << 4) | (y << 2) | x
+                occ[z::4, y::4, x::4] = ((w >> np.uint64(bit)) & np.uint64(1)).astype(np.uint8)[: (n - z + 3) // 4, : (n - y + 3) // 4, : (n - x + 3) // 4]
+    return occ
+
+
+@pytest.mark.parametrize("max_level", [0, 2, 4])
+def test_flatten_boxes_to_bitmap(bgr, oracle, max_level):
+    occ, boxes, m = _map(bgr, oracle, 64, 1, max_level)
+    assert m.occupied_cells() == int(occ.sum())
+    assert np.array_equal(_bits_to_occ(m.download_bitmap(), 64), occ)
+
+
+def test_incremental_update(bgr, oracle):
+    occ, boxes, m = _map(bgr, oracle, 64, 1, 2)
+    occ2 = oracle.make_map(64, seed=2)
+    b2 = oracle.grid_to_boxes(occ2, 0.05, (0, 0, 0), 2)
+    m.update_boxes(add=None, remove=boxes)
+    assert m.occupied_cells() == 0
+    m.update_boxes(add=b2)
+    assert np.array_equal(_bits_to_occ(m.download_bitmap(), 64), occ2)
+    # partial refresh: drop a tenth of the leaves, add them back
+    part = b2[::10]
+    m.update_boxes(remove=part)
+    assert m.occupied_cells() == int(occ2.sum()) - int(round(((part[:, 3] / 0.05) ** 3).sum()))
+    m.update_boxes(add=part)
+    assert np.array_equal(_bits_to_occ(m.download_bitmap(), 64), occ2)
+
+
+def test_box_validation(bgr, oracle):
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64))
+    with pytest.raises(RuntimeError):
+        m.set_boxes(np.array([[0.03, 0.025, 0.025, 0.05, 1, 0.5]]))      # off-grid centre
+    with pytest.raises(RuntimeError):
+        m.set_boxes(np.array([[0.025, 0.025, 0.025, 0.07, 1, 0.5]]))     # size not res*2^L
+    with pytest.raises(RuntimeError):
+        m.set_boxes(np.array([[4.025, 0.025, 0.025, 0.05, 1, 0.5]]))     # outside
+    m.set_boxes(np.array([[0.025, 0.025, 0.025, 0.05, 0.3, 0.5]]))       # below threshold: ignored
+    assert m.occupied_cells() == 0
+    # empty map => free (the reference returns a stale flag there; documented divergence)
+    assert not m.isStateValid([1.0, 1.0, 1.0]) and not m.isLineValid([0.1, 0.1, 0.1], [3, 3, 3])
+
+
+def _points_near_obstacles(O, occ, n, seed, spread):
+    zz, yy, xx = np.nonzero(occ)
+    mt = O.MT(seed)
+    pick = (mt.real(n) * len(zz)).astype(np.int64)
+    c = np.stack([xx[pick], yy[pick], zz[pick]], 1).astype(np.float64) * 0.05
+    return (c + (mt.real(3 * n).reshape(n, 3) - 0.5) * spread).astype(np.float32)
+
+
+@pytest.mark.parametrize("max_level", [0, 2])
+def test_spheres_match_mpr_oracle(bgr, oracle, max_level):
+    occ, boxes, m = _map(bgr, oracle, 64, 1, max_level)
+    pts = np.concatenate([oracle.points(21, 3000, 3.2), _points_near_obstacles(oracle, occ, 3000, 22, 0.5)])
+    hit, band = m.collide_spheres(pts, 0.1)
+    ohit, oband = oracle.collide_spheres(boxes, pts, 0.1, mode=1)
+    diff = hit != ohit
+    assert not (diff & (band == 0)).any(), "mismatch outside the tolerance band: %d" % int((diff & (band == 0)).sum())
+    assert np.array_equal(band, oband)
+    assert 0.2 < hit.mean() < 0.98
+
+
+def test_spheres_known_answers(bgr, oracle):
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64))
+    box = np.array([[1.025, 1.025, 1.025, 0.05, 1.0, 0.5]])
+    m.set_boxes(box)
+    for sep, want in ((1e-3, 0), (1e-5, 0), (-1e-5, 1), (-1e-3, 1)):
+        for d in np.eye(3):
+            c = np.array([1.025, 1.025, 1.025]) + d * (0.025 + 0.1 + sep)
+            c32 = c.astype(np.float32)
+            gap = oracle.sep_sphere_box(c32.astype(np.float64), 0.1, box[0, :3], 0.05)
+            hit, band = m.collide_spheres(c32.reshape(1, 3), 0.1)
+            assert hit[0] == (1 if gap < 0 else 0)
+            assert band[0] == (1 if abs(gap) <= 1e-6 else 0)
+            if abs(sep) >= 1e-4:
+                assert hit[0] == want == int(oracle.mpr_sphere_box(c32.astype(np.float64), 0.1, box[0, :3], 0.05)[0])
+
+
+def _edges(O, occ, n, seed, lo=0.15, hi=3.0, extent=3.2):
+    mt = O.MT(seed)
+    p1 = _points_near_obstacles(O, occ, n, seed + 1, 1.0)
+    u = mt.real(2 * n).reshape(n, 2)
+    ct = 2 * u[:, 0] - 1
+    st = np.sqrt(1 - ct * ct)
+    ph = 2 * np.pi * u[:, 1]
+    d = np.stack([st * np.cos(ph), st * np.sin(ph), ct], 1)
+    ln = lo * (hi / lo) ** mt.real(n)
+    p2 = (p1 + d * ln[:, None]).astype(np.float32)
+    return p1, p2
+
+
+@pytest.mark.parametrize("shape", [0, 1])
+@pytest.mark.parametrize("max_level", [0, 2])
+def test_edges_match_mpr_oracle(bgr, oracle, shape, max_level):
+    occ, boxes, m = _map(bgr, oracle, 64, 1, max_level)
+    p1, p2 = _edges(oracle, occ, 4000, 31)
+    # axis-aligned, diagonal and -z (Eigen's antiparallel branch) edges
+    extra1 = np.array([[0.3, 0.3, 0.3], [0.3, 0.3, 0.3], [0.3, 0.3, 2.9], [1.0, 1.0, 1.0]], dtype=np.float32)
+    extra2 = np.array([[2.9, 0.3, 0.3], [2.9, 2.9, 2.9], [0.3, 0.3, 0.3], [1.0, 1.0, 1.0]], dtype=np.float32)
+    p1, p2 = np.concatenate([p1, extra1]), np.concatenate([p2, extra2])
+    hit, band = m.collide_edges(p1, p2, 0.03, shape)
+    ohit, oband = oracle.collide_edges(boxes, p1, p2, 0.03, shape, mode=1)
+    st = m.last_stats()
+    assert st["iter_cap"] == 0
+    diff = hit != ohit
+    assert not (diff & (band == 0)).any(), "mismatch outside the band: %s" % np.nonzero(diff & (band == 0))[0][:10]
+    assert not ((oband == 1) & (band == 0)).any(), "oracle-band contact not flagged"
+    assert diff.sum() <= band.sum()
+    assert 0.1 < hit.mean() < 0.95
+
+
+def test_edges_mode0_equals_mode1_oracle(oracle):
+    """the oracle's conservative culling never changes the reference-literal loop's result"""
+    occ = oracle.make_map(32, seed=4, n_walls=2)
+    boxes = oracle.grid_to_boxes(occ, 0.05, (0, 0, 0), 2)
+    p1, p2 = _edges(oracle, occ, 300, 41, 0.1, 1.5, 1.6)
+    a, _ = oracle.collide_edges(boxes, p1, p2, 0.03, 0, mode=0, want_band=False)
+    b, _ = oracle.collide_edges(boxes, p1, p2, 0.03, 0, mode=1, want_band=False)
+    assert np.array_equal(a, b)
+
+
+def test_edges_known_answers(bgr, oracle):
+    """cylinder vs a single leaf at exact separations."""
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64))
+    box = np.array([[1.025, 1.025, 1.025, 0.05, 1.0, 0.5]])
+    m.set_boxes(box)
+    for sep in (1e-3, 1e-5, -1e-5, -1e-3):
+        # side contact: vertical edge passing the box at radial gap `sep`
+        x = 1.025 + 0.025 + 0.03 + sep
+        p1 = np.array([[x, 1.025, 0.5]], dtype=np.float32)
+        p2 = np.array([[x, 1.025, 1.5]], dtype=np.float32)
+        hit, band = m.collide_edges(p1, p2, 0.03, 0)
+        ohit, oband = oracle.collide_edges(box, p1, p2, 0.03, 0, mode=0)
+        assert hit[0] == ohit[0] or band[0]
+        if abs(sep) >= 1e-4:
+            assert hit[0] == (1 if sep < 0 else 0) and band[0] == 0
+        # cap contact: flat cap facing the box (a capsule would reach further)
+        z = 1.025 - 0.025 - sep
+        p1 = np.array([[1.025, 1.025, 0.2]], dtype=np.float32)
+        p2 = np.array([[1.025, 1.025, z]], dtype=np.float32)
+        hit, band = m.collide_edges(p1, p2, 0.03, 0)
+        ohit, _ = oracle.collide_edges(box, p1, p2, 0.03, 0, mode=0)
+        assert hit[0] == ohit[0] or band[0]
+        if abs(sep) >= 1e-4:
+            assert hit[0] == (1 if sep < 0 else 0)
+    # flat-capped cylinder vs capsule: a gap of 0.02 in front of the cap is free for the
+    # cylinder (parity shape) and a hit for the capsule (conservative superset)
+    p1 = np.array([[1.025, 1.025, 0.2]], dtype=np.float32)
+    p2 = np.array([[1.025, 1.025, 0.98]], dtype=np.float32)
+    assert m.collide_edges(p1, p2, 0.03, 0)[0][0] == 0
+    assert m.collide_edges(p1, p2, 0.03, 1)[0][0] == 1
+    assert m.isLineValid(p1[0], p2[0]) is False
+
+
+def test_edges_device_pointers(bgr, oracle):
+    import torch
+    occ, boxes, m = _map(bgr, oracle, 64, 1, 2)
+    p1, p2 = _edges(oracle, occ, 3000, 51)
+    h0, b0 = m.collide_edges(p1, p2)
+    d1, d2 = torch.from_numpy(p1).cuda(), torch.from_numpy(p2).cuda()
+    h1, b1 = m.collide_edges(d1, d2)
+    torch.cuda.synchronize()
+    assert np.array_equal(h0, h1.cpu().numpy()) and np.array_equal(b0, b1.cpu().numpy())
+
+
+def test_edges_large_map_properties(bgr, oracle):
+    """256^3 map: order independence, idempotence, reversal symmetry outside the band."""
+    occ = oracle.make_map(256, seed=9, n_walls=4, wall_thick=4, door_cells=6)
+    boxes = oracle.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (256, 256, 256))
+    m.set_boxes(boxes)
+    assert m.occupied_cells() == int(occ.sum())
+    mt = oracle.MT(77)
+    p1 = (mt.real(3 * 100000).reshape(-1, 3) * 12.8).astype(np.float32)
+    p2, _ = _edges(oracle, occ, 100000, 78, extent=12.8)
+    p2 = (p1 + (p2 - p2.mean(0)) * 0.2).astype(np.float32)
+    h, b = m.collide_edges(p1, p2)
+    h2, b2 = m.collide_edges(p1, p2)
+    assert np.array_equal(h, h2) and np.array_equal(b, b2)
+    perm = np.random.default_rng(1).permutation(len(p1))
+    hp, bp = m.collide_edges(p1[perm], p2[perm])
+    assert np.array_equal(hp, h[perm]) and np.array_equal(bp, b[perm])
+    hr, br = m.collide_edges(p2, p1)
+    bad = (hr != h) & (b == 0) & (br == 0)
+    assert not bad.any()
+    # oracle on a subsample
+    sub = slice(0, 400)
+    oh, ob = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
+    assert not ((oh != h[sub]) & (b[sub] == 0)).any()

@@ -1,0 +1,196 @@
+"""GPU parity: bgr_nns_* (through the C ABI) vs the CPU oracle, bit-exact.
+
+Reference surface: Nabo::NNSearchF::createKDTreeLinearHeap / knn (rrt_star_milestones.cpp:
+1306-1312) and Nearest() (:138-154)."""
+import numpy as np
+import pytest
+
+from conftest import canon_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(B, O, pts, q, k, method, flags=0, max_radius=np.inf, max_radii=None):
+    nns = B.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(method)
+    idx, d2, _ = nns.knn(q, k, 0.0, flags, max_radius, max_radii)
+    oi, od = O.knn_brute(pts, q, k, flags, max_radius, max_radii)
+    assert np.array_equal(d2.view(np.uint32), od.view(np.uint32)), "distances differ"
+    assert np.array_equal(idx, oi), "indices differ"
+    nns.close()
+
+
+@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("n,nq,k", [(5000, 300, 10), (40000, 1000, 16), (33, 7, 32), (1500, 64, 1), (70000, 333, 5)])
+def test_knn_matches_oracle(bgr, oracle, method, n, nq, k):
+    pts = oracle.points(2, n, 25.6)
+    q = oracle.points(3, nq, 25.6)
+    _check(bgr, oracle, pts, q, k, method)
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_knn_self_match_rule(bgr, oracle, method):
+    """queries = nodes: without ALLOW_SELF_MATCH points with d2 <= FLT_EPSILON are skipped."""
+    pts = oracle.points(2, 30000, 25.6)
+    q = pts[:2000].copy()
+    _check(bgr, oracle, pts, q, 16, method, flags=0)
+    _check(bgr, oracle, pts, q, 16, method, flags=bgr.ALLOW_SELF_MATCH | bgr.SORT_RESULTS)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(method)
+    idx, d2, _ = nns.knn(q, 4, 0.0, bgr.ALLOW_SELF_MATCH)
+    assert np.array_equal(idx[:, 0], np.arange(2000, dtype=np.int32))
+    assert (d2[:, 0] == 0).all()
+    idx, d2, _ = nns.knn(q, 4, 0.0, 0)
+    assert (idx[:, 0] != np.arange(2000)).all() and (d2[:, 0] > np.finfo(np.float32).eps).all()
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_knn_lattice_ties(bgr, oracle, method):
+    """integer lattice: many exactly equal distances; ties must come out in index order."""
+    g = np.arange(12, dtype=np.float32)
+    pts = np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3)
+    rng = np.random.default_rng(7)
+    pts = pts[rng.permutation(len(pts))]
+    q = np.concatenate([pts[:200] + np.float32(0.5), pts[200:300]])
+    for k in (6, 16, 27):
+        _check(bgr, oracle, pts, q, k, method, flags=bgr.ALLOW_SELF_MATCH)
+        _check(bgr, oracle, pts, q, k, method, flags=0)
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_knn_radius(bgr, oracle, method):
+    pts = oracle.points(2, 20000, 10.0)
+    q = oracle.points(3, 500, 10.0)
+    _check(bgr, oracle, pts, q, 16, method, max_radius=0.35)
+    radii = (oracle.MT(11).real(500) * 0.6).astype(np.float32)
+    _check(bgr, oracle, pts, q, 8, method, max_radii=radii)
+    # unfilled slots: idx -1, d2 +inf
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(method)
+    idx, d2, _ = nns.knn(q, 16, 0.0, 0, 0.05)
+    assert ((idx == -1) == np.isinf(d2)).all() and (idx == -1).any()
+
+
+@pytest.mark.parametrize("method", [1, 2])
+def test_knn_append_only_store(bgr, oracle, method):
+    """create + repeated append == one-shot create (replaces the reference's per-iteration rebuild)."""
+    pts = oracle.points(5, 50000, 5.0)
+    q = oracle.points(6, 400, 5.0)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts[:20000])
+    nns.set_method(method)
+    nns.knn(q, 10)                         # builds the index over the first part
+    for a, b in ((20000, 20001), (20001, 23000), (23000, 50000)):
+        nns.append(pts[a:b])
+        idx, d2, _ = nns.knn(q, 10)
+        oi, od = oracle.knn_brute(pts[:b], q, 10)
+        assert canon_equal(idx, d2, oi, od)
+    assert len(nns) == 50000
+
+
+def test_knn_clustered_and_outside_queries(bgr, oracle):
+    """non-uniform node density (RRT-like clusters) and queries far outside the node AABB."""
+    rng = np.random.default_rng(3)
+    centers = rng.uniform(0, 20, (12, 3))
+    pts = (centers[rng.integers(0, 12, 60000)] + rng.normal(0, 0.15, (60000, 3))).astype(np.float32)
+    q = np.concatenate([rng.uniform(-30, 50, (300, 3)), pts[:300] + 0.01]).astype(np.float32)
+    for method in (1, 2):
+        _check(bgr, oracle, pts, q, 16, method)
+
+
+def test_knn_errors_like_libnabo(bgr, oracle):
+    pts = oracle.points(2, 10, 1.0)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    q = pts[:2]
+    with pytest.raises(RuntimeError):   # k > N-1 without self match (why the reference guards V.size()>5)
+        nns.knn(q, 10)
+    nns.knn(q, 10, 0.0, bgr.ALLOW_SELF_MATCH)
+    with pytest.raises(RuntimeError):
+        nns.knn(q, 11, 0.0, bgr.ALLOW_SELF_MATCH)
+    with pytest.raises(RuntimeError):   # unknown flag bits
+        nns.knn(q, 2, 0.0, 4)
+    with pytest.raises(RuntimeError):   # approximate search is not offered
+        nns.knn(q, 2, 0.5)
+    with pytest.raises(RuntimeError):
+        bgr.NNSearchF.createKDTreeLinearHeap(np.zeros((4, 2), np.float32), dim=2)
+
+
+def test_knn_device_pointers_and_stream(bgr, oracle):
+    import torch
+    pts = oracle.points(2, 30000, 25.6)
+    q = oracle.points(3, 1000, 25.6)
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        dp = torch.from_numpy(pts).cuda()
+        dq = torch.from_numpy(q).cuda()
+        nns = bgr.NNSearchF.createKDTreeLinearHeap(dp, stream=st.cuda_stream)
+        idx, d2, _ = nns.knn(dq, 16)
+    st.synchronize()
+    oi, od = oracle.knn_brute(pts, q, 16)
+    assert canon_equal(idx.cpu().numpy(), d2.cpu().numpy(), oi, od)
+
+
+def test_knn_merge_shards(bgr, oracle):
+    """index-range shards + merge == single search (the multi-GPU exchange step, on one GPU)."""
+    import torch
+    pts = oracle.points(5, 40000, 25.6)
+    q = oracle.points(6, 700, 25.6)
+    g, k = 4, 16
+    dq = torch.from_numpy(q).cuda()
+    slabs_i, slabs_d = [], []
+    for s in range(g):
+        lo, hi = s * 10000, (s + 1) * 10000
+        nns = bgr.NNSearchF.createKDTreeLinearHeap(pts[lo:hi])
+        nns.set_index_base(lo)
+        i, d, _ = nns.knn(dq, k)
+        slabs_i.append(i)
+        slabs_d.append(d)
+    torch.cuda.synchronize()
+    si, sd = torch.stack(slabs_i), torch.stack(slabs_d)
+    oi_t = torch.empty_like(slabs_i[0])
+    od_t = torch.empty_like(slabs_d[0])
+    bgr.knn_merge_dev(si, sd, oi_t, od_t)
+    torch.cuda.synchronize()
+    oi, od = oracle.knn_brute(pts, q, k)
+    assert canon_equal(oi_t.cpu().numpy(), od_t.cpu().numpy(), oi, od)
+
+
+@pytest.mark.parametrize("n,nq", [(1, 5), (777, 100), (5000, 2000), (120000, 512)])
+def test_nearest_matches_reference_literal(bgr, oracle, n, nq):
+    pts = oracle.points(2, n, 3.2)
+    q = oracle.points(3, nq, 3.2)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    idx, dist = nns.nearest(q)
+    oi, od = oracle.nearest(pts, q)
+    assert np.array_equal(idx, oi)
+    assert np.array_equal(dist.view(np.uint32), od.view(np.uint32))
+
+
+def test_nearest_last_index_wins_ties(bgr, oracle):
+    pts = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 0, 0], [0, 0, 0]], dtype=np.float32)
+    q = np.array([[0, 0, 0], [1, 0, 0], [0.5, 0, 0]], dtype=np.float32)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    idx, _ = nns.nearest(q)
+    oi, _ = oracle.nearest(pts, q)
+    assert idx.tolist() == oi.tolist() == [4, 3, 4]
+
+
+def test_knn_full_size_properties(bgr, oracle):
+    """BASELINE config 2 (1M nodes, 64k queries, k=16): grid == brute on the GPU, and an
+    oracle check on a 256-query subsample; sortedness; distances recomputed on the host."""
+    n, nq, k = 1_000_000, 65_536, 16
+    pts = oracle.points(2, n, 25.6)
+    q = oracle.points(3, nq, 25.6)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(bgr.METHOD_GRID)
+    gi, gd, _ = nns.knn(q, k)
+    assert (np.diff(gd, axis=1) >= 0).all()
+    sub = slice(0, 4096)
+    nns.set_method(bgr.METHOD_BRUTE)
+    bi, bd, _ = nns.knn(q[sub], k)
+    assert canon_equal(gi[sub], gd[sub], bi, bd)
+    oi, od = oracle.knn_brute(pts, q[:256], k)
+    assert canon_equal(gi[:256], gd[:256], oi, od)
+    # d2 recomputed in numpy f32 with the same operation order
+    d = q[:, None, :] - pts[gi]
+    r = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
+    assert np.array_equal(r.astype(np.float32).view(np.uint32), gd.view(np.uint32))
