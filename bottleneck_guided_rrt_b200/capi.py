@@ -46,6 +46,7 @@ def lib():
     vp, i64, i32, f32, f64, u32 = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_double, C.c_uint
     L.bgr_last_error.restype = C.c_char_p
     L.bgr_version.restype = i32
+    L.bgr_launch_count.restype = C.c_uint64
     L.bgr_device_count.argtypes = [vp]
     L.bgr_device_info.argtypes = [vp, vp, vp]
     L.bgr_nns_create.argtypes = [vp, i64, i32, u32, vp]

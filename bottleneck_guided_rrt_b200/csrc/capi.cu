@@ -1,6 +1,7 @@
 // Error plumbing and device queries of the C ABI (include/bgrrt.h).
 #include <cstdarg>
 #include <cstdio>
+#include <atomic>
 #include "common.cuh"
 
 namespace bgr {
@@ -14,6 +15,10 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+static std::atomic<unsigned long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+unsigned long long launches() { return g_launches.load(std::memory_order_relaxed); }
 
 int num_sms() {
     static int sms = 0;
@@ -32,6 +37,7 @@ extern "C" {
 
 const char* bgr_last_error(void) { return bgr::get_error(); }
 int bgr_version(void) { return BGR_VERSION; }
+uint64_t bgr_launch_count(void) { return bgr::launches(); }
 
 int bgr_device_count(int* count) {
     BGR_ARG(count != nullptr, "count is null");

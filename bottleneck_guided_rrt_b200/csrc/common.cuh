@@ -11,6 +11,7 @@ namespace bgr {
 
 void set_error(const char* fmt, ...);
 const char* get_error();
+void note_launch();
 
 #define BGR_CUDA(call)                                                                   \
     do {                                                                                 \
@@ -20,6 +21,13 @@ const char* get_error();
                            cudaGetErrorString(e__));                                     \
             return BGR_ERR_CUDA;                                                         \
         }                                                                                \
+    } while (0)
+
+// after every kernel launch: count it (bench.py's gpu_launches) and surface launch errors
+#define BGR_LAUNCH_CHECK()                                                               \
+    do {                                                                                 \
+        bgr::note_launch();                                                              \
+        BGR_CUDA(cudaGetLastError());                                                    \
     } while (0)
 
 #define BGR_CHECK(rc_expr)                                                               \

@@ -171,14 +171,14 @@ inline int exclusive_scan(int32_t* d, int64_t n, DevBuf<int32_t>& sums, cudaStre
     for (size_t l = 0; l + 1 < sizes.size() + 1 && ns.back() > 0; ++l) {
         const int64_t cur = ns.back();
         scan_block_kernel<<<(unsigned)div_up(cur, 1024), 1024, 0, st>>>(data.back(), cur, lv[l]);
-        BGR_CUDA(cudaGetLastError());
+        BGR_LAUNCH_CHECK();
         if (cur <= 1024) break;
         data.push_back(lv[l]);
         ns.push_back(div_up(cur, 1024));
     }
     for (int l = (int)data.size() - 2; l >= 0; --l) {
         scan_add_kernel<<<(unsigned)div_up(ns[l], 1024), 1024, 0, st>>>(data[l], ns[l], data[l + 1]);
-        BGR_CUDA(cudaGetLastError());
+        BGR_LAUNCH_CHECK();
     }
     return BGR_OK;
 }
@@ -193,7 +193,7 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
     const int nb = 512;
     BGR_CHECK(G.partial.reserve(nb * 6, st, false));
     bbox_kernel<<<nb, 256, 0, st>>>(x, y, z, n, G.partial.p);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     std::vector<float> hp((size_t)nb * 6);
     BGR_CUDA(cudaMemcpyAsync(hp.data(), G.partial.p, hp.size() * sizeof(float), cudaMemcpyDeviceToHost, st));
     BGR_CUDA(cudaStreamSynchronize(st));
@@ -241,10 +241,10 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
     BGR_CUDA(cudaMemsetAsync(G.cell_start.p, 0, (size_t)(ncells + 1) * sizeof(int32_t), st));
     BGR_CUDA(cudaMemsetAsync(G.cursor.p, 0, (size_t)ncells * sizeof(int32_t), st));
     cell_count_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(x, y, z, n, gm, G.cell_id.p, G.cell_start.p);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     BGR_CHECK(exclusive_scan(G.cell_start.p, ncells + 1, G.block_sums, st));
     scatter_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(x, y, z, n, G.cell_id.p, G.cell_start.p, G.cursor.p, G.pts.p);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     G.geom = gm;
     G.n_indexed = n;
     return BGR_OK;
@@ -408,7 +408,7 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     a.max_radius = max_radius; a.max_radii = d_radii;
     a.idx = d_idx; a.d2 = d_d2; a.index_base = index_base; a.counter = counter;
     grid_knn_kernel<<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 

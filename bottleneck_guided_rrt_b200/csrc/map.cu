@@ -512,7 +512,7 @@ int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
     BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
     BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
     raster_kernel<<<(unsigned)div_up((int64_t)recs.size(), 256), 256, 0, h->stream>>>(h->view(), h->recs.p, (int64_t)recs.size(), set);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     BGR_CUDA(cudaStreamSynchronize(h->stream));   // recs is a host temporary
     return BGR_OK;
 }
@@ -599,7 +599,7 @@ int bgr_map_occupied_cells(bgr_map* h, int64_t* cells) {
     BGR_CHECK(h->stats.reserve(4, h->stream, false));
     BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 8, h->stream));
     popcount_kernel<<<256, 256, 0, h->stream>>>(h->bits[0].p, h->words[0], h->stats.p);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     unsigned long long c = 0;
     BGR_CUDA(cudaMemcpyAsync(&c, h->stats.p, 8, cudaMemcpyDeviceToHost, h->stream));
     BGR_CUDA(cudaStreamSynchronize(h->stream));
@@ -620,7 +620,7 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
     BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_spheres arguments");
     if (n == 0) return BGR_OK;
     collide_spheres_kernel<<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 
@@ -651,7 +651,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     a.p1 = d_p1; a.p2 = d_p2; a.n = n; a.radius = radius; a.shape = shape;
     a.hit = d_hit; a.band = d_band; a.stats = h->stats.p;
     collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(a);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 

@@ -61,7 +61,7 @@ int append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
     BGR_CHECK(grow_store(h, h->n + m));
     deinterleave_kernel<<<(unsigned)div_up(m, 256), 256, 0, h->stream>>>(d_pts, m, h->x.p + h->n,
                                                                           h->y.p + h->n, h->z.p + h->n);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     h->n += m;
     return BGR_OK;
 }
@@ -77,7 +77,7 @@ int launch_brute(bgr_nns* h, BruteArgs a, int chunks) {
     }
     dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
     knn_brute_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 
@@ -90,7 +90,7 @@ int launch_nearest(bgr_nns* h, NearestArgs a, int chunks) {
     }
     dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
     nearest_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 
@@ -140,7 +140,7 @@ int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flag
     if (chunks > 1) {
         knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
                                                                          nq, k, d_idx, d_d2);
-        BGR_CUDA(cudaGetLastError());
+        BGR_LAUNCH_CHECK();
     }
     return BGR_OK;
 }
@@ -333,7 +333,7 @@ int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx
     }
     nearest_reduce_kernel<<<(unsigned)div_up(nq, 256), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
                                                                             nq, d_idx, d_dist);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 
@@ -369,7 +369,7 @@ int bgr_knn_merge_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int6
     BGR_ARG(g >= 1 && nq >= 0 && k >= 1 && k <= 32, "bad merge arguments (k<=32)");
     if (nq == 0) return BGR_OK;
     knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, (cudaStream_t)stream>>>(d_idx_in, d_d2_in, g, nq, k, d_idx, d_d2);
-    BGR_CUDA(cudaGetLastError());
+    BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
 

@@ -42,6 +42,8 @@ typedef enum bgr_status {
 
 const char* bgr_last_error(void);
 int bgr_version(void);
+/* number of CUDA kernels this library has launched in this process (monotonic) */
+uint64_t bgr_launch_count(void);
 int bgr_device_count(int* count);
 /* SM count, SM clock (kHz), L2 bytes of the current device */
 int bgr_device_info(int* sms, int* sm_clock_khz, int64_t* l2_bytes);
