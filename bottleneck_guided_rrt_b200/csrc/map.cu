@@ -176,7 +176,7 @@ struct EdgeSetup {       // per-edge broadphase frame, shared memory
     int ax, i_lo, nslab;
 };
 
-enum { F_HIT = 1, F_DEEP = 2, F_INFL = 4, F_DEFL = 8, F_CAP = 16 };
+enum { F_HIT = 1, F_DEEP = 2, F_INFL = 4, F_DEFL = 8, F_CAP = 16, F_OVERFLOW = 32 };
 
 struct EdgeArgs {
     MapView m;
@@ -185,8 +185,9 @@ struct EdgeArgs {
     int64_t n;
     double radius;
     int shape;
-    uint8_t* hit;
-    uint8_t* band;
+    int want_band;
+    int only_overflow;           // process only edges whose narrow-phase queue overflowed
+    unsigned* gflags;            // per-edge result flags (F_*), consumed by edges_finalize_kernel
     unsigned long long* stats;   // [4]
 };
 
@@ -219,11 +220,14 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t e0 = (int64_t)blockIdx.x * kEdgesPerCta;
     const int ne = (int)min((int64_t)kEdgesPerCta, a.n - e0);
+    const bool mine = tid < ne && (!a.only_overflow || (a.gflags[e0 + tid] & F_OVERFLOW));
+    if (!__syncthreads_or(mine)) return;
     if (tid == 0) { qcount = 0; st_items = st_cand = st_mpr = st_cap = 0; }
 
     // ---- phase 0: per-edge setup (thread per edge)
     int myslabs = 0;
-    if (tid < ne) {
+    flags[tid] = 0;
+    if (mine) {
         const int64_t e = e0 + tid;
         const float p1[3] = {a.p1[3 * e], a.p1[3 * e + 1], a.p1[3 * e + 2]};
         const float p2[3] = {a.p2[3 * e], a.p2[3 * e + 1], a.p2[3 * e + 2]};
@@ -250,7 +254,6 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
         const bool finite = isfinite(s.c[0] + s.c[1] + s.c[2] + s.h);
         if (!finite) s.nslab = 0;
         es[tid] = s;
-        flags[tid] = 0;
         myslabs = s.nslab;
     }
     // block exclusive prefix sum of slab counts
@@ -357,7 +360,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
                     unsigned f = 0;
                     if (mpr_shape_box(o, bc, e, kBandTol, &capped)) f |= F_HIT;
                     ++n_mpr;
-                    if (a.band) {
+                    if (a.want_band) {
                         ShapeObj oi = o, od = o;
                         oi.radius += kBandFlag; od.radius = fmax(0.0, od.radius - kBandFlag);
                         if (o.type == kShapeCyl) { oi.height += kBandFlag; od.height = fmax(0.0, od.height - kBandFlag); }
@@ -392,7 +395,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
         const bool h = mpr_shape_box(o, bc, e, kBandTol, &capped) != 0;
         ++n_mpr;
         if (h) f |= F_HIT;
-        if (a.band) {
+        if (a.want_band) {
             // flag results that flip under a +-2.5e-6 m inflation (covers MPR's 1e-6 band)
             ShapeObj o2 = o;
             if (h) {
@@ -411,15 +414,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
     }
     __syncthreads();
 
-    if (tid < ne) {
-        const unsigned f = flags[tid];
-        const bool h = (f & F_HIT) != 0;
-        a.hit[e0 + tid] = h ? 1 : 0;
-        if (a.band) {
-            const bool b = !(f & F_DEEP) && ((h && !(f & F_DEFL)) || (!h && (f & F_INFL)) || (f & F_CAP));
-            a.band[e0 + tid] = b ? 1 : 0;
-        }
-    }
+    if (mine) a.gflags[e0 + tid] = flags[tid];
     if (a.stats) {
         atomicAdd(&st_cand, n_cand);
         atomicAdd(&st_mpr, n_mpr);
@@ -432,6 +427,324 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
             atomicAdd(a.stats + 3, st_cap);
         }
     }
+}
+
+// ------------------------------------------------------------------ edges, fast path
+// sweep kernel  : items (edge, slab) -> 64-bit occupancy mask of the item's <=8x8-cell
+//                 rectangle; the set bits of the 32 items of a warp are then processed
+//                 DENSELY (one candidate per lane, prefix sum + n-th-set-bit) so the
+//                 double-precision certificate math runs with full warps.  Ambiguous
+//                 (edge, leaf) pairs go to a global queue (one atomicAdd per warp).
+// narrow kernel : grid-stride over the queue, exact MPR (+ band flag), atomicOr on flags.
+// finalize      : flags -> hit / in_band bytes.
+constexpr int kSweepThreads = 256;
+constexpr int kSweepEdges = 256;
+constexpr int kRectMax = 8;
+
+struct SweepEdge {
+    double c[3], u[3], h;
+    int ax, i_lo;
+};
+struct NarrowRec {
+    uint32_t edge, a, b, pad;   // a = L<<12 | lx, b = ly<<12 | lz
+};
+struct Edge2Args {
+    MapView m;
+    const float* p1;
+    const float* p2;
+    int64_t n;
+    double radius;
+    int shape;
+    int want_band;
+    unsigned* gflags;
+    NarrowRec* queue;
+    unsigned queue_cap;
+    unsigned* qctl;              // [0] queue fill, [1] edges that overflowed the queue
+    unsigned long long* stats;   // [4]
+    uint8_t* hit;
+    uint8_t* band;
+};
+
+__global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a) {
+    __shared__ SweepEdge es[kSweepEdges];
+    __shared__ int prefix[kSweepEdges + 1];
+    __shared__ unsigned eflags[kSweepEdges];
+    __shared__ int warp_sums[kSweepThreads / 32];
+    __shared__ unsigned long long st_cand;
+
+    const MapView& m = a.m;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t e0 = (int64_t)blockIdx.x * kSweepEdges;
+    const int ne = (int)min((int64_t)kSweepEdges, a.n - e0);
+    const double rm = a.radius + kSweepMargin;
+    if (tid == 0) st_cand = 0;
+
+    // ---- phase 0: per-edge frame (thread per edge)
+    int myslabs = 0;
+    eflags[tid] = 0;
+    if (tid < ne) {
+        const int64_t e = e0 + tid;
+        const float p1[3] = {a.p1[3 * e], a.p1[3 * e + 1], a.p1[3 * e + 2]};
+        const float p2[3] = {a.p2[3 * e], a.p2[3 * e + 1], a.p2[3 * e + 2]};
+        const ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+        D3 u = {0, 0, 1};
+        quat_rot(u, o.rot);
+        d3_scale(u, 1.0 / sqrt(d3_dot(u, u)));
+        SweepEdge s;
+        s.c[0] = o.pos.x; s.c[1] = o.pos.y; s.c[2] = o.pos.z;
+        s.u[0] = u.x; s.u[1] = u.y; s.u[2] = u.z;
+        s.h = o.height;
+        s.ax = 0;
+        if (fabs(s.u[1]) > fabs(s.u[s.ax])) s.ax = 1;
+        if (fabs(s.u[2]) > fabs(s.u[s.ax])) s.ax = 2;
+        const double pa = s.c[s.ax] - s.h * s.u[s.ax], pb = s.c[s.ax] + s.h * s.u[s.ax];
+        int lo = (int)floor((fmin(pa, pb) - rm - m.origin[s.ax]) * m.inv_res);
+        int hi = (int)floor((fmax(pa, pb) + rm - m.origin[s.ax]) * m.inv_res);
+        lo = max(lo, 0);
+        hi = min(hi, m.dims[s.ax] - 1);
+        s.i_lo = lo;
+        myslabs = max(0, hi - lo + 1);
+        if (!isfinite(s.c[0] + s.c[1] + s.c[2] + s.h)) myslabs = 0;
+        es[tid] = s;
+    }
+    {
+        int inc = myslabs;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = lane < kSweepThreads / 32 ? warp_sums[lane] : 0;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(kFull, w, o);
+                if (lane >= o) w += t;
+            }
+            if (lane < kSweepThreads / 32) warp_sums[lane] = w;
+        }
+        __syncthreads();
+        const int off = warp ? warp_sums[warp - 1] : 0;
+        prefix[tid + 1] = off + inc;
+        if (tid == 0) prefix[0] = 0;
+    }
+    __syncthreads();
+    const int total = prefix[kSweepEdges];
+    const double sqrt3 = 1.7320508075688772;
+    unsigned long long n_cand = 0;
+
+    for (int w0 = 0; w0 < total; w0 += kSweepThreads) {
+        // ---- one item per thread: occupancy mask of its rectangle
+        const int w = w0 + tid;
+        unsigned long long occ = 0;
+        int info_a = 0, info_b = 0;   // el | slab<<8 ; b0 | c0<<12
+        if (w < total) {
+            int lo = 0, hi = kSweepEdges;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (prefix[mid] <= w) lo = mid; else hi = mid;
+            }
+            const int el = lo;
+            const SweepEdge& s = es[el];
+            const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
+            const int i = s.i_lo + (w - prefix[el]);
+            const double x0 = m.origin[ax] + (double)i * m.res - rm, x1 = m.origin[ax] + (double)(i + 1) * m.res + rm;
+            const double a0ax = s.c[ax] - s.h * s.u[ax];
+            const double dax = 2.0 * s.h * s.u[ax];
+            double t0 = 0.0, t1 = 1.0;
+            if (fabs(dax) > 1e-12) {
+                const double ta = (x0 - a0ax) / dax, tb = (x1 - a0ax) / dax;
+                t0 = fmax(0.0, fmin(ta, tb));
+                t1 = fmin(1.0, fmax(ta, tb));
+            }
+            if (t0 <= t1) {
+                int r0[2], r1[2];
+                bool none = false;
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const int b = k ? cx : bx;
+                    const double a0b = s.c[b] - s.h * s.u[b], db = 2.0 * s.h * s.u[b];
+                    const double pa = a0b + t0 * db, pb = a0b + t1 * db;
+                    int lo_b = (int)floor((fmin(pa, pb) - rm - m.origin[b]) * m.inv_res);
+                    int hi_b = (int)floor((fmax(pa, pb) + rm - m.origin[b]) * m.inv_res);
+                    lo_b = max(lo_b, 0);
+                    hi_b = min(hi_b, m.dims[b] - 1);
+                    hi_b = min(hi_b, lo_b + kRectMax - 1);   // host guarantees the hull fits kRectMax cells
+                    r0[k] = lo_b;
+                    r1[k] = hi_b;
+                    none |= lo_b > hi_b;
+                }
+                if (!none) {
+                    for (int jc = r0[1]; jc <= r1[1]; ++jc)
+                        for (int jb = r0[0]; jb <= r1[0]; ++jb) {
+                            int v[3];
+                            v[ax] = i; v[bx] = jb; v[cx] = jc;
+                            if (test_bit(m.lv[0], v[0], v[1], v[2]))
+                                occ |= 1ull << ((jc - r0[1]) * kRectMax + (jb - r0[0]));
+                        }
+                    info_a = el | (i << 8);
+                    info_b = r0[0] | (r0[1] << 12);
+                }
+            }
+        }
+        // ---- dense processing of the warp's candidates
+        const int cnt = __popcll(occ);
+        int incl = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const int T = __shfl_sync(kFull, incl, 31);
+        for (int j0 = 0; j0 < T; j0 += 32) {
+            const int j = j0 + lane;
+            const bool active = j < T;
+            int src = 0;
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) {
+                const int v = __shfl_sync(kFull, incl, src + step - 1);
+                if (v <= j) src += step;
+            }
+            src = min(src, 31);
+            const int s_incl = __shfl_sync(kFull, incl, src), s_cnt = __shfl_sync(kFull, cnt, src);
+            const unsigned long long s_occ = __shfl_sync(kFull, occ, src);
+            const int s_a = __shfl_sync(kFull, info_a, src), s_b = __shfl_sync(kFull, info_b, src);
+            bool ambiguous = false;
+            NarrowRec rec;
+            int el = 0;
+            if (active) {
+                const int rank = j - (s_incl - s_cnt);
+                const unsigned lo32 = (unsigned)s_occ, hi32 = (unsigned)(s_occ >> 32);
+                const int clo = __popc(lo32);
+                const int bit = rank < clo ? (int)__fns(lo32, 0, rank + 1) : 32 + (int)__fns(hi32, 0, rank - clo + 1);
+                el = s_a & 255;
+                const int i = s_a >> 8, b0 = s_b & 4095, c0 = s_b >> 12;
+                const SweepEdge& s = es[el];
+                const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
+                int v[3], l[3];
+                v[ax] = i; v[bx] = b0 + (bit & (kRectMax - 1)); v[cx] = c0 + (bit >> 3);
+                const int L = find_leaf(m, v[0], v[1], v[2], l[0], l[1], l[2]);
+                // one representative cell per (item, leaf)
+                if (v[bx] == max(b0, l[bx]) && v[cx] == max(c0, l[cx])) {
+                    ++n_cand;
+                    D3 bc;
+                    double e;
+                    leaf_box(m, L, l[0], l[1], l[2], bc, e);
+                    const double wx = bc.x - s.c[0], wy = bc.y - s.c[1], wz = bc.z - s.c[2];
+                    const double al = wx * s.u[0] + wy * s.u[1] + wz * s.u[2];
+                    double g_out2, g_in, rc = e * sqrt3 * (1.0 + 1e-9);
+                    bool deep;
+                    if (a.shape == BGR_SHAPE_CAPSULE) {
+                        const double t = fmax(-s.h, fmin(s.h, al));
+                        const double ex = wx - t * s.u[0], ey = wy - t * s.u[1], ez = wz - t * s.u[2];
+                        const double dseg = sqrt(ex * ex + ey * ey + ez * ez);
+                        const double go = dseg - (a.radius + kCertMargin);
+                        g_out2 = go > 0 ? go * go : 0.0;
+                        g_in = dseg - (a.radius - kCertMargin);
+                        deep = g_in < e;
+                    } else {
+                        const double ex = wx - al * s.u[0], ey = wy - al * s.u[1], ez = wz - al * s.u[2];
+                        const double rho = sqrt(ex * ex + ey * ey + ez * ez);
+                        const double dao = fmax(0.0, fabs(al) - (s.h + kCertMargin)), dqo = fmax(0.0, rho - (a.radius + kCertMargin));
+                        g_out2 = dao * dao + dqo * dqo;
+                        const double dai = fmax(0.0, fabs(al) - (s.h - kCertMargin)), dqi = fmax(0.0, rho - (a.radius - kCertMargin));
+                        deep = (dai * dai + dqi * dqi < e * e) && s.h > kCertMargin && a.radius > kCertMargin;
+                    }
+                    if (g_out2 > rc * rc) {
+                        // clear miss
+                    } else if (deep) {
+                        atomicOr(&eflags[el], F_HIT | F_DEEP);
+                    } else {
+                        ambiguous = true;
+                        rec.edge = (uint32_t)(e0 + el);
+                        rec.a = ((uint32_t)L << 12) | (uint32_t)l[0];
+                        rec.b = ((uint32_t)l[1] << 12) | (uint32_t)l[2];
+                        rec.pad = 0;
+                    }
+                }
+            }
+            const unsigned am = __ballot_sync(kFull, ambiguous);
+            if (am) {
+                unsigned base = 0;
+                if (lane == __ffs(am) - 1) base = atomicAdd(a.qctl, (unsigned)__popc(am));
+                base = __shfl_sync(kFull, base, __ffs(am) - 1);
+                if (ambiguous) {
+                    const unsigned slot = base + __popc(am & ((1u << lane) - 1u));
+                    if (slot < a.queue_cap) a.queue[slot] = rec;
+                    else atomicOr(&eflags[el], F_OVERFLOW);
+                }
+            }
+        }
+    }
+    if (a.stats) atomicAdd(&st_cand, n_cand);
+    __syncthreads();
+    if (tid < ne) {
+        a.gflags[e0 + tid] = eflags[tid];
+        if (eflags[tid] & F_OVERFLOW) atomicAdd(a.qctl + 1, 1u);
+    }
+    if (a.stats && tid == 0) {
+        atomicAdd(a.stats + 0, (unsigned long long)total);
+        atomicAdd(a.stats + 1, st_cand);
+    }
+}
+
+__global__ void __launch_bounds__(128) edges_narrow_kernel(Edge2Args a) {
+    const MapView& m = a.m;
+    const unsigned count = min(a.qctl[0], a.queue_cap);
+    unsigned long long n_mpr = 0, n_cap = 0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const NarrowRec rec = a.queue[i];
+        const unsigned cur = __ldcg(a.gflags + rec.edge);
+        if (cur & (F_DEEP | F_OVERFLOW)) continue;
+        if ((cur & F_HIT) && (!a.want_band || (cur & F_DEFL))) continue;   // already decided
+        const int L = (int)(rec.a >> 12), lx = (int)(rec.a & 4095), ly = (int)(rec.b >> 12), lz = (int)(rec.b & 4095);
+        D3 bc;
+        double e;
+        leaf_box(m, L, lx, ly, lz, bc, e);
+        const int64_t eg = rec.edge;
+        const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
+        const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
+        ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+        int capped = 0;
+        unsigned f = 0;
+        const bool h = mpr_shape_box(o, bc, e, kBandTol, &capped) != 0;
+        ++n_mpr;
+        if (h) f |= F_HIT;
+        if (a.want_band) {
+            ShapeObj o2 = o;
+            if (h) {
+                o2.radius = fmax(0.0, o2.radius - kBandFlag);
+                if (o.type == kShapeCyl) o2.height = fmax(0.0, o2.height - kBandFlag);
+                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_DEFL;
+            } else {
+                o2.radius += kBandFlag;
+                if (o.type == kShapeCyl) o2.height += kBandFlag;
+                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_INFL;
+            }
+            ++n_mpr;
+        }
+        if (capped) { f |= F_CAP; ++n_cap; }
+        if (f) atomicOr(a.gflags + rec.edge, f);
+    }
+    if (a.stats) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_mpr += __shfl_xor_sync(kFull, n_mpr, o);
+            n_cap += __shfl_xor_sync(kFull, n_cap, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (n_mpr) atomicAdd(a.stats + 2, n_mpr);
+            if (n_cap) atomicAdd(a.stats + 3, n_cap);
+        }
+    }
+}
+
+__global__ void edges_finalize_kernel(const unsigned* __restrict__ gflags, int64_t n, uint8_t* __restrict__ hit,
+                                      uint8_t* __restrict__ band) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned f = gflags[i];
+    const bool h = (f & F_HIT) != 0;
+    hit[i] = h ? 1 : 0;
+    if (band) band[i] = (!(f & F_DEEP) && ((h && !(f & F_DEFL)) || (!h && (f & F_INFL)) || (f & F_CAP))) ? 1 : 0;
 }
 
 }  // namespace
@@ -451,6 +764,8 @@ struct bgr_map {
     DevBuf<float> p1_dev, p2_dev;
     DevBuf<uint8_t> hit_dev, band_dev;
     DevBuf<unsigned long long> stats;
+    DevBuf<unsigned> eflags, qctl;
+    DevBuf<NarrowRec> queue;
     uint64_t last_stats[4] = {0, 0, 0, 0};
 
     MapView view() const {
@@ -643,14 +958,41 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_edges arguments");
     BGR_ARG(shape == BGR_SHAPE_CYLINDER || shape == BGR_SHAPE_CAPSULE, "unknown shape %d", shape);
     BGR_ARG(radius + kSweepMargin < 64 * h->res, "radius too large for the sweep (>= 64 cells)");
+    BGR_ARG(n < ((int64_t)1 << 31), "too many edges in one call");
     if (n == 0) return BGR_OK;
     BGR_CHECK(h->stats.reserve(4, h->stream, false));
+    BGR_CHECK(h->eflags.reserve(n, h->stream, false));
+    BGR_CHECK(h->qctl.reserve(2, h->stream, false));
     BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 4 * sizeof(unsigned long long), h->stream));
-    EdgeArgs a;
-    a.m = h->view();
-    a.p1 = d_p1; a.p2 = d_p2; a.n = n; a.radius = radius; a.shape = shape;
-    a.hit = d_hit; a.band = d_band; a.stats = h->stats.p;
-    collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(a);
+    BGR_CUDA(cudaMemsetAsync(h->qctl.p, 0, 2 * sizeof(unsigned), h->stream));
+    EdgeArgs ma;
+    ma.m = h->view();
+    ma.p1 = d_p1; ma.p2 = d_p2; ma.n = n; ma.radius = radius; ma.shape = shape;
+    ma.want_band = d_band != nullptr; ma.gflags = h->eflags.p; ma.stats = h->stats.p;
+    // fast path needs the swept hull of one slab to fit a kRectMax x kRectMax cell rectangle:
+    // extent <= res (slope <= 1 on the dominant axis) + 2*(radius+margin) + 2*(radius+margin)
+    const bool fast = (h->res + 4.0 * (radius + kSweepMargin)) / h->res + 1.0 <= (double)kRectMax;
+    if (fast) {
+        const int64_t cap = std::max<int64_t>(1 << 16, 4 * n);
+        BGR_CHECK(h->queue.reserve(cap, h->stream, false));
+        Edge2Args a;
+        a.m = ma.m;
+        a.p1 = d_p1; a.p2 = d_p2; a.n = n; a.radius = radius; a.shape = shape;
+        a.want_band = ma.want_band; a.gflags = h->eflags.p;
+        a.queue = h->queue.p; a.queue_cap = (unsigned)std::min<int64_t>(cap, 0x7fffffff);
+        a.qctl = h->qctl.p; a.stats = h->stats.p; a.hit = d_hit; a.band = d_band;
+        edges_sweep_kernel<<<(unsigned)div_up(n, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
+        BGR_LAUNCH_CHECK();
+        const int nblk = (int)std::min<int64_t>(4LL * num_sms(), std::max<int64_t>(1, div_up(cap, 128)));
+        edges_narrow_kernel<<<nblk, 128, 0, h->stream>>>(a);
+        BGR_LAUNCH_CHECK();
+        ma.only_overflow = 1;   // no-op unless the queue overflowed
+    } else {
+        ma.only_overflow = 0;
+    }
+    collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(ma);
+    BGR_LAUNCH_CHECK();
+    edges_finalize_kernel<<<(unsigned)div_up(n, 256), 256, 0, h->stream>>>(h->eflags.p, n, d_hit, d_band);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
@@ -688,7 +1030,7 @@ int bgr_map_destroy(bgr_map* h) {
     cudaStreamSynchronize(h->stream);
     for (int L = 0; L <= kMaxLevel; ++L) h->bits[L].release();
     h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
-    h->stats.release();
+    h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
     delete h;
     return BGR_OK;
 }
