@@ -50,8 +50,9 @@ class ShardedNNSearch:
                            torch.empty((self.world, nq, k), dtype=d2.dtype, device=d2.device),
                            torch.empty_like(idx), torch.empty_like(d2))
         _, si, sd, oi, od = self._slabs
-        self.dist.all_gather_into_tensor(si, idx.contiguous(), group=self.group)
-        self.dist.all_gather_into_tensor(sd, d2.contiguous(), group=self.group)
+        # concatenated-rows form (G*Q, k): accepted by both NCCL and gloo
+        self.dist.all_gather_into_tensor(si.view(self.world * nq, k), idx.contiguous(), group=self.group)
+        self.dist.all_gather_into_tensor(sd.view(self.world * nq, k), d2.contiguous(), group=self.group)
         self.merge(si, sd, oi, od)
         return oi, od
 
