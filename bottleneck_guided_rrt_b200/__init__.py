@@ -21,4 +21,12 @@ from .capi import (  # noqa: F401
     lib,
     library_path,
     knn_merge_dev,
+    Planner,
+    PlannerParams,
+    PLAN_EDGE_CHECK,
+    PLAN_REWIRE,
+    PLAN_QUIRKS,
+    PLAN_NO_GOAL,
+    PLAN_MODE_RS,
+    PLAN_MODE_MS,
 )

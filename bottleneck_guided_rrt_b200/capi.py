@@ -77,8 +77,42 @@ def lib():
     L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_last_stats.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
+    L.bgr_planner_create.argtypes = [vp, vp, vp, i64, vp, i32, vp]
+    L.bgr_planner_set_stream.argtypes = [vp, vp]
+    L.bgr_planner_step.argtypes = [vp, vp, vp]
+    L.bgr_planner_run.argtypes = [vp, i64, i64, vp]
+    L.bgr_planner_size.restype = i64
+    L.bgr_planner_size.argtypes = [vp]
+    L.bgr_planner_get_tree.argtypes = [vp, vp, vp]
+    L.bgr_planner_get_path.argtypes = [vp, vp, vp]
+    L.bgr_planner_stats.argtypes = [vp, vp]
+    L.bgr_planner_nns.argtypes = [vp, vp]
+    L.bgr_planner_destroy.argtypes = [vp]
     _LIB = L
     return L
+
+
+PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL = 1, 2, 4, 8
+PLAN_MODE_RS, PLAN_MODE_MS = 0, 1
+
+
+class PlannerParams(C.Structure):
+    """bgr_planner_params (include/bgrrt.h).
+    Defaults are the reference's compile-time constants."""
+    _fields_ = [("start", C.c_float * 3), ("goal", C.c_float * 3), ("eta", C.c_float), ("goal_tol", C.c_float),
+                ("goal_chance", C.c_float), ("mode", C.c_int32), ("k", C.c_int32), ("batch", C.c_int32),
+                ("edge_shape", C.c_int32), ("flags", C.c_uint32), ("seed", C.c_uint32), ("pad_", C.c_uint32),
+                ("state_radius", C.c_double), ("edge_radius", C.c_double)]
+
+    def __init__(self, start, goal, mode=PLAN_MODE_MS, k=5, batch=1, flags=PLAN_QUIRKS, seed=5489, eta=0.15,
+                 goal_tol=0.4, goal_chance=0.1, state_radius=0.1, edge_radius=0.03, edge_shape=SHAPE_CYLINDER):
+        super().__init__()
+        self.start[:] = [float(v) for v in start]
+        self.goal[:] = [float(v) for v in goal]
+        self.eta, self.goal_tol, self.goal_chance = eta, goal_tol, goal_chance
+        self.mode, self.k, self.batch, self.edge_shape = mode, k, batch, edge_shape
+        self.flags, self.seed = flags, seed
+        self.state_radius, self.edge_radius = state_radius, edge_radius
 
 
 def _check(rc):
@@ -329,3 +363,59 @@ class OccupancyMap:
                                     np.asarray(point2, dtype=np.float32).reshape(1, 3), 0.03, SHAPE_CYLINDER,
                                     want_band=False)
         return bool(hit[0])
+
+
+class Planner:
+    """Batched extension loop of the reference planner (rrt_star_milestones.cpp:1160-1406 /
+    rrt_star.cpp:1140-1300) on the device: bgr_planner_*.  `omap` is an OccupancyMap."""
+
+    def __init__(self, params, omap, table, milestones=None, stream=None):
+        t = _host_f32(table)
+        m = _host_f32(milestones) if milestones is not None else np.zeros((0, 3), np.float32)
+        h = C.c_void_p()
+        _check(lib().bgr_planner_create(C.byref(params), omap._h, _ptr(t), t.shape[0], _ptr(m) if len(m) else None,
+                                        m.shape[0], C.byref(h)))
+        self._h, self._map, self.params = h, omap, params
+        if stream:
+            _check(lib().bgr_planner_set_stream(self._h, C.c_void_p(stream)))
+
+    def __del__(self):
+        self.close()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgr_planner_destroy(self._h)
+            self._h = None
+
+    def __len__(self):
+        return int(lib().bgr_planner_size(self._h))
+
+    def step(self):
+        a, g = C.c_int(0), C.c_int(0)
+        _check(lib().bgr_planner_step(self._h, C.byref(a), C.byref(g)))
+        return a.value, bool(g.value)
+
+    def run(self, max_nodes, max_batches=1 << 40):
+        g = C.c_int(0)
+        _check(lib().bgr_planner_run(self._h, max_nodes, max_batches, C.byref(g)))
+        return bool(g.value)
+
+    def tree(self):
+        n = len(self)
+        xyz = np.empty((n, 3), dtype=np.float32)
+        par = np.empty(n, dtype=np.int32)
+        _check(lib().bgr_planner_get_tree(self._h, _ptr(xyz), _ptr(par)))
+        return xyz, par
+
+    def path(self):
+        n = C.c_int64(0)
+        _check(lib().bgr_planner_get_path(self._h, None, C.byref(n)))
+        out = np.empty(n.value, dtype=np.int32)
+        _check(lib().bgr_planner_get_path(self._h, _ptr(out), C.byref(n)))
+        return out
+
+    def stats(self):
+        s = np.zeros(8, dtype=np.int64)
+        _check(lib().bgr_planner_stats(self._h, _ptr(s)))
+        return dict(zip(("batches", "candidates", "rejected_state", "rejected_edge", "improved_parent", "rewired",
+                         "in_band", "goal_candidate"), (int(v) for v in s)))

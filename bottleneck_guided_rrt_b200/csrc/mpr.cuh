@@ -191,8 +191,8 @@ __device__ __noinline__ int mpr_shape_box(const ShapeObj& o, const D3& bc, doubl
     }
 }
 
-// The reference's f32 transform setup for the edge shape (MS:396-437), see oracle/src/collide.cpp
-// edge_frame_f32 for the derivation of Eigen's setFromTwoVectors((0,0,1), p2-p1).
+// The reference's f32 transform setup for the edge shape (MS:396-437): Eigen quaternion
+// setFromTwoVectors((0,0,1), p2-p1) written out.
 __device__ __forceinline__ ShapeObj make_edge_obj(const float p1[3], const float p2[3], double radius, int shape) {
     ShapeObj o;
     const float cx = __fdiv_rn(__fadd_rn(p1[0], p2[0]), 2.f), cy = __fdiv_rn(__fadd_rn(p1[1], p2[1]), 2.f),

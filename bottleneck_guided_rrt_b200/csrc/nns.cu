@@ -7,6 +7,7 @@
 #include "grid.cuh"
 #include "knn_brute.cuh"
 #include "nearest.cuh"
+#include "internal.cuh"
 
 using namespace bgr;
 
@@ -170,6 +171,13 @@ int check_knn_args(const bgr_nns* h, int64_t nq, int k, float eps, unsigned flag
 }
 
 }  // namespace
+
+namespace bgr {
+int nns_reserve(bgr_nns* h, int64_t n) { return grow_store(h, n); }
+void nns_soa(bgr_nns* h, float** x, float** y, float** z) { *x = h->x.p; *y = h->y.p; *z = h->z.p; }
+void nns_set_size(bgr_nns* h, int64_t n) { h->n = n; }
+cudaStream_t nns_stream(bgr_nns* h) { return h->stream; }
+}  // namespace bgr
 
 extern "C" {
 

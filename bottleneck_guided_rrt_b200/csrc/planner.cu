@@ -1,0 +1,619 @@
+// bgr_planner_* — the extension loop of the reference planner, B candidates per launch.
+// Reference: abb_manipulator/src/rrt_star_milestones.cpp main() MS:1160-1406 (sampler
+// MS:1171-1219, steer MS:1233-1268, cost_wiring MS:802-831, extend_tree MS:834-853, parent rule
+// MS:1322-1323, goal test MS:1340, goal node MS:1346-1347) and rrt_star.cpp RS:1145-1178 (10 %
+// goal-bias sampler).  Every candidate of a step is evaluated against the tree snapshot at step
+// start; batch = 1 is the reference's sequential loop.  The hot primitives are the library's own
+// device entry points (Nearest, kNN, sphere / edge collision); this file adds the small
+// per-candidate kernels around them and keeps the whole tree on the device:
+//   positions  : the planner's bgr_nns store (SoA x/y/z in HBM, append-only)
+//   parents    : int32 array (the reference keeps them as float in V[i][3])
+//   MT19937    : 624-word state in HBM, advanced by a one-CTA kernel (3-phase parallel twist)
+// One 48-byte counter block is read back per step (accepted count, goal flag, statistics).
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "internal.cuh"
+
+using namespace bgr;
+
+namespace {
+
+constexpr int kMtN = 624, kMtM = 397;
+
+struct PlanDev {                 // device view shared by the kernels
+    bgr_planner_params p;
+    const float *x, *y, *z;      // node store
+    int32_t* par;
+    int64_t n;                   // snapshot size
+    int B, K, W;                 // candidates, neighbours, stream words per candidate
+    int have_knn;
+    const uint32_t* words;
+    const float* table;
+    int64_t nt;
+    const float* milestones;
+    float *prand, *pnew;
+    uint8_t* found;
+    int32_t* near;
+    uint8_t *hit, *band;
+    int32_t* knn_idx;
+    float *e1, *e2;
+    uint8_t *ehit, *eband;
+    float* costs;                // [B][K+1], slot K = via the Nearest node
+    uint8_t* ok;
+    int32_t *parent, *new_index;
+    float* cost;
+    unsigned long long* rkey;    // per node rewire proposal key
+    long long* counters;         // [0] accepted [1] goal candidate (-1) [2..] stats deltas
+};
+
+// ------------------------------------------------------------------ MT19937 on the device
+__device__ __forceinline__ uint32_t mt_twist(uint32_t u, uint32_t v) {   // mtrand.h:77-82
+    return (((u & 0x80000000u) | (v & 0x7FFFFFFFu)) >> 1) ^ ((v & 1u) ? 0x9908B0DFu : 0u);
+}
+__device__ __forceinline__ uint32_t mt_temper(uint32_t x) {              // mtrand.h:84-93
+    x ^= (x >> 11);
+    x ^= (x << 7) & 0x9D2C5680u;
+    x ^= (x << 15) & 0xEFC60000u;
+    return x ^ (x >> 18);
+}
+// state: [0..623] words, [624] position.  Produces n tempered words in stream order.
+__global__ void __launch_bounds__(256) mt_fill_kernel(uint32_t* __restrict__ state, uint32_t* __restrict__ out, int n) {
+    __shared__ uint32_t s[kMtN];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kMtN; i += blockDim.x) s[i] = state[i];
+    int pos = (int)state[kMtN];
+    __syncthreads();
+    int done = 0;
+    while (done < n) {
+        if (pos == kMtN) {                    // gen_state (mtrand.cpp:12-19), three dependent phases
+            uint32_t v = 0;
+            // phase 1: i in [0,227): needs old s[i], s[i+1], s[i+397]
+            if (tid < kMtN - kMtM) v = s[tid + kMtM] ^ mt_twist(s[tid], s[tid + 1]);
+            __syncthreads();
+            if (tid < kMtN - kMtM) s[tid] = v;
+            __syncthreads();
+            // phase 2: i in [227,454): needs old s[i], s[i+1] and NEW s[i-227]
+            for (int half = 0; half < 2; ++half) {
+                const int lo = (kMtN - kMtM) + half * (kMtN - kMtM);           // 227, 454
+                const int hi = min(lo + (kMtN - kMtM), kMtN - 1);             // 454, 623
+                const int i = lo + tid;
+                if (i < hi) v = s[i - (kMtN - kMtM)] ^ mt_twist(s[i], s[i + 1]);
+                __syncthreads();
+                if (i < hi) s[i] = v;
+                __syncthreads();
+            }
+            if (tid == 0) s[kMtN - 1] = s[kMtM - 1] ^ mt_twist(s[kMtN - 1], s[0]);
+            __syncthreads();
+            pos = 0;
+        }
+        const int take = min(n - done, kMtN - pos);
+        for (int i = tid; i < take; i += blockDim.x) out[done + i] = mt_temper(s[pos + i]);
+        done += take;
+        pos += take;
+        __syncthreads();
+    }
+    for (int i = tid; i < kMtN; i += blockDim.x) state[i] = s[i];
+    if (tid == 0) state[kMtN] = (uint32_t)pos;
+}
+
+// libstdc++ uniform_real_distribution<double>(a,b) over mt19937 (MS:1171-1184):
+// generate_canonical<double,53> = (w0 + w1*2^32) / 2^64, clamped below 1
+__device__ __forceinline__ double std_uniform(uint32_t w0, uint32_t w1, double a, double b) {
+    double sum = __dadd_rn(0.0, __dmul_rn((double)w0, 1.0));
+    sum = __dadd_rn(sum, __dmul_rn((double)w1, 4294967296.0));
+    double r = sum / 18446744073709551616.0;
+    if (r >= 1.0) r = 0.99999999999999988897769753748;   // nextafter(1, 0)
+    return __dadd_rn(__dmul_rn(r, b - a), a);
+}
+
+// Norm(x1,x2) MS:130-134: f32 differences, f64 squares / sum ((x^2+y^2)+z^2) / root, f32 result
+__device__ __forceinline__ float norm_ref(float ax, float ay, float az, float bx, float by, float bz) {
+    const double dx = (double)__fsub_rn(bx, ax), dy = (double)__fsub_rn(by, ay), dz = (double)__fsub_rn(bz, az);
+    const double s = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+    return __double2float_rn(__dsqrt_rn(s));
+}
+
+// ------------------------------------------------------------------ per-candidate kernels
+__global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 | RS:1155-1178
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d.B) return;
+    const uint32_t* w = d.words + (size_t)c * d.W;
+    const float rand_chance = __double2float_rn(std_uniform(w[0], w[1], 0.0, 1.0));
+    long long ri = (long long)(float)(int)std_uniform(w[2], w[3], 0.0, (double)d.nt);   // float random_indice = int(x(gen))
+    if (ri > d.nt - 1) ri = d.nt - 1;
+    const float* src;
+    if (d.p.mode == BGR_PLAN_MODE_MS) {
+        int mi = (int)std_uniform(w[4], w[5], 0.0, 3.0);
+        if (mi > 2) mi = 2;
+        if ((double)rand_chance > 0.8) src = d.table + 3 * ri;
+        else if ((double)rand_chance < 0.8 && (double)rand_chance > 0.5) src = d.p.goal;
+        else src = d.milestones + 3 * mi;
+    } else {
+        src = rand_chance > d.p.goal_chance ? d.table + 3 * ri : d.p.goal;
+    }
+    d.prand[3 * c] = src[0];
+    d.prand[3 * c + 1] = src[1];
+    d.prand[3 * c + 2] = src[2];
+}
+
+__global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d.B) return;
+    const int32_t ni = d.near[c];
+    const float nx = d.x[ni], ny = d.y[ni], nz = d.z[ni];
+    const float rx = d.prand[3 * c], ry = d.prand[3 * c + 1], rz = d.prand[3 * c + 2];
+    float ox, oy, oz;
+    uint8_t found;
+    if (norm_ref(nx, ny, nz, rx, ry, rz) <= d.p.eta) {
+        ox = rx; oy = ry; oz = rz;
+        found = 1;
+    } else {
+        const float dx = __fsub_rn(rx, nx), dy = __fsub_rn(ry, ny), dz = __fsub_rn(rz, nz);
+        const double s = __dadd_rn(__dadd_rn(__dmul_rn((double)dz, (double)dz), __dmul_rn((double)dy, (double)dy)),
+                                   __dmul_rn((double)dx, (double)dx));               // MS:1246: z^2 + y^2 + x^2
+        const float mag = __double2float_rn(__dsqrt_rn(s));
+        ox = __fadd_rn(nx, __fmul_rn(d.p.eta, __fdiv_rn(dx, mag)));
+        oy = __fadd_rn(ny, __fmul_rn(d.p.eta, __fdiv_rn(dy, mag)));
+        oz = __fadd_rn(nz, __fmul_rn(d.p.eta, __fdiv_rn(dz, mag)));
+        found = 0;
+    }
+    d.pnew[3 * c] = ox; d.pnew[3 * c + 1] = oy; d.pnew[3 * c + 2] = oz;
+    d.found[c] = found;
+}
+
+// candidate parent of slot j of candidate c: j < K the j-th neighbour, j == K the Nearest node
+__device__ __forceinline__ int32_t slot_node(const PlanDev& d, int c, int j) {
+    if (j == d.K) return d.near[c];
+    return d.have_knn ? d.knn_idx[(size_t)c * d.K + j] : -1;
+}
+
+__global__ void plan_edges_kernel(PlanDev d) {                 // edge list for isLineValid geometry
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.B * (d.K + 1)) return;
+    const int c = t / (d.K + 1), j = t % (d.K + 1);
+    const int32_t ind = d.hit[c] ? -1 : slot_node(d, c, j);
+    float a[3], b[3];
+    if (ind >= 0) {
+        a[0] = d.x[ind]; a[1] = d.y[ind]; a[2] = d.z[ind];
+        b[0] = d.pnew[3 * c]; b[1] = d.pnew[3 * c + 1]; b[2] = d.pnew[3 * c + 2];
+    } else {                                                   // unused slot: an edge far outside every map
+        a[0] = a[1] = a[2] = -1.0e9f;
+        b[0] = b[1] = -1.0e9f; b[2] = -1.0e9f + 128.f;
+    }
+    for (int k = 0; k < 3; ++k) { d.e1[3 * (size_t)t + k] = a[k]; d.e2[3 * (size_t)t + k] = b[k]; }
+}
+
+// cost_wiring(tree, tree[P], child) MS:802-831: f32 accumulation from the child upwards; the
+// walk ends at index <= 0, so the edge into the root is never added.
+__device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, float cz) {
+    const float px = d.x[P], py = d.y[P], pz = d.z[P];
+    float cost = __fadd_rn(0.f, norm_ref(px, py, pz, cx, cy, cz));
+    int cur = d.par[P];
+    float lx = px, ly = py, lz = pz;                           // previous node on the walk (P first)
+    while (cur > 0) {
+        const float qx = d.x[cur], qy = d.y[cur], qz = d.z[cur];
+        cost = __fadd_rn(cost, norm_ref(qx, qy, qz, lx, ly, lz));
+        lx = qx; ly = qy; lz = qz;
+        cur = d.par[cur];
+    }
+    return cost;
+}
+
+__global__ void plan_cost_kernel(PlanDev d) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.B * (d.K + 1)) return;
+    const int c = t / (d.K + 1), j = t % (d.K + 1);
+    if (d.hit[c]) return;
+    const int32_t ind = slot_node(d, c, j);
+    if (ind < 0) return;
+    d.costs[t] = chain_cost(d, ind, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]);
+}
+
+__global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS:838-853 + MS:1322-1323
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d.B) return;
+    const bool edge_check = d.p.flags & BGR_PLAN_EDGE_CHECK, quirks = d.p.flags & BGR_PLAN_QUIRKS;
+    const int K1 = d.K + 1;
+    d.ok[c] = 0;
+    long long band = d.band[c];
+    if (edge_check && !d.hit[c])
+        for (int j = 0; j < K1; ++j)
+            if (slot_node(d, c, j) >= 0) band += d.eband[(size_t)c * K1 + j];
+    if (band) atomicAdd((unsigned long long*)&d.counters[8], (unsigned long long)band);
+    if (d.hit[c]) { atomicAdd((unsigned long long*)&d.counters[4], 1ull); return; }
+    if (edge_check && d.ehit[(size_t)c * K1 + d.K]) { atomicAdd((unsigned long long*)&d.counters[5], 1ull); return; }
+    int32_t parent_index = d.near[c];
+    float lowest = d.costs[(size_t)c * K1 + d.K];             // current_cost MS:1316
+    float mycost = lowest;
+    if (d.have_knn) {
+        int32_t pc = -5;
+        for (int j = 0; j < d.K; ++j) {
+            if (edge_check && d.ehit[(size_t)c * K1 + j]) continue;
+            const float temp = d.costs[(size_t)c * K1 + j];
+            if (temp < lowest) { pc = d.knn_idx[(size_t)c * d.K + j]; lowest = temp; }
+        }
+        if (pc > 0) {
+            parent_index = pc;
+            mycost = lowest;
+            atomicAdd((unsigned long long*)&d.counters[6], 1ull);
+        }
+    }
+    d.parent[c] = (quirks && d.found[c]) ? d.near[c] : parent_index;
+    d.cost[c] = mycost;
+    d.ok[c] = 1;
+}
+
+// One CTA: goal cut (first accepted candidate within goal_tol, MS:1340), ordered compaction,
+// append to the store (MS:1325-1327) and the goal node (MS:1346-1347).
+__global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, float* y, float* z) {
+    __shared__ int s_goal;
+    __shared__ int warp_tot[32];
+    __shared__ int s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool no_goal = d.p.flags & BGR_PLAN_NO_GOAL;
+    if (tid == 0) { s_goal = 0x7fffffff; s_base = 0; }
+    __syncthreads();
+    if (!no_goal)
+        for (int c = tid; c < d.B; c += blockDim.x)
+            if (d.ok[c] && norm_ref(d.p.goal[0], d.p.goal[1], d.p.goal[2], d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]) < d.p.goal_tol)
+                atomicMin(&s_goal, c);
+    __syncthreads();
+    const int goal_c = s_goal;
+    for (int c0 = 0; c0 < d.B; c0 += blockDim.x) {
+        const int c = c0 + tid;
+        const int take = (c < d.B && d.ok[c] && c <= goal_c) ? 1 : 0;
+        int inc = take;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_tot[lane];
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(kFull, w, o);
+                if (lane >= o) w += t;
+            }
+            warp_tot[lane] = w;
+        }
+        __syncthreads();
+        const int base = s_base;
+        const int rank = base + (warp ? warp_tot[warp - 1] : 0) + inc - take;
+        if (c < d.B) d.new_index[c] = take ? (int32_t)(d.n + rank) : -1;
+        if (take) {
+            const int64_t ni = d.n + rank;
+            x[ni] = d.pnew[3 * c]; y[ni] = d.pnew[3 * c + 1]; z[ni] = d.pnew[3 * c + 2];
+            d.par[ni] = d.parent[c];
+        }
+        __syncthreads();
+        if (tid == 0) s_base = base + warp_tot[31];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const int acc = s_base;
+        d.counters[0] = acc;
+        d.counters[1] = goal_c == 0x7fffffff ? -1 : goal_c;
+        if (goal_c != 0x7fffffff) {
+            const int64_t gi = d.n + acc;
+            x[gi] = d.p.goal[0]; y[gi] = d.p.goal[1]; z[gi] = d.p.goal[2];
+            d.par[gi] = (int32_t)(gi - 1);                      // goal.push_back(V.size()-1)
+        }
+    }
+}
+
+// rewiring (beyond reference): neighbour `ind` adopts the new node when
+// cost(new) + Norm(tree[ind], new) < cost(ind) (and the edge is free); one proposal per node
+// survives: the smallest (new cost bits, new index) key.
+__device__ __forceinline__ bool rewire_proposal(const PlanDev& d, int t, int32_t* ind_out, unsigned long long* key) {
+    const int c = t / d.K, j = t % d.K;
+    const int32_t ni = d.new_index[c];
+    if (ni < 0) return false;
+    const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
+    if (ind <= 0 || ind == d.par[ni]) return false;
+    if ((d.p.flags & BGR_PLAN_EDGE_CHECK) && d.ehit[(size_t)c * (d.K + 1) + j]) return false;
+    const float ix = d.x[ind], iy = d.y[ind], iz = d.z[ind];
+    const float nc = __fadd_rn(d.cost[c], norm_ref(ix, iy, iz, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]));
+    const float oc = chain_cost(d, d.par[ind], ix, iy, iz);
+    if (!(nc < oc)) return false;
+    *ind_out = ind;
+    *key = ((unsigned long long)__float_as_uint(nc) << 32) | (unsigned)ni;
+    return true;
+}
+__global__ void plan_rewire_propose_kernel(PlanDev d) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.B * d.K) return;
+    int32_t ind;
+    unsigned long long key;
+    if (rewire_proposal(d, t, &ind, &key)) atomicMin(&d.rkey[ind], key);
+}
+__global__ void plan_rewire_apply_kernel(PlanDev d, const int32_t* __restrict__ par_snapshot_unused) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.B * d.K) return;
+    const int c = t / d.K, j = t % d.K;
+    const int32_t ni = d.new_index[c];
+    if (ni < 0) return;
+    const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
+    if (ind <= 0 || ind >= d.n) return;
+    const unsigned long long key = d.rkey[ind];
+    if (key == ~0ull || (unsigned)(key & 0xffffffffu) != (unsigned)ni) return;
+    // several slots of the same candidate can name the same node only once (kNN lists are sets)
+    d.par[ind] = ni;
+    atomicAdd((unsigned long long*)&d.counters[7], 1ull);
+}
+__global__ void plan_rewire_clear_kernel(PlanDev d) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= d.B * d.K) return;
+    const int32_t ind = d.knn_idx[(size_t)t];
+    if (ind > 0 && ind < d.n) d.rkey[ind] = ~0ull;
+}
+
+void mt_seed_host(uint32_t* s, uint32_t seed) {               // mtrand.cpp:21-31
+    s[0] = seed;
+    for (int i = 1; i < kMtN; ++i) s[i] = 1812433253u * (s[i - 1] ^ (s[i - 1] >> 30)) + (uint32_t)i;
+    s[kMtN] = kMtN;
+}
+
+}  // namespace
+
+struct bgr_planner {
+    bgr_planner_params p;
+    bgr_map* map = nullptr;
+    bgr_nns* nns = nullptr;
+    cudaStream_t stream = nullptr;
+    int64_t nt = 0;
+    int nm = 0;
+    int goal_reached = 0;
+    int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, -1};
+    DevBuf<uint32_t> mt_state, words;
+    DevBuf<float> table, milestones, prand, pnew, near_dist, knn_d2, e1, e2, costs, cost;
+    DevBuf<uint8_t> found, hit, band, ehit, eband, ok;
+    DevBuf<int32_t> par, near, knn_idx, parent, new_index;
+    DevBuf<unsigned long long> rkey;
+    int64_t rkey_init = 0;       // entries of rkey already set to ~0
+    DevBuf<long long> counters;
+    PinBuf host_counters;
+};
+
+extern "C" {
+
+int bgr_planner_destroy(bgr_planner* pl) {
+    if (!pl) return BGR_OK;
+    cudaStreamSynchronize(pl->stream);
+    if (pl->nns) bgr_nns_destroy(pl->nns);
+    pl->mt_state.release(); pl->words.release(); pl->table.release(); pl->milestones.release();
+    pl->prand.release(); pl->pnew.release(); pl->near_dist.release(); pl->knn_d2.release();
+    pl->e1.release(); pl->e2.release(); pl->costs.release(); pl->cost.release();
+    pl->found.release(); pl->hit.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
+    pl->ok.release(); pl->par.release(); pl->near.release(); pl->knn_idx.release(); pl->parent.release();
+    pl->new_index.release(); pl->rkey.release(); pl->counters.release(); pl->host_counters.release();
+    delete pl;
+    return BGR_OK;
+}
+
+int bgr_planner_create(const bgr_planner_params* p, bgr_map* map, const float* table, int64_t nt,
+                       const float* milestones, int nm, bgr_planner** out) {
+    BGR_ARG(out != nullptr, "out is null");
+    *out = nullptr;
+    BGR_ARG(p != nullptr && map != nullptr, "null params / map");
+    BGR_ARG(table != nullptr && nt >= 1 && nt <= (1 << 24), "sample table must hold 1..2^24 rows");
+    BGR_ARG(p->k >= 1 && p->k <= 32, "k must be in 1..32");
+    BGR_ARG(p->batch >= 1 && p->batch <= 65536, "batch must be in 1..65536");
+    BGR_ARG(p->mode == BGR_PLAN_MODE_RS || p->mode == BGR_PLAN_MODE_MS, "unknown sampler mode %d", p->mode);
+    BGR_ARG(p->mode != BGR_PLAN_MODE_MS || (milestones != nullptr && nm >= 3), "mode MS needs >= 3 milestone points");
+    BGR_ARG((p->flags & ~15u) == 0, "unknown planner flags %u", p->flags);
+    BGR_ARG(p->eta > 0.f && p->state_radius >= 0 && p->edge_radius >= 0, "bad eta / radii");
+    bgr_planner* pl = new bgr_planner;
+    pl->p = *p;
+    pl->map = map;
+    pl->nt = nt;
+    pl->nm = nm;
+    int rc = bgr_nns_create(p->start, 1, 3, 0, &pl->nns);                     // V = [[xs,ys,zs,-1]] MS:1152-1156
+    auto fail = [&](int r) { bgr_planner_destroy(pl); return r; };
+    if (rc != BGR_OK) return fail(rc);
+    cudaStream_t st = pl->stream;
+    if ((rc = pl->table.reserve(3 * nt, st, false)) != BGR_OK) return fail(rc);
+    if ((rc = pl->milestones.reserve(3 * std::max(nm, 1), st, false)) != BGR_OK) return fail(rc);
+    if ((rc = pl->mt_state.reserve(kMtN + 1, st, false)) != BGR_OK) return fail(rc);
+    if ((rc = pl->par.reserve(1024, st, false)) != BGR_OK) return fail(rc);
+    if ((rc = pl->counters.reserve(16, st, false)) != BGR_OK) return fail(rc);
+    if ((rc = pl->host_counters.reserve(16 * sizeof(long long))) != BGR_OK) return fail(rc);
+    uint32_t s[kMtN + 1];
+    mt_seed_host(s, p->seed);
+    const int32_t root_parent = -1;
+    if (cudaMemcpyAsync(pl->table.p, table, (size_t)3 * nt * sizeof(float), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        (nm > 0 && cudaMemcpyAsync(pl->milestones.p, milestones, (size_t)3 * nm * sizeof(float), cudaMemcpyHostToDevice, st) != cudaSuccess) ||
+        cudaMemcpyAsync(pl->mt_state.p, s, sizeof(s), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaMemcpyAsync(pl->par.p, &root_parent, sizeof(int32_t), cudaMemcpyHostToDevice, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess) {
+        set_error("planner upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return fail(BGR_ERR_CUDA);
+    }
+    *out = pl;
+    return BGR_OK;
+}
+
+int bgr_planner_set_stream(bgr_planner* pl, void* stream) {
+    BGR_ARG(pl != nullptr, "null planner");
+    BGR_CUDA(cudaStreamSynchronize(pl->stream));
+    pl->stream = (cudaStream_t)stream;
+    BGR_CHECK(bgr_nns_set_stream(pl->nns, stream));
+    BGR_CHECK(bgr_map_set_stream(pl->map, stream));
+    return BGR_OK;
+}
+
+int64_t bgr_planner_size(const bgr_planner* pl) { return pl ? bgr_nns_size(pl->nns) : -1; }
+
+int bgr_planner_nns(bgr_planner* pl, bgr_nns** out) {
+    BGR_ARG(pl != nullptr && out != nullptr, "bad arguments");
+    *out = pl->nns;
+    return BGR_OK;
+}
+
+int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
+    BGR_ARG(pl != nullptr, "null planner");
+    if (n_accepted) *n_accepted = 0;
+    if (goal_reached) *goal_reached = pl->goal_reached;
+    if (pl->goal_reached) return BGR_OK;
+    const bgr_planner_params& P = pl->p;
+    const int B = P.batch, K = P.k, K1 = K + 1;
+    const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
+    const int64_t N = bgr_nns_size(pl->nns);
+    const bool edge_check = P.flags & BGR_PLAN_EDGE_CHECK, rewire = P.flags & BGR_PLAN_REWIRE;
+    const bool have_knn = N > K;                                               // MS:1273
+    cudaStream_t st = pl->stream;
+    BGR_ARG(N + B + 1 < ((int64_t)1 << 31), "tree too large");
+    // capacity for this step's appends (+ the goal node)
+    BGR_CHECK(nns_reserve(pl->nns, N + B + 1));
+    BGR_CHECK(pl->par.reserve(N + B + 1, st, true, N));
+    BGR_CHECK(pl->words.reserve((int64_t)B * W, st, false));
+    BGR_CHECK(pl->prand.reserve(3 * (int64_t)B, st, false));
+    BGR_CHECK(pl->pnew.reserve(3 * (int64_t)B, st, false));
+    BGR_CHECK(pl->near_dist.reserve(B, st, false));
+    BGR_CHECK(pl->found.reserve(B, st, false));
+    BGR_CHECK(pl->hit.reserve(B, st, false));
+    BGR_CHECK(pl->band.reserve(B, st, false));
+    BGR_CHECK(pl->ok.reserve(B, st, false));
+    BGR_CHECK(pl->near.reserve(B, st, false));
+    BGR_CHECK(pl->parent.reserve(B, st, false));
+    BGR_CHECK(pl->new_index.reserve(B, st, false));
+    BGR_CHECK(pl->cost.reserve(B, st, false));
+    BGR_CHECK(pl->knn_idx.reserve((int64_t)B * K, st, false));
+    BGR_CHECK(pl->knn_d2.reserve((int64_t)B * K, st, false));
+    BGR_CHECK(pl->costs.reserve((int64_t)B * K1, st, false));
+    if (edge_check) {
+        BGR_CHECK(pl->e1.reserve(3 * (int64_t)B * K1, st, false));
+        BGR_CHECK(pl->e2.reserve(3 * (int64_t)B * K1, st, false));
+        BGR_CHECK(pl->ehit.reserve((int64_t)B * K1, st, false));
+        BGR_CHECK(pl->eband.reserve((int64_t)B * K1, st, false));
+    }
+    if (rewire) {
+        const int64_t old_cap = pl->rkey.cap;
+        BGR_CHECK(pl->rkey.reserve(N + B + 1, st, true, pl->rkey_init));
+        if (pl->rkey.cap != old_cap || pl->rkey_init < pl->rkey.cap) {
+            BGR_CUDA(cudaMemsetAsync(pl->rkey.p + pl->rkey_init, 0xFF, (size_t)(pl->rkey.cap - pl->rkey_init) * sizeof(unsigned long long), st));
+            pl->rkey_init = pl->rkey.cap;
+        }
+    }
+    PlanDev d;
+    d.p = P;
+    float *x, *y, *z;
+    nns_soa(pl->nns, &x, &y, &z);
+    d.x = x; d.y = y; d.z = z;
+    d.par = pl->par.p;
+    d.n = N; d.B = B; d.K = K; d.W = W; d.have_knn = have_knn;
+    d.words = pl->words.p; d.table = pl->table.p; d.nt = pl->nt; d.milestones = pl->milestones.p;
+    d.prand = pl->prand.p; d.pnew = pl->pnew.p; d.found = pl->found.p; d.near = pl->near.p;
+    d.hit = pl->hit.p; d.band = pl->band.p; d.knn_idx = pl->knn_idx.p;
+    d.e1 = pl->e1.p; d.e2 = pl->e2.p; d.ehit = pl->ehit.p; d.eband = pl->eband.p;
+    d.costs = pl->costs.p; d.ok = pl->ok.p; d.parent = pl->parent.p; d.new_index = pl->new_index.p;
+    d.cost = pl->cost.p; d.rkey = pl->rkey.p; d.counters = pl->counters.p;
+
+    const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);
+    BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
+    mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, pl->words.p, B * W);
+    BGR_LAUNCH_CHECK();
+    plan_sample_kernel<<<gb, 256, 0, st>>>(d);
+    BGR_LAUNCH_CHECK();
+    BGR_CHECK(bgr_nns_nearest_dev(pl->nns, pl->prand.p, B, pl->near.p, pl->near_dist.p));
+    plan_steer_kernel<<<gb, 256, 0, st>>>(d);
+    BGR_LAUNCH_CHECK();
+    BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
+    if (have_knn)
+        BGR_CHECK(bgr_nns_knn_dev(pl->nns, pl->pnew.p, B, K, 0.f, 0u, INFINITY, nullptr, pl->knn_idx.p, pl->knn_d2.p, nullptr));
+    if (edge_check) {
+        plan_edges_kernel<<<gbk1, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+        BGR_CHECK(bgr_map_collide_edges_dev(pl->map, pl->e1.p, pl->e2.p, (int64_t)B * K1, P.edge_radius, P.edge_shape,
+                                            pl->ehit.p, pl->eband.p));
+    }
+    plan_cost_kernel<<<gbk1, 256, 0, st>>>(d);
+    BGR_LAUNCH_CHECK();
+    plan_select_kernel<<<gb, 256, 0, st>>>(d);
+    BGR_LAUNCH_CHECK();
+    plan_commit_kernel<<<1, 1024, 0, st>>>(d, x, y, z);
+    BGR_LAUNCH_CHECK();
+    if (rewire && have_knn) {
+        plan_rewire_propose_kernel<<<gbk, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+        plan_rewire_apply_kernel<<<gbk, 256, 0, st>>>(d, nullptr);
+        BGR_LAUNCH_CHECK();
+        plan_rewire_clear_kernel<<<gbk, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+    }
+    long long* hc = (long long*)pl->host_counters.p;
+    BGR_CUDA(cudaMemcpyAsync(hc, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    BGR_CUDA(cudaStreamSynchronize(st));
+    const int acc = (int)hc[0];
+    const bool goal = hc[1] >= 0;
+    nns_set_size(pl->nns, N + acc + (goal ? 1 : 0));
+    pl->stats[0] += 1;
+    pl->stats[1] += B;
+    pl->stats[2] += hc[4];
+    pl->stats[3] += hc[5];
+    pl->stats[4] += hc[6];
+    pl->stats[5] += hc[7];
+    pl->stats[6] += hc[8];
+    if (goal) {
+        pl->goal_reached = 1;
+        pl->stats[7] = hc[1];
+    }
+    if (n_accepted) *n_accepted = acc;
+    if (goal_reached) *goal_reached = pl->goal_reached;
+    return BGR_OK;
+}
+
+int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached) {
+    BGR_ARG(pl != nullptr, "null planner");
+    for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes; ++b)
+        BGR_CHECK(bgr_planner_step(pl, nullptr, nullptr));
+    if (goal_reached) *goal_reached = pl->goal_reached;
+    return BGR_OK;
+}
+
+int bgr_planner_get_tree(bgr_planner* pl, float* xyz, int32_t* parent) {
+    BGR_ARG(pl != nullptr && xyz != nullptr && parent != nullptr, "bad arguments");
+    const int64_t n = bgr_nns_size(pl->nns);
+    float *x, *y, *z;
+    nns_soa(pl->nns, &x, &y, &z);
+    std::vector<float> hx(n), hy(n), hz(n);
+    BGR_CUDA(cudaMemcpyAsync(hx.data(), x, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
+    BGR_CUDA(cudaMemcpyAsync(hy.data(), y, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
+    BGR_CUDA(cudaMemcpyAsync(hz.data(), z, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
+    BGR_CUDA(cudaMemcpyAsync(parent, pl->par.p, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
+    BGR_CUDA(cudaStreamSynchronize(pl->stream));
+    for (int64_t i = 0; i < n; ++i) { xyz[3 * i] = hx[i]; xyz[3 * i + 1] = hy[i]; xyz[3 * i + 2] = hz[i]; }
+    return BGR_OK;
+}
+
+int bgr_planner_get_path(bgr_planner* pl, int32_t* path, int64_t* n_out) {   // BuildPlan MS:156-171
+    BGR_ARG(pl != nullptr && n_out != nullptr, "bad arguments");
+    const int64_t n = bgr_nns_size(pl->nns);
+    std::vector<int32_t> par(n);
+    BGR_CUDA(cudaMemcpyAsync(par.data(), pl->par.p, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
+    BGR_CUDA(cudaStreamSynchronize(pl->stream));
+    std::vector<int32_t> rev;
+    int64_t cur = n - 1, guard = 0;
+    while (cur > 0 && guard++ <= n) {
+        rev.push_back((int32_t)cur);
+        cur = par[cur];
+    }
+    BGR_ARG(guard <= n, "parent chain does not reach the root (cycle)");
+    rev.push_back(0);
+    const int64_t len = (int64_t)rev.size();
+    if (path) {
+        BGR_ARG(*n_out >= len, "path buffer too small (%lld < %lld)", (long long)*n_out, (long long)len);
+        for (int64_t i = 0; i < len; ++i) path[i] = rev[len - 1 - i];
+    }
+    *n_out = len;
+    return BGR_OK;
+}
+
+int bgr_planner_stats(bgr_planner* pl, int64_t out[8]) {
+    BGR_ARG(pl != nullptr && out != nullptr, "bad arguments");
+    std::memcpy(out, pl->stats, sizeof(pl->stats));
+    return BGR_OK;
+}
+
+}  // extern "C"

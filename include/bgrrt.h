@@ -146,6 +146,65 @@ int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* 
 int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
 int bgr_map_destroy(bgr_map* map);
 
+/* ------------------------------------------------------------------ batched planner step */
+/* The extension loop of rrt_star_milestones.cpp main() (MS:1160-1406; rrt_star.cpp
+ * RS:1140-1300 for the 10 % goal-bias sampler) for B candidates per launch, evaluated against
+ * the tree snapshot at step start; batch = 1 is the reference's sequential loop.  Per
+ * candidate: sampler (MS:1171-1219 | RS:1145-1178; ONE seeded MT19937 stream, draw order
+ * y, x, (z), two 32-bit words per uniform_real_distribution<double> draw) -> Nearest
+ * (MS:138-154) -> steer (MS:1233-1268) -> isStateValid (MS:310-351) -> knn K (MS:1309-1312,
+ * when size > K, MS:1273) -> cost_wiring (MS:802-831) / extend_tree (MS:834-853) -> parent
+ * rule (MS:1322-1323) -> append (MS:1325-1327) -> goal test (MS:1340) -> goal node
+ * (MS:1346-1347).  The tree lives on the device: positions in the planner's own bgr_nns
+ * store, parents as int32. */
+#define BGR_PLAN_EDGE_CHECK 1u  /* beyond reference: isLineValid geometry on candidate parent edges */
+#define BGR_PLAN_REWIRE 2u      /* beyond reference: real rewiring (MS:883/923 only print) */
+#define BGR_PLAN_QUIRKS 4u      /* MS:1236-1238: rows of the `found` branch keep the Nearest index as parent */
+#define BGR_PLAN_NO_GOAL 8u     /* never stop / append the goal node: grow the tree to max_nodes */
+#define BGR_PLAN_MODE_RS 0      /* rrt_star.cpp sampler: rand_chance > goal_chance ? table : goal */
+#define BGR_PLAN_MODE_MS 1      /* rrt_star_milestones.cpp sampler: >0.8 table, (0.5,0.8) goal, else milestone[int z] */
+
+typedef struct bgr_planner_params {
+    float start[3], goal[3];
+    float eta;            /* MS:100  0.15 */
+    float goal_tol;       /* MS:1340 0.4  */
+    float goal_chance;    /* RS:67   0.1 (mode RS) */
+    int32_t mode;
+    int32_t k;            /* MS:1309 5; 1..32 */
+    int32_t batch;        /* candidates per step, 1..65536 */
+    int32_t edge_shape;   /* BGR_SHAPE_* for BGR_PLAN_EDGE_CHECK */
+    uint32_t flags;
+    uint32_t seed;        /* MT19937 seed (std::mt19937(seed) / mtrand.cpp seed()) */
+    uint32_t pad_;
+    double state_radius;  /* MS:322 0.1  */
+    double edge_radius;   /* MS:437 0.03 */
+} bgr_planner_params;
+
+typedef struct bgr_planner bgr_planner;
+
+/* map is borrowed (must outlive the planner).  table_xyz: the sample domain replacing the
+ * reference's reachability table rows (MS:1138-1140,1195-1197), nt x 3 host floats, nt <= 2^24.
+ * milestones_xyz: nm x 3 host floats (MS:249-271), nm >= 3 in mode MS. */
+int bgr_planner_create(const bgr_planner_params* params, bgr_map* map, const float* table_xyz, int64_t nt,
+                       const float* milestones_xyz, int nm, bgr_planner** out);
+int bgr_planner_set_stream(bgr_planner* pl, void* cuda_stream);
+/* one batch; n_accepted / goal_reached may be NULL */
+int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached);
+/* steps until the goal is reached, the tree has >= max_nodes nodes or max_batches were run */
+int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached);
+int64_t bgr_planner_size(const bgr_planner* pl);
+/* tree download: xyz as 3 x N column-major (x0,y0,z0,...), parent[0] = -1 */
+int bgr_planner_get_tree(bgr_planner* pl, float* xyz_3xN, int32_t* parent);
+/* BuildPlan (MS:156-218): node indices from the root to the last node (the goal node once the
+ * goal is reached); returns the length through *n (query with path == NULL) */
+int bgr_planner_get_path(bgr_planner* pl, int32_t* path, int64_t* n);
+/* [0] batches [1] candidates [2] rejected by the state check [3] rejected by the edge check
+ * [4] improved parents [5] rewired nodes [6] in-band collision results [7] goal candidate */
+int bgr_planner_stats(bgr_planner* pl, int64_t out[8]);
+/* the planner's node store (borrowed): knn / nearest queries against the growing tree */
+int bgr_planner_nns(bgr_planner* pl, bgr_nns** out);
+int bgr_planner_destroy(bgr_planner* pl);
+
 #ifdef __cplusplus
 }
 #endif

@@ -90,6 +90,38 @@ double orc_sep_cyl_box(const float p1[3], const float p2[3], double r, double dr
 /* the reference's f32 cylinder frame: out = {cx,cy,cz, qx,qy,qz,qw, lz} as doubles */
 void orc_edge_frame(const float p1[3], const float p2[3], double out[8]);
 
+/* ---------------- planner loop (MS:1160-1406 / RS:1140-1300), B candidates per step ---- */
+#define ORC_PLAN_EDGE_CHECK 1u   /* beyond reference: isLineValid geometry on candidate parent edges */
+#define ORC_PLAN_REWIRE     2u   /* beyond reference: real rewiring (the reference only prints) */
+#define ORC_PLAN_QUIRKS     4u   /* MS:1236-1238: `found` rows keep the Nearest index as stored parent */
+#define ORC_PLAN_NO_GOAL    8u   /* do not stop / append the goal node (grow to max_nodes) */
+typedef struct orc_plan_params {   /* same layout as bgr_planner_params (include/bgrrt.h) */
+    float start[3], goal[3];
+    float eta;            /* MS:100  0.15 */
+    float goal_tol;       /* MS:1340 0.4  */
+    float goal_chance;    /* RS:67   0.1 (mode 0) */
+    int32_t mode;         /* 0 = RS sampler, 1 = MS sampler (0.8/0.5 + 3 milestones) */
+    int32_t k;            /* MS:1309 5 */
+    int32_t batch;        /* candidates per step; 1 = the reference's sequential loop */
+    int32_t edge_shape;   /* 0 cylinder (MS:437), 1 capsule */
+    uint32_t flags;
+    uint32_t seed;
+    uint32_t pad_;
+    double state_radius;  /* MS:322 0.1  */
+    double edge_radius;   /* MS:437 0.03 */
+} orc_plan_params;
+typedef struct orc_planner orc_planner;
+orc_planner* orc_planner_create(const orc_plan_params* p, const double* boxes, int64_t nb,
+                                const float* table_xyz, int64_t nt, const float* milestones_xyz, int nm);
+void    orc_planner_destroy(orc_planner*);
+int     orc_planner_step(orc_planner*, int* n_accepted, int* goal_reached);
+int     orc_planner_run(orc_planner*, int64_t max_nodes, int64_t max_batches);
+int64_t orc_planner_size(const orc_planner*);
+void    orc_planner_get_tree(const orc_planner*, float* xyz, int32_t* parent);
+/* [0] batches [1] candidates [2] rejected by state check [3] rejected by edge check
+ * [4] improved parents [5] rewired nodes [6] in-band collision results [7] goal candidate */
+void    orc_planner_stats(const orc_planner*, int64_t out[8]);
+
 /* ---------------- synthetic maps ---------------------------------------- */
 /* Occupancy grid (uint8, x fastest: idx = (z*ny + y)*nx + x) -> toBoxes list with
  * octree-aligned pruning up to 2^max_level cells.  Returns number of boxes written

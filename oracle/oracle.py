@@ -64,6 +64,15 @@ def lib():
         L.orc_grid_to_boxes.restype = i64
         L.orc_grid_to_boxes.argtypes = [vp, i32, i32, i32, f64, vp, i32, vp, i64]
         L.orc_make_map.argtypes = [vp, i32, f64, u32, i32, i32, i32, f64]
+        L.orc_planner_create.restype = vp
+        L.orc_planner_create.argtypes = [vp, vp, i64, vp, i64, vp, i32]
+        L.orc_planner_destroy.argtypes = [vp]
+        L.orc_planner_step.argtypes = [vp, vp, vp]
+        L.orc_planner_run.argtypes = [vp, i64, i64]
+        L.orc_planner_size.restype = i64
+        L.orc_planner_size.argtypes = [vp]
+        L.orc_planner_get_tree.argtypes = [vp, vp, vp]
+        L.orc_planner_stats.argtypes = [vp, vp]
         _LIB = L
     return _LIB
 
@@ -270,3 +279,46 @@ class RefMT:
 
     def real(self):
         return self.L.ref_mt_real()
+
+
+class Planner:
+    """CPU restatement of the planner loop (oracle/src/planner.cpp).  `params` is any ctypes
+    struct with the orc_plan_params layout (the product's PlannerParams has it)."""
+
+    def __init__(self, params, boxes, table, milestones=None):
+        b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 6)
+        t = _f32(table).reshape(-1, 3)
+        m = _f32(milestones).reshape(-1, 3) if milestones is not None else np.zeros((0, 3), np.float32)
+        self._keep = (b, t, m)
+        self._h = lib().orc_planner_create(C.byref(params), _p(b), b.shape[0], _p(t), t.shape[0], _p(m), m.shape[0])
+        if not self._h:
+            raise ValueError("orc_planner_create failed")
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_planner_destroy(self._h)
+            self._h = None
+
+    def __len__(self):
+        return int(lib().orc_planner_size(self._h))
+
+    def step(self):
+        a, g = C.c_int(0), C.c_int(0)
+        lib().orc_planner_step(self._h, C.byref(a), C.byref(g))
+        return a.value, bool(g.value)
+
+    def run(self, max_nodes, max_batches=1 << 40):
+        return bool(lib().orc_planner_run(self._h, max_nodes, max_batches))
+
+    def tree(self):
+        n = len(self)
+        xyz = np.empty((n, 3), dtype=np.float32)
+        par = np.empty(n, dtype=np.int32)
+        lib().orc_planner_get_tree(self._h, _p(xyz), _p(par))
+        return xyz, par
+
+    def stats(self):
+        s = np.zeros(8, dtype=np.int64)
+        lib().orc_planner_stats(self._h, _p(s))
+        return dict(zip(("batches", "candidates", "rejected_state", "rejected_edge", "improved_parent", "rewired",
+                         "in_band", "goal_candidate"), (int(v) for v in s)))

@@ -1,0 +1,63 @@
+"""CPU suite: the oracle's planner loop against a literal pure-Python walk of the reference's
+sequential iteration (rrt_star.cpp RS:1140-1300 with batch = 1) built from the oracle's own
+primitives — checks the loop STRUCTURE (draw order, V.size() > K guard, parent rule, `found`
+quirk, goal node), not the primitives, which test_oracle.py pins."""
+import numpy as np
+
+
+def _chain_cost(O, xyz, par, P, child):
+    cost = np.float32(0) + np.float32(O.norm(xyz[P], child))
+    cur, l, prev = par[P], 0, 0
+    while cur > 0:
+        cost = np.float32(cost + np.float32(O.norm(xyz[cur], xyz[P] if l == 0 else xyz[prev])))
+        l, prev, cur = 1, cur, par[cur]
+    return cost
+
+
+def test_sequential_loop_literal(oracle, bgr):
+    from bottleneck_guided_rrt_b200 import synth
+    O = oracle
+    occ = synth.make_map(64, 1, occupancy=0.0)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 2)
+    table = synth.points(9, 5000, 3.2)
+    start, goal = (0.2, 0.2, 0.2), (1.0, 0.6, 0.5)
+    P = bgr.PlannerParams(start, goal, mode=bgr.PLAN_MODE_RS, k=5, batch=1, flags=bgr.PLAN_QUIRKS, seed=99, goal_chance=0.2)
+    op = O.Planner(P, boxes, table)
+    op.run(200, 500)
+    oxyz, opar = op.tree()
+
+    mt = O.MT(99)
+    xyz, par = [np.array(start, np.float32)], [-1]
+    goal_f = np.array(goal, np.float32)
+    for _ in range(500):
+        if len(xyz) >= 200:
+            break
+        rc = np.float32(mt.std_uniform(0.0, 1.0))
+        ri = int(np.float32(int(mt.std_uniform(0.0, float(len(table))))))
+        prand = table[ri] if rc > np.float32(0.2) else goal_f
+        V = np.stack(xyz)
+        ni, _ = O.nearest(V, prand[None])
+        ni = int(ni[0])
+        pnew, found = O.steer(V[ni], prand, 0.15)
+        hit, _ = O.collide_spheres(boxes, pnew[None], 0.1, want_band=False)
+        if hit[0]:
+            continue
+        parent = ni
+        if len(xyz) > 5:
+            idx, _ = O.knn_brute(V, pnew[None], 5)
+            lowest, pc = _chain_cost(O, V, par, ni, pnew), -5
+            for ind in idx[0]:
+                t = _chain_cost(O, V, par, int(ind), pnew)
+                if t < lowest:
+                    pc, lowest = int(ind), t
+            if pc > 0:
+                parent = pc
+        xyz.append(pnew)
+        par.append(ni if found else parent)          # MS:1236-1238 quirk
+        if np.float32(O.norm(goal_f, pnew)) < np.float32(0.4):
+            par.append(len(xyz) - 1)
+            xyz.append(goal_f)
+            break
+    assert len(xyz) == len(opar)
+    assert np.array_equal(np.stack(xyz).view(np.uint32), oxyz.view(np.uint32))
+    assert par == opar.tolist()
