@@ -13,6 +13,7 @@ from .capi import (  # noqa: F401
     METHOD_AUTO,
     METHOD_BRUTE,
     METHOD_GRID,
+    METHOD_GRID_GENERAL,
     SHAPE_CYLINDER,
     SHAPE_CAPSULE,
     BgrError,

@@ -15,7 +15,7 @@ import numpy as np
 ALLOW_SELF_MATCH = 1
 SORT_RESULTS = 2
 TOUCH_STATISTICS = 1
-METHOD_AUTO, METHOD_BRUTE, METHOD_GRID = 0, 1, 2
+METHOD_AUTO, METHOD_BRUTE, METHOD_GRID, METHOD_GRID_GENERAL = 0, 1, 2, 3
 SHAPE_CYLINDER, SHAPE_CAPSULE = 0, 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))

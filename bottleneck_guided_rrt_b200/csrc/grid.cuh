@@ -276,6 +276,8 @@ struct GridKnnArgs {
     float* d2;
     int64_t index_base;
     unsigned long long* counter;
+    int fast;            // enable the one-pass ring-1 path
+    float fast_target;   // expected survivors the a-priori threshold aims at (k + ~2.5 sqrt k)
 };
 
 __device__ __forceinline__ uint32_t radius_sentinel_g(float mr) {
@@ -284,23 +286,150 @@ __device__ __forceinline__ uint32_t radius_sentinel_g(float mr) {
     return __float_as_uint(mr2) + 1u;
 }
 
-__global__ void __launch_bounds__(256) grid_knn_kernel(GridKnnArgs a) {
-    const int lane = threadIdx.x & 31;
-    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+constexpr int kFastCap = 64;          // per-warp candidate buffer of the fast path
+constexpr int kGridWarps = 8;
+
+// Fast path of a query whose k neighbours lie inside ring 1 (the common case by construction:
+// ~8 nodes per cell).  ONE pass over the 3x3x3 block with an a-priori threshold tau (from the
+// local node density), survivors compacted into a per-warp shared-memory buffer, then a single
+// 64-bit bitonic sort — instead of maintaining the sorted list through ~200 candidates.
+// Exactness: every node of the block (and of the unsorted tail) with d2 <= tau is in the
+// buffer; tau < b2 (nearest unscanned face), so if the buffer holds >= k admissible nodes its
+// k smallest keys are the global answer; if tau already equals the radius limit the (shorter)
+// answer is complete too.  Otherwise tau is rescaled from the observed count and the pass is
+// repeated; after kFastTries the caller falls back to the general ring search.
+constexpr int kFastTries = 3;
+
+__global__ void __launch_bounds__(kGridWarps * 32) grid_knn_kernel(GridKnnArgs a) {
+    __shared__ unsigned long long cand[kGridWarps][kFastCap];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
     if (qi >= a.nq) return;
     const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
     const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
     const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
     const float lim = __uint_as_float(sent - 1u);
+    unsigned long long touched = 0;
+    const GridGeom& gm = a.gm;
+    int cx = 0, cy = 0, cz = 0;
+    if (a.n_indexed > 0) {
+        cx = cell_coord(qx, gm.mn[0], gm.inv_cs, gm.g[0]);
+        cy = cell_coord(qy, gm.mn[1], gm.inv_cs, gm.g[1]);
+        cz = cell_coord(qz, gm.mn[2], gm.inv_cs, gm.g[2]);
+    }
+    auto dist2 = [&](float px, float py, float pz) {
+        const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
+        return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+    };
+    // nearest unscanned face after `ring` rings, squared and shrunk by the rounding slack of the
+    // cell computation (+inf when the block reaches every border)
+    auto face2 = [&](int ring) {
+        float b = __uint_as_float(kInfBits);
+        const float qv[3] = {qx, qy, qz};
+        const int cc[3] = {cx, cy, cz};
+#pragma unroll
+        for (int ax = 0; ax < 3; ++ax) {
+            if (cc[ax] - ring > 0) b = fminf(b, qv[ax] - (gm.mn[ax] + (float)(cc[ax] - ring) * gm.cs));
+            if (cc[ax] + ring + 1 < gm.g[ax]) b = fminf(b, (gm.mn[ax] + (float)(cc[ax] + ring + 1) * gm.cs) - qv[ax]);
+        }
+        if (b == __uint_as_float(kInfBits)) return b;
+        const float bs = fmaxf(0.f, b - 2e-3f * gm.cs);
+        return bs * bs * (1.f - 2e-6f);
+    };
+
+    // ------------------------------------------------------------------ fast path
+    if (a.n_indexed > 0 && a.fast) {
+        // the 9 x-rows of ring 1: lane t < 9 owns row (dy,dz)
+        int rs = 0, re = 0;
+        if (lane < 9) {
+            const int yy = cy + lane % 3 - 1, zz = cz + lane / 3 - 1;
+            if (yy >= 0 && yy < gm.g[1] && zz >= 0 && zz < gm.g[2]) {
+                const int x0 = max(cx - 1, 0), x1 = min(cx + 1, gm.g[0] - 1);
+                const int64_t rb = ((int64_t)zz * gm.g[1] + yy) * gm.g[0];
+                rs = __ldg(a.cell_start + rb + x0);
+                re = __ldg(a.cell_start + rb + x1 + 1);
+            }
+        }
+        int n27 = re - rs;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) n27 += __shfl_xor_sync(kFull, n27, o);   // lanes 0..15 hold rows
+        n27 = __shfl_sync(kFull, n27, 0);
+        const float b2 = face2(1);
+        // largest usable threshold: strictly below the unscanned region, within the radius limit
+        const float tmax = fminf(lim, b2 == __uint_as_float(kInfBits) ? lim : __uint_as_float(max(__float_as_uint(b2), 1u) - 1u));
+        if (n27 > 0) {
+            const int nxr = min(cx + 1, gm.g[0] - 1) - max(cx - 1, 0) + 1, nyr = min(cy + 1, gm.g[1] - 1) - max(cy - 1, 0) + 1,
+                      nzr = min(cz + 1, gm.g[2] - 1) - max(cz - 1, 0) + 1;
+            const float vol = (float)(nxr * nyr * nzr) * gm.cs * gm.cs * gm.cs;
+            const float r3 = a.fast_target * vol / (4.18879f * (float)n27);
+            const float r0 = cbrtf(r3);
+            float tau = fminf(r0 * r0, tmax);
+            for (int attempt = 0; attempt < kFastTries; ++attempt) {
+                int c = 0;
+                auto consider = [&](float px, float py, float pz, uint32_t pidx, bool valid) {
+                    const float d = dist2(px, py, pz);
+                    const bool pass = valid && (d <= tau) && (self || d > FLT_EPSILON);
+                    const unsigned m = __ballot_sync(kFull, pass);
+                    if (pass) {
+                        const int slot = c + __popc(m & ((1u << lane) - 1u));
+                        if (slot < kFastCap) cand[wib][slot] = pack_key(__float_as_uint(d), pidx);
+                    }
+                    c += __popc(m);
+                };
+                for (int64_t base = a.n_indexed; base < a.n; base += 32) {          // unsorted tail
+                    const int64_t j = base + lane;
+                    const bool valid = j < a.n;
+                    consider(valid ? a.x[j] : 0.f, valid ? a.y[j] : 0.f, valid ? a.z[j] : 0.f, (uint32_t)j, valid);
+                }
+#pragma unroll 1
+                for (int row = 0; row < 9; ++row) {
+                    const int s0 = __shfl_sync(kFull, rs, row), e0 = __shfl_sync(kFull, re, row);
+                    for (int b = s0; b < e0; b += 32) {
+                        const int j = b + lane;
+                        const bool valid = j < e0;
+                        float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid) p = __ldg(a.pts + j);
+                        consider(p.x, p.y, p.z, (uint32_t)__float_as_int(p.w), valid);
+                    }
+                }
+                touched += (unsigned long long)(n27 + (a.n - a.n_indexed));
+                if (c <= kFastCap && (c >= a.k || (tau >= tmax && tmax >= lim))) {
+                    __syncwarp();
+                    unsigned long long key = lane < c ? cand[wib][lane] : kKey64Max;
+                    warp_sort32_u64(key, lane);
+                    if (c > 32) {
+                        unsigned long long k2 = 32 + lane < c ? cand[wib][32 + lane] : kKey64Max;
+                        warp_sort32_u64(k2, lane);
+                        warp_merge32_u64(key, k2, lane);
+                    }
+                    if (lane < a.k) {
+                        const bool empty = key == kKey64Max;
+                        a.idx[qi * a.k + lane] = empty ? -1 : (int32_t)((int64_t)(uint32_t)key + a.index_base);
+                        a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float((uint32_t)(key >> 32));
+                    }
+                    if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+                    return;
+                }
+                __syncwarp();
+                if (c > kFastCap) {
+                    const float f = cbrtf(a.fast_target / (float)c);
+                    tau = tau * f * f;
+                } else {
+                    if (tau >= tmax) break;                       // needs ring 2: general search
+                    const float f = c > 0 ? cbrtf((a.fast_target + 6.f) / (float)c) : 2.f;
+                    tau = fminf(tmax, tau * f * f * 1.15f);
+                }
+            }
+        }
+    }
+
+    // ------------------------------------------------------------------ general ring search
     WarpList L;
     L.init(sent);
     uint32_t tau_d = sent, tau_i = 0u;
     float tau_f = __uint_as_float(sent);
-    unsigned long long touched = 0;
-
     auto offer = [&](float px, float py, float pz, uint32_t pidx, bool valid) {
-        const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
-        const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        const float d = dist2(px, py, pz);
         const bool pass = valid && (d <= tau_f) && (self || d > FLT_EPSILON);
         if (__any_sync(kFull, pass)) {
             warp_offer(L, pass, __float_as_uint(d), pidx, tau_d, tau_i, a.k, lane);
@@ -318,10 +447,6 @@ __global__ void __launch_bounds__(256) grid_knn_kernel(GridKnnArgs a) {
     touched += (unsigned long long)(a.n - a.n_indexed);
 
     if (a.n_indexed > 0) {
-        const GridGeom& gm = a.gm;
-        const int cx = cell_coord(qx, gm.mn[0], gm.inv_cs, gm.g[0]);
-        const int cy = cell_coord(qy, gm.mn[1], gm.inv_cs, gm.g[1]);
-        const int cz = cell_coord(qz, gm.mn[2], gm.inv_cs, gm.g[2]);
         const int gmax = max(gm.g[0], max(gm.g[1], gm.g[2]));
         for (int ring = 1; ring <= gmax; ++ring) {
             // items of this ring: every (y,z) row of the block contributes two items;
@@ -370,17 +495,8 @@ __global__ void __launch_bounds__(256) grid_knn_kernel(GridKnnArgs a) {
                 }
             }
             // ---- termination: nearest unscanned face (inf when the block reaches the border)
-            float b = __uint_as_float(kInfBits);
-            const float qv[3] = {qx, qy, qz};
-            const int cc[3] = {cx, cy, cz};
-#pragma unroll
-            for (int ax = 0; ax < 3; ++ax) {
-                if (cc[ax] - ring > 0) b = fminf(b, qv[ax] - (gm.mn[ax] + (float)(cc[ax] - ring) * gm.cs));
-                if (cc[ax] + ring + 1 < gm.g[ax]) b = fminf(b, (gm.mn[ax] + (float)(cc[ax] + ring + 1) * gm.cs) - qv[ax]);
-            }
-            if (b == __uint_as_float(kInfBits)) break;               // whole grid scanned
-            const float bs = fmaxf(0.f, b - 2e-3f * gm.cs);
-            const float b2 = bs * bs * (1.f - 2e-6f);
+            const float b2 = face2(ring);
+            if (b2 == __uint_as_float(kInfBits)) break;               // whole grid scanned
             if (b2 > lim) break;                                      // nothing farther is admissible
             if (tau_d != sent && tau_f < b2) break;                   // k found, all closer than the rest
         }
@@ -397,7 +513,7 @@ __global__ void __launch_bounds__(256) grid_knn_kernel(GridKnnArgs a) {
 inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,
                     const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
                     const float* d_radii, int32_t* d_idx, float* d_d2, int64_t index_base,
-                    unsigned long long* counter, cudaStream_t st) {
+                    unsigned long long* counter, int fast, cudaStream_t st) {
     GridKnnArgs a;
     a.gm = G.geom;
     a.pts = G.pts.p;
@@ -407,6 +523,8 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
     a.max_radius = max_radius; a.max_radii = d_radii;
     a.idx = d_idx; a.d2 = d_d2; a.index_base = index_base; a.counter = counter;
+    a.fast = fast;
+    a.fast_target = (float)k + 2.5f * sqrtf((float)k) + 1.f;
     grid_knn_kernel<<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
     return BGR_OK;

@@ -247,7 +247,7 @@ int bgr_nns_set_stream(bgr_nns* h, void* stream) {
 }
 
 int bgr_nns_set_method(bgr_nns* h, int method) {
-    BGR_ARG(h != nullptr && method >= 0 && method <= 2, "bad method");
+    BGR_ARG(h != nullptr && method >= 0 && method <= 3, "bad method");
     h->method = method;
     return BGR_OK;
 }
@@ -272,6 +272,8 @@ int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, 
     if (nq == 0) return BGR_OK;
     int method = h->method;
     if (method == BGR_METHOD_AUTO) method = (h->n >= 16384) ? BGR_METHOD_GRID : BGR_METHOD_BRUTE;
+    const int grid_fast = method != BGR_METHOD_GRID_GENERAL;
+    if (method == BGR_METHOD_GRID_GENERAL) method = BGR_METHOD_GRID;
     if (method == BGR_METHOD_GRID) {
         // re-bucket when the unsorted tail grew past a quarter of the indexed part
         if (h->grid.n_indexed == 0 || (h->n - h->grid.n_indexed) > std::max<int64_t>(4096, h->grid.n_indexed / 4))
@@ -282,7 +284,7 @@ int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, 
             BGR_CUDA(cudaMemsetAsync(h->counter.p, 0, sizeof(unsigned long long), h->stream));
         }
         BGR_CHECK(grid_knn(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, k, flags, max_radius, d_radii,
-                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, h->stream));
+                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, grid_fast, h->stream));
         if (stats) {
             unsigned long long c = 0;
             BGR_CUDA(cudaMemcpyAsync(&c, h->counter.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));

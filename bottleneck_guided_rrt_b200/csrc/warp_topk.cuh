@@ -80,6 +80,43 @@ __device__ __forceinline__ void warp_sort32(uint32_t& d, uint32_t& i, int lane) 
     }
 }
 
+// ---- 64-bit packed keys: (d2 bits << 32) | index, compared as one unsigned integer.
+// Keys of real candidates are distinct (indices are unique); the all-ones sentinel may repeat,
+// which no compare-exchange below is sensitive to.
+constexpr unsigned long long kKey64Max = ~0ull;
+__device__ __forceinline__ unsigned long long pack_key(uint32_t d, uint32_t i) {
+    return ((unsigned long long)d << 32) | (unsigned long long)i;
+}
+__device__ __forceinline__ unsigned long long shfl_xor_u64(unsigned long long v, int m) {
+    const uint32_t lo = __shfl_xor_sync(kFull, (uint32_t)v, m), hi = __shfl_xor_sync(kFull, (uint32_t)(v >> 32), m);
+    return ((unsigned long long)hi << 32) | lo;
+}
+// bitonic sort, one key per lane, ascending across lanes (15 compare-exchange stages)
+__device__ __forceinline__ void warp_sort32_u64(unsigned long long& key, int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int s = size >> 1; s > 0; s >>= 1) {
+            const unsigned long long o = shfl_xor_u64(key, s);
+            const bool take_min = ((lane & size) == 0) == ((lane & s) == 0);
+            if ((o < key) == take_min) key = o;
+        }
+    }
+}
+// `key` ascending across lanes, `other` ascending across lanes: keep the 32 smallest of the
+// union in `key`, ascending (reverse + bitonic merge, 6 stages)
+__device__ __forceinline__ void warp_merge32_u64(unsigned long long& key, unsigned long long other, int lane) {
+    const uint32_t lo = __shfl_sync(kFull, (uint32_t)other, 31 - lane), hi = __shfl_sync(kFull, (uint32_t)(other >> 32), 31 - lane);
+    const unsigned long long r = ((unsigned long long)hi << 32) | lo;
+    if (r < key) key = r;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        const unsigned long long o = shfl_xor_u64(key, s);
+        const bool take_min = (lane & s) == 0;
+        if ((o < key) == take_min) key = o;
+    }
+}
+
 // Offer one candidate per lane (pass == this lane's candidate may belong to the top-k) to
 // the list; tau_* is the warp-uniform key of entry k-1 and is updated.  Few candidates:
 // serial ballot/insert; many: bitonic sort + merge.  `eligible` must already contain the

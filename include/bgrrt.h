@@ -59,7 +59,8 @@ typedef struct bgr_nns bgr_nns;
 /* search methods for bgr_nns_set_method */
 #define BGR_METHOD_AUTO 0
 #define BGR_METHOD_BRUTE 1   /* exact brute-force scan (FP32-pipe bound) */
-#define BGR_METHOD_GRID 2    /* exact grid-bucketed scan with ring expansion */
+#define BGR_METHOD_GRID 2    /* exact grid-bucketed scan: one-pass ring-1 path, ring expansion behind it */
+#define BGR_METHOD_GRID_GENERAL 3 /* diagnostic: the ring-expansion search only */
 
 /* Replaces Nabo::NNSearchF::createKDTreeLinearHeap(cloud) (MS:1306).  cloud is copied to
  * an append-only SoA buffer in HBM (libnabo keeps a reference instead).  n may be 0. */

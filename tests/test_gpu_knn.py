@@ -20,7 +20,7 @@ def _check(B, O, pts, q, k, method, flags=0, max_radius=np.inf, max_radii=None):
     nns.close()
 
 
-@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("method", [1, 2, 3])
 @pytest.mark.parametrize("n,nq,k", [(5000, 300, 10), (40000, 1000, 16), (33, 7, 32), (1500, 64, 1), (70000, 333, 5)])
 def test_knn_matches_oracle(bgr, oracle, method, n, nq, k):
     pts = oracle.points(2, n, 25.6)
@@ -28,7 +28,7 @@ def test_knn_matches_oracle(bgr, oracle, method, n, nq, k):
     _check(bgr, oracle, pts, q, k, method)
 
 
-@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("method", [1, 2, 3])
 def test_knn_self_match_rule(bgr, oracle, method):
     """queries = nodes: without ALLOW_SELF_MATCH points with d2 <= FLT_EPSILON are skipped."""
     pts = oracle.points(2, 30000, 25.6)
@@ -44,7 +44,7 @@ def test_knn_self_match_rule(bgr, oracle, method):
     assert (idx[:, 0] != np.arange(2000)).all() and (d2[:, 0] > np.finfo(np.float32).eps).all()
 
 
-@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("method", [1, 2, 3])
 def test_knn_lattice_ties(bgr, oracle, method):
     """integer lattice: many exactly equal distances; ties must come out in index order."""
     g = np.arange(12, dtype=np.float32)
@@ -57,7 +57,7 @@ def test_knn_lattice_ties(bgr, oracle, method):
         _check(bgr, oracle, pts, q, k, method, flags=0)
 
 
-@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("method", [1, 2, 3])
 def test_knn_radius(bgr, oracle, method):
     pts = oracle.points(2, 20000, 10.0)
     q = oracle.points(3, 500, 10.0)
@@ -71,7 +71,7 @@ def test_knn_radius(bgr, oracle, method):
     assert ((idx == -1) == np.isinf(d2)).all() and (idx == -1).any()
 
 
-@pytest.mark.parametrize("method", [1, 2])
+@pytest.mark.parametrize("method", [1, 2, 3])
 def test_knn_append_only_store(bgr, oracle, method):
     """create + repeated append == one-shot create (replaces the reference's per-iteration rebuild)."""
     pts = oracle.points(5, 50000, 5.0)
@@ -93,7 +93,7 @@ def test_knn_clustered_and_outside_queries(bgr, oracle):
     centers = rng.uniform(0, 20, (12, 3))
     pts = (centers[rng.integers(0, 12, 60000)] + rng.normal(0, 0.15, (60000, 3))).astype(np.float32)
     q = np.concatenate([rng.uniform(-30, 50, (300, 3)), pts[:300] + 0.01]).astype(np.float32)
-    for method in (1, 2):
+    for method in (1, 2, 3):
         _check(bgr, oracle, pts, q, 16, method)
 
 
@@ -184,6 +184,9 @@ def test_knn_full_size_properties(bgr, oracle):
     nns.set_method(bgr.METHOD_GRID)
     gi, gd, _ = nns.knn(q, k)
     assert (np.diff(gd, axis=1) >= 0).all()
+    nns.set_method(bgr.METHOD_GRID_GENERAL)          # ring-expansion search only: same answer
+    ri, rd, _ = nns.knn(q, k)
+    assert canon_equal(gi, gd, ri, rd)
     sub = slice(0, 4096)
     nns.set_method(bgr.METHOD_BRUTE)
     bi, bd, _ = nns.knn(q[sub], k)
