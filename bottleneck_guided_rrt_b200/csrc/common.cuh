@@ -52,6 +52,17 @@ inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 int num_sms();  // of the current device (cached)
 
+// Filter image of a node for the brute-force kNN scan (knn_brute.cuh): {-2x,-2y,-2z,|p|^2''},
+// |p|^2'' = f32 sum of squares shrunk by 16 ulp and rounded down — it absorbs the rounding of
+// this sum and of the 3-FMA filter chain so the filter can never reject a true neighbour.
+// Every writer of the node store (append, planner commit) must write it with the node.
+#ifdef __CUDACC__
+__device__ __forceinline__ float4 filter_image(float px, float py, float pz) {
+    const float pn = __fadd_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)), __fmul_rn(pz, pz));
+    return make_float4(-2.f * px, -2.f * py, -2.f * pz, __fmul_rd(pn, 0.99999904632568359375f));
+}
+#endif
+
 // growable device buffer (append-only stores double their capacity)
 template <typename T>
 struct DevBuf {

@@ -5,7 +5,7 @@
 namespace bgr {
 // node store of a bgr_nns handle (nns.cu)
 int nns_reserve(bgr_nns* h, int64_t n);                       // capacity only, NaN padded, size unchanged
-void nns_soa(bgr_nns* h, float** x, float** y, float** z);    // current SoA arrays (valid until the next reserve)
+void nns_soa(bgr_nns* h, float** x, float** y, float** z, float4** f4);   // current arrays (valid until the next reserve)
 void nns_set_size(bgr_nns* h, int64_t n);                     // after a device-side append
 cudaStream_t nns_stream(bgr_nns* h);
 }  // namespace bgr

@@ -19,6 +19,7 @@ struct bgr_nns {
     int64_t index_base = 0;
     // append-only SoA store, NaN padded to a multiple of kTile
     DevBuf<float> x, y, z;
+    DevBuf<float4> f4;           // filter image {-2x,-2y,-2z,|p|^2''} (knn_brute.cuh)
     int64_t n = 0;
     // scratch
     DevBuf<float> stage_f;       // interleaved staging for host API / appends
@@ -31,12 +32,14 @@ struct bgr_nns {
 namespace {
 
 __global__ void deinterleave_kernel(const float* __restrict__ src, int64_t m, float* __restrict__ x,
-                                    float* __restrict__ y, float* __restrict__ z) {
+                                    float* __restrict__ y, float* __restrict__ z, float4* __restrict__ f4) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < m) {
-        x[i] = src[3 * i];
-        y[i] = src[3 * i + 1];
-        z[i] = src[3 * i + 2];
+        const float px = src[3 * i], py = src[3 * i + 1], pz = src[3 * i + 2];
+        x[i] = px;
+        y[i] = py;
+        z[i] = pz;
+        f4[i] = filter_image(px, py, pz);
     }
 }
 
@@ -47,12 +50,14 @@ int grow_store(bgr_nns* h, int64_t need) {
     BGR_CHECK(h->x.reserve(need, h->stream, true, h->n));
     BGR_CHECK(h->y.reserve(need, h->stream, true, h->n));
     BGR_CHECK(h->z.reserve(need, h->stream, true, h->n));
+    BGR_CHECK(h->f4.reserve(need, h->stream, true, h->n));
     (void)old_cap;
     // 0xFF bytes = NaN: padded nodes can never be admitted by any comparison
     const int64_t cap = h->x.cap;
     BGR_CUDA(cudaMemsetAsync(h->x.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
     BGR_CUDA(cudaMemsetAsync(h->y.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
     BGR_CUDA(cudaMemsetAsync(h->z.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float), h->stream));
+    BGR_CUDA(cudaMemsetAsync(h->f4.p + h->n, 0xFF, (size_t)(cap - h->n) * sizeof(float4), h->stream));
     return BGR_OK;
 }
 
@@ -61,13 +66,14 @@ int append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
     BGR_ARG(h->n + m < (int64_t)1 << 31, "node count exceeds int32 index range");
     BGR_CHECK(grow_store(h, h->n + m));
     deinterleave_kernel<<<(unsigned)div_up(m, 256), 256, 0, h->stream>>>(d_pts, m, h->x.p + h->n,
-                                                                          h->y.p + h->n, h->z.p + h->n);
+                                                                          h->y.p + h->n, h->z.p + h->n, h->f4.p + h->n);
     BGR_LAUNCH_CHECK();
     h->n += m;
     return BGR_OK;
 }
 
-constexpr size_t kBruteSmem = (size_t)kStages * 3 * kTile * sizeof(float) + 2 * kStages * sizeof(uint64_t);
+constexpr size_t kBruteSmem = (size_t)kStages * kTile * sizeof(float4) + 2 * kStages * sizeof(uint64_t);
+constexpr size_t kNearestSmem = (size_t)kStages * 3 * kTile * sizeof(float) + 2 * kStages * sizeof(uint64_t);
 
 template <int R>
 int launch_brute(bgr_nns* h, BruteArgs a, int chunks) {
@@ -86,11 +92,11 @@ template <int R>
 int launch_nearest(bgr_nns* h, NearestArgs a, int chunks) {
     static bool attr_set = false;
     if (!attr_set) {
-        BGR_CUDA(cudaFuncSetAttribute(nearest_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBruteSmem));
+        BGR_CUDA(cudaFuncSetAttribute(nearest_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNearestSmem));
         attr_set = true;
     }
     dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
-    nearest_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
+    nearest_kernel<R><<<grid, kBruteThreads, kNearestSmem, h->stream>>>(a);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
@@ -120,7 +126,7 @@ int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flag
     int64_t per;
     plan_scan(nq, h->n, &R, &chunks, &per);
     BruteArgs a;
-    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = h->n;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.f4 = h->f4.p; a.n = h->n;
     a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
     a.max_radius = max_radius; a.max_radii = d_radii;
     a.chunk_nodes = per;
@@ -174,7 +180,10 @@ int check_knn_args(const bgr_nns* h, int64_t nq, int k, float eps, unsigned flag
 
 namespace bgr {
 int nns_reserve(bgr_nns* h, int64_t n) { return grow_store(h, n); }
-void nns_soa(bgr_nns* h, float** x, float** y, float** z) { *x = h->x.p; *y = h->y.p; *z = h->z.p; }
+void nns_soa(bgr_nns* h, float** x, float** y, float** z, float4** f4) {
+    *x = h->x.p; *y = h->y.p; *z = h->z.p;
+    if (f4) *f4 = h->f4.p;
+}
 void nns_set_size(bgr_nns* h, int64_t n) { h->n = n; }
 cudaStream_t nns_stream(bgr_nns* h) { return h->stream; }
 }  // namespace bgr
@@ -366,7 +375,7 @@ int bgr_nns_nearest(bgr_nns* h, const float* q, int64_t nq, int32_t* idx, float*
 int bgr_nns_destroy(bgr_nns* h) {
     if (!h) return BGR_OK;
     cudaStreamSynchronize(h->stream);
-    h->x.release(); h->y.release(); h->z.release();
+    h->x.release(); h->y.release(); h->z.release(); h->f4.release();
     h->stage_f.release(); h->q_dev.release(); h->radii_dev.release(); h->d2_dev.release();
     h->part_d2.release(); h->idx_dev.release(); h->part_idx.release(); h->counter.release();
     grid_release(h->grid);

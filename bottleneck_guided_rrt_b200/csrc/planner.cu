@@ -246,7 +246,7 @@ __global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS
 
 // One CTA: goal cut (first accepted candidate within goal_tol, MS:1340), ordered compaction,
 // append to the store (MS:1325-1327) and the goal node (MS:1346-1347).
-__global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, float* y, float* z) {
+__global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, float* y, float* z, float4* f4) {
     __shared__ int s_goal;
     __shared__ int warp_tot[32];
     __shared__ int s_base;
@@ -285,6 +285,7 @@ __global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, 
         if (take) {
             const int64_t ni = d.n + rank;
             x[ni] = d.pnew[3 * c]; y[ni] = d.pnew[3 * c + 1]; z[ni] = d.pnew[3 * c + 2];
+            f4[ni] = filter_image(d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]);
             d.par[ni] = d.parent[c];
         }
         __syncthreads();
@@ -298,6 +299,7 @@ __global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, 
         if (goal_c != 0x7fffffff) {
             const int64_t gi = d.n + acc;
             x[gi] = d.p.goal[0]; y[gi] = d.p.goal[1]; z[gi] = d.p.goal[2];
+            f4[gi] = filter_image(d.p.goal[0], d.p.goal[1], d.p.goal[2]);
             d.par[gi] = (int32_t)(gi - 1);                      // goal.push_back(V.size()-1)
         }
     }
@@ -499,7 +501,8 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     PlanDev d;
     d.p = P;
     float *x, *y, *z;
-    nns_soa(pl->nns, &x, &y, &z);
+    float4* f4;
+    nns_soa(pl->nns, &x, &y, &z, &f4);
     d.x = x; d.y = y; d.z = z;
     d.par = pl->par.p;
     d.n = N; d.B = B; d.K = K; d.W = W; d.have_knn = have_knn;
@@ -532,7 +535,7 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_LAUNCH_CHECK();
     plan_select_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
-    plan_commit_kernel<<<1, 1024, 0, st>>>(d, x, y, z);
+    plan_commit_kernel<<<1, 1024, 0, st>>>(d, x, y, z, f4);
     BGR_LAUNCH_CHECK();
     if (rewire && have_knn) {
         plan_rewire_propose_kernel<<<gbk, 256, 0, st>>>(d);
@@ -576,7 +579,7 @@ int bgr_planner_get_tree(bgr_planner* pl, float* xyz, int32_t* parent) {
     BGR_ARG(pl != nullptr && xyz != nullptr && parent != nullptr, "bad arguments");
     const int64_t n = bgr_nns_size(pl->nns);
     float *x, *y, *z;
-    nns_soa(pl->nns, &x, &y, &z);
+    nns_soa(pl->nns, &x, &y, &z, nullptr);
     std::vector<float> hx(n), hy(n), hz(n);
     BGR_CUDA(cudaMemcpyAsync(hx.data(), x, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
     BGR_CUDA(cudaMemcpyAsync(hy.data(), y, (size_t)n * 4, cudaMemcpyDeviceToHost, pl->stream));
