@@ -381,15 +381,28 @@ __global__ void __launch_bounds__(kGridWarps * 32) grid_knn_kernel(GridKnnArgs a
                     const bool valid = j < a.n;
                     consider(valid ? a.x[j] : 0.f, valid ? a.y[j] : 0.f, valid ? a.z[j] : 0.f, (uint32_t)j, valid);
                 }
+                // rows in groups of three: the three leading LDG.128 are in flight together
 #pragma unroll 1
-                for (int row = 0; row < 9; ++row) {
-                    const int s0 = __shfl_sync(kFull, rs, row), e0 = __shfl_sync(kFull, re, row);
-                    for (int b = s0; b < e0; b += 32) {
-                        const int j = b + lane;
-                        const bool valid = j < e0;
-                        float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (valid) p = __ldg(a.pts + j);
-                        consider(p.x, p.y, p.z, (uint32_t)__float_as_int(p.w), valid);
+                for (int g = 0; g < 9; g += 3) {
+                    int s0[3], e0[3];
+                    float4 p[3];
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        s0[i] = __shfl_sync(kFull, rs, g + i);
+                        e0[i] = __shfl_sync(kFull, re, g + i);
+                        p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (s0[i] + lane < e0[i]) p[i] = __ldg(a.pts + s0[i] + lane);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        if (s0[i] < e0[i]) consider(p[i].x, p[i].y, p[i].z, (uint32_t)__float_as_int(p[i].w), s0[i] + lane < e0[i]);
+                        for (int b = s0[i] + 32; b < e0[i]; b += 32) {      // rows longer than a warp (rare)
+                            const int j = b + lane;
+                            const bool valid = j < e0[i];
+                            float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (valid) q4 = __ldg(a.pts + j);
+                            consider(q4.x, q4.y, q4.z, (uint32_t)__float_as_int(q4.w), valid);
+                        }
                     }
                 }
                 touched += (unsigned long long)(n27 + (a.n - a.n_indexed));
