@@ -97,13 +97,20 @@ def dist_env():
 
 
 # ------------------------------------------------------------------------------ GPU arm
-def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s=0.25):
+def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s=0.25, prewarm_iters=None):
     """W warm-up steps, then exactly K timed steps; each step has its own CUDA event pair on
-    `stream` and L2 is flushed (untimed) between steps.  Returns total ms of the K steps."""
-    t0 = time.perf_counter()
-    while time.perf_counter() - t0 < prewarm_s:      # untimed clock ramp (idle SM clock is 120 MHz)
-        step_fn()
+    `stream` and L2 is flushed (untimed) between steps.  Returns total ms of the K steps.
+    A step that contains a collective must pass prewarm_iters: a wall-clock-bounded ramp would
+    run a different number of collectives on each rank (deadlock)."""
+    if prewarm_iters is not None:
+        for _ in range(prewarm_iters):
+            step_fn()
         stream.synchronize()
+    else:
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < prewarm_s:      # untimed clock ramp (idle SM clock is 120 MHz)
+            step_fn()
+            stream.synchronize()
     for _ in range(warmup):
         flush()
         step_fn()
@@ -292,7 +299,7 @@ def run_ours(args):
             def shard_step():
                 snn.knn(sq, K_NN)
 
-            sh_ms = max_over_ranks(timed_steps(torch, stream, shard_step, args.steps, args.warmup, flush, barrier))
+            sh_ms = max_over_ranks(timed_steps(torch, stream, shard_step, args.steps, args.warmup, flush, barrier, prewarm_iters=20))
             out["sharded_knn"] = {"value": N_QUERIES / (sh_ms / args.steps * 1e-3), "unit": "queries/s",
                                   "ms_per_step": sh_ms / args.steps, "nodes_total": SHARD_NODES * world,
                                   "nodes_per_gpu": SHARD_NODES, "queries": N_QUERIES, "k": K_NN,

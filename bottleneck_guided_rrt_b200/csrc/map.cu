@@ -440,9 +440,13 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
 constexpr int kSweepThreads = 256;
 constexpr int kSweepEdges = 256;
 constexpr int kRectMax = 8;
+constexpr int kSqCap = 2048;      // shared-memory queue of ambiguous (edge, leaf) pairs per CTA
+constexpr int kSqFlushAt = 1024;  // flush (filtered by F_DEEP) once the queue is this full
 
 struct SweepEdge {
     double c[3], u[3], h;
+    double sb, sc;      // lateral slopes d(b)/d(ax), d(c)/d(ax) of the axis line (|.| <= 1: ax is dominant)
+    double xlo, xhi;    // extent of the axis segment on ax
     int ax, i_lo;
 };
 struct NarrowRec {
@@ -465,11 +469,62 @@ struct Edge2Args {
     uint8_t* band;
 };
 
+// CTA-wide: move the shared-memory queue to the global queue, dropping the pairs of edges
+// that already hold a deep-hit certificate (all pairs of an edge come from its own CTA, so the
+// filter is exact at the final flush).  Must be called by all threads of the CTA.
+__device__ __forceinline__ void sweep_flush(const Edge2Args& a, const unsigned long long* sq, int* sq_count,
+                                            unsigned* eflags, int64_t e0) {
+    __syncthreads();
+    const int n = min(*sq_count, kSqCap);
+    const int lane = threadIdx.x & 31;
+    for (int base = 0; base < n; base += kSweepThreads) {
+        const int j = base + (int)threadIdx.x;
+        unsigned long long rec = 0;
+        bool keep = false;
+        if (j < n) {
+            rec = sq[j];
+            keep = !(eflags[(int)(rec >> 40)] & F_DEEP);
+        }
+        const unsigned km = __ballot_sync(kFull, keep);
+        if (km) {
+            unsigned gbase = 0;
+            if (lane == __ffs(km) - 1) gbase = atomicAdd(a.qctl, (unsigned)__popc(km));
+            gbase = __shfl_sync(kFull, gbase, __ffs(km) - 1);
+            if (keep) {
+                const unsigned slot = gbase + __popc(km & ((1u << lane) - 1u));
+                const int el = (int)(rec >> 40);
+                if (slot < a.queue_cap) {
+                    NarrowRec r;
+                    r.edge = (uint32_t)(e0 + el);
+                    r.a = (uint32_t)((rec >> 24) & 0xFFFFu);          // L<<12 | lx
+                    r.b = (uint32_t)(rec & 0xFFFFFFu);                // ly<<12 | lz
+                    r.pad = 0;
+                    a.queue[slot] = r;
+                } else {
+                    atomicOr(&eflags[el], F_OVERFLOW);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *sq_count = 0;
+    __syncthreads();
+}
+
+// (ax, b, c) coordinates -> (x, y, z), with b = (ax+1)%3 and c = (ax+2)%3; selects, no local arrays
+__device__ __forceinline__ void unperm(int ax, int i, int jb, int jc, int& x, int& y, int& z) {
+    x = ax == 0 ? i : (ax == 1 ? jc : jb);
+    y = ax == 0 ? jb : (ax == 1 ? i : jc);
+    z = ax == 0 ? jc : (ax == 1 ? jb : i);
+}
+
 __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a) {
     __shared__ SweepEdge es[kSweepEdges];
+    __shared__ unsigned long long sq[kSqCap];
     __shared__ int prefix[kSweepEdges + 1];
     __shared__ unsigned eflags[kSweepEdges];
     __shared__ int warp_sums[kSweepThreads / 32];
+    __shared__ int sq_count;
     __shared__ unsigned long long st_cand;
 
     const MapView& m = a.m;
@@ -477,7 +532,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
     const int64_t e0 = (int64_t)blockIdx.x * kSweepEdges;
     const int ne = (int)min((int64_t)kSweepEdges, a.n - e0);
     const double rm = a.radius + kSweepMargin;
-    if (tid == 0) st_cand = 0;
+    if (tid == 0) { st_cand = 0; sq_count = 0; }
 
     // ---- phase 0: per-edge frame (thread per edge)
     int myslabs = 0;
@@ -497,9 +552,15 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
         s.ax = 0;
         if (fabs(s.u[1]) > fabs(s.u[s.ax])) s.ax = 1;
         if (fabs(s.u[2]) > fabs(s.u[s.ax])) s.ax = 2;
+        const int bx = (s.ax + 1) % 3, cx = (s.ax + 2) % 3;
+        const double inv_uax = 1.0 / s.u[s.ax];            // |u[ax]| >= 1/sqrt(3): u is a unit vector
+        s.sb = s.u[bx] * inv_uax;
+        s.sc = s.u[cx] * inv_uax;
         const double pa = s.c[s.ax] - s.h * s.u[s.ax], pb = s.c[s.ax] + s.h * s.u[s.ax];
-        int lo = (int)floor((fmin(pa, pb) - rm - m.origin[s.ax]) * m.inv_res);
-        int hi = (int)floor((fmax(pa, pb) + rm - m.origin[s.ax]) * m.inv_res);
+        s.xlo = fmin(pa, pb);
+        s.xhi = fmax(pa, pb);
+        int lo = (int)floor((s.xlo - rm - m.origin[s.ax]) * m.inv_res);
+        int hi = (int)floor((s.xhi + rm - m.origin[s.ax]) * m.inv_res);
         lo = max(lo, 0);
         hi = min(hi, m.dims[s.ax] - 1);
         s.i_lo = lo;
@@ -534,6 +595,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
     unsigned long long n_cand = 0;
 
     for (int w0 = 0; w0 < total; w0 += kSweepThreads) {
+        if (__syncthreads_or(tid == 0 && sq_count >= kSqFlushAt)) sweep_flush(a, sq, &sq_count, eflags, e0);
         // ---- one item per thread: occupancy mask of its rectangle
         const int w = w0 + tid;
         unsigned long long occ = 0;
@@ -548,43 +610,36 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
             const SweepEdge& s = es[el];
             const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
             const int i = s.i_lo + (w - prefix[el]);
+            // the part of the axis segment whose ax coordinate lies in the slab inflated by rm
+            // (clamped to the segment: slabs past an end see the end point + the rm margin)
             const double x0 = m.origin[ax] + (double)i * m.res - rm, x1 = m.origin[ax] + (double)(i + 1) * m.res + rm;
-            const double a0ax = s.c[ax] - s.h * s.u[ax];
-            const double dax = 2.0 * s.h * s.u[ax];
-            double t0 = 0.0, t1 = 1.0;
-            if (fabs(dax) > 1e-12) {
-                const double ta = (x0 - a0ax) / dax, tb = (x1 - a0ax) / dax;
-                t0 = fmax(0.0, fmin(ta, tb));
-                t1 = fmin(1.0, fmax(ta, tb));
-            }
-            if (t0 <= t1) {
-                int r0[2], r1[2];
-                bool none = false;
+            const double xa = fmin(fmax(x0, s.xlo), s.xhi) - s.c[ax], xb = fmax(fmin(x1, s.xhi), s.xlo) - s.c[ax];
+            int r0[2], r1[2];
+            bool none = false;
 #pragma unroll
-                for (int k = 0; k < 2; ++k) {
-                    const int b = k ? cx : bx;
-                    const double a0b = s.c[b] - s.h * s.u[b], db = 2.0 * s.h * s.u[b];
-                    const double pa = a0b + t0 * db, pb = a0b + t1 * db;
-                    int lo_b = (int)floor((fmin(pa, pb) - rm - m.origin[b]) * m.inv_res);
-                    int hi_b = (int)floor((fmax(pa, pb) + rm - m.origin[b]) * m.inv_res);
-                    lo_b = max(lo_b, 0);
-                    hi_b = min(hi_b, m.dims[b] - 1);
-                    hi_b = min(hi_b, lo_b + kRectMax - 1);   // host guarantees the hull fits kRectMax cells
-                    r0[k] = lo_b;
-                    r1[k] = hi_b;
-                    none |= lo_b > hi_b;
-                }
-                if (!none) {
-                    for (int jc = r0[1]; jc <= r1[1]; ++jc)
-                        for (int jb = r0[0]; jb <= r1[0]; ++jb) {
-                            int v[3];
-                            v[ax] = i; v[bx] = jb; v[cx] = jc;
-                            if (test_bit(m.lv[0], v[0], v[1], v[2]))
-                                occ |= 1ull << ((jc - r0[1]) * kRectMax + (jb - r0[0]));
-                        }
-                    info_a = el | (i << 8);
-                    info_b = r0[0] | (r0[1] << 12);
-                }
+            for (int k = 0; k < 2; ++k) {
+                const int b = k ? cx : bx;
+                const double sl = k ? s.sc : s.sb;
+                const double pa = s.c[b] + xa * sl, pb = s.c[b] + xb * sl;
+                int lo_b = (int)floor((fmin(pa, pb) - rm - m.origin[b]) * m.inv_res);
+                int hi_b = (int)floor((fmax(pa, pb) + rm - m.origin[b]) * m.inv_res);
+                lo_b = max(lo_b, 0);
+                hi_b = min(hi_b, m.dims[b] - 1);
+                hi_b = min(hi_b, lo_b + kRectMax - 1);   // host guarantees the hull fits kRectMax cells
+                r0[k] = lo_b;
+                r1[k] = hi_b;
+                none |= lo_b > hi_b;
+            }
+            if (!none) {
+                for (int jc = r0[1]; jc <= r1[1]; ++jc)
+                    for (int jb = r0[0]; jb <= r1[0]; ++jb) {
+                        int vx, vy, vz;
+                        unperm(ax, i, jb, jc, vx, vy, vz);
+                        if (test_bit(m.lv[0], vx, vy, vz))
+                            occ |= 1ull << ((jc - r0[1]) * kRectMax + (jb - r0[0]));
+                    }
+                info_a = el | (i << 8);
+                info_b = r0[0] | (r0[1] << 12);
             }
         }
         // ---- dense processing of the warp's candidates
@@ -609,7 +664,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
             const unsigned long long s_occ = __shfl_sync(kFull, occ, src);
             const int s_a = __shfl_sync(kFull, info_a, src), s_b = __shfl_sync(kFull, info_b, src);
             bool ambiguous = false;
-            NarrowRec rec;
+            unsigned long long rec = 0;
             int el = 0;
             if (active) {
                 const int rank = j - (s_incl - s_cnt);
@@ -619,12 +674,14 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                 el = s_a & 255;
                 const int i = s_a >> 8, b0 = s_b & 4095, c0 = s_b >> 12;
                 const SweepEdge& s = es[el];
-                const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
-                int v[3], l[3];
-                v[ax] = i; v[bx] = b0 + (bit & (kRectMax - 1)); v[cx] = c0 + (bit >> 3);
-                const int L = find_leaf(m, v[0], v[1], v[2], l[0], l[1], l[2]);
+                const int ax = s.ax;
+                const int vb = b0 + (bit & (kRectMax - 1)), vc = c0 + (bit >> 3);
+                int vx, vy, vz, l[3];
+                unperm(ax, i, vb, vc, vx, vy, vz);
+                const int L = find_leaf(m, vx, vy, vz, l[0], l[1], l[2]);
+                const int lb = ax == 0 ? l[1] : (ax == 1 ? l[2] : l[0]), lc = ax == 0 ? l[2] : (ax == 1 ? l[0] : l[1]);
                 // one representative cell per (item, leaf)
-                if (v[bx] == max(b0, l[bx]) && v[cx] == max(c0, l[cx])) {
+                if (vb == max(b0, lb) && vc == max(c0, lc)) {
                     ++n_cand;
                     D3 bc;
                     double e;
@@ -654,27 +711,40 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                     } else if (deep) {
                         atomicOr(&eflags[el], F_HIT | F_DEEP);
                     } else {
-                        ambiguous = true;
-                        rec.edge = (uint32_t)(e0 + el);
-                        rec.a = ((uint32_t)L << 12) | (uint32_t)l[0];
-                        rec.b = ((uint32_t)l[1] << 12) | (uint32_t)l[2];
-                        rec.pad = 0;
+                        ambiguous = !(eflags[el] & F_DEEP);
+                        rec = ((unsigned long long)el << 40) | ((unsigned long long)L << 36) |
+                              ((unsigned long long)l[0] << 24) | ((unsigned long long)l[1] << 12) | (unsigned long long)l[2];
                     }
                 }
             }
             const unsigned am = __ballot_sync(kFull, ambiguous);
             if (am) {
-                unsigned base = 0;
-                if (lane == __ffs(am) - 1) base = atomicAdd(a.qctl, (unsigned)__popc(am));
+                int base = 0;
+                if (lane == __ffs(am) - 1) base = atomicAdd(&sq_count, __popc(am));
                 base = __shfl_sync(kFull, base, __ffs(am) - 1);
                 if (ambiguous) {
-                    const unsigned slot = base + __popc(am & ((1u << lane) - 1u));
-                    if (slot < a.queue_cap) a.queue[slot] = rec;
-                    else atomicOr(&eflags[el], F_OVERFLOW);
+                    const int slot = base + __popc(am & ((1u << lane) - 1u));
+                    if (slot < kSqCap) {
+                        sq[slot] = rec;
+                    } else {
+                        // shared queue full (a flush happens at the next item batch): straight to the global queue
+                        const unsigned g = atomicAdd(a.qctl, 1u);
+                        if (g < a.queue_cap) {
+                            NarrowRec r;
+                            r.edge = (uint32_t)(e0 + el);
+                            r.a = (uint32_t)((rec >> 24) & 0xFFFFu);
+                            r.b = (uint32_t)(rec & 0xFFFFFFu);
+                            r.pad = 0;
+                            a.queue[g] = r;
+                        } else {
+                            atomicOr(&eflags[el], F_OVERFLOW);
+                        }
+                    }
                 }
             }
         }
     }
+    sweep_flush(a, sq, &sq_count, eflags, e0);
     if (a.stats) atomicAdd(&st_cand, n_cand);
     __syncthreads();
     if (tid < ne) {
