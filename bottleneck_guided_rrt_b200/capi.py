@@ -65,6 +65,15 @@ def lib():
     L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_destroy.argtypes = [vp]
     L.bgr_knn_merge_dev.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
+    L.bgr_peer_handle_bytes.restype = i32
+    L.bgr_peer_create.argtypes = [i32, i32, i64, vp]
+    L.bgr_peer_export.argtypes = [vp, vp]
+    L.bgr_peer_open.argtypes = [vp, i32, vp]
+    L.bgr_peer_slab.argtypes = [vp, vp, vp]
+    L.bgr_peer_result.argtypes = [vp, vp, vp]
+    L.bgr_peer_merge_dev.argtypes = [vp, i64, i32, vp]
+    L.bgr_peer_status.argtypes = [vp, vp, vp]
+    L.bgr_peer_destroy.argtypes = [vp]
     L.bgr_map_create.argtypes = [f64, vp, vp, vp]
     L.bgr_map_set_stream.argtypes = [vp, vp]
     L.bgr_map_set_boxes.argtypes = [vp, vp, i64]
@@ -264,6 +273,65 @@ def knn_merge_dev(idx_slabs, d2_slabs, idx_out, d2_out, stream=0):
     _check(lib().bgr_knn_merge_dev(_ptr(idx_slabs), _ptr(d2_slabs), g, nq, k, _ptr(idx_out), _ptr(d2_out),
                                    C.c_void_p(stream or 0)))
     return idx_out, d2_out
+
+
+class _DevView:
+    """raw device memory as a __cuda_array_interface__ object (torch.as_tensor wraps it, no copy)"""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class PeerExchange:
+    """bgr_peer_*: the sharded search's exchange step over NVLink peer memory (CUDA IPC windows,
+    one merge kernel with peer loads/stores instead of all-gather + merge).  `exchange_handles`
+    is a callable that takes this rank's handle (bytes) and returns the list of all ranks'
+    handles (e.g. torch.distributed.all_gather_object)."""
+
+    def __init__(self, rank, world, max_entries, exchange_handles, device=None):
+        h = C.c_void_p()
+        _check(lib().bgr_peer_create(rank, world, max_entries, C.byref(h)))
+        self._h, self.rank, self.world, self.device = h, rank, world, device
+        nb = lib().bgr_peer_handle_bytes()
+        buf = C.create_string_buffer(nb)
+        _check(lib().bgr_peer_export(self._h, buf))
+        handles = exchange_handles(bytes(buf.raw))
+        for p, hb in enumerate(handles):
+            if p != rank:
+                _check(lib().bgr_peer_open(self._h, p, C.create_string_buffer(hb, nb)))
+
+    def __del__(self):
+        self.close()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bgr_peer_destroy(self._h)
+            self._h = None
+
+    def _region(self, fn):
+        pi, pd = C.c_void_p(), C.c_void_p()
+        _check(fn(self._h, C.byref(pi), C.byref(pd)))
+        return pi.value, pd.value
+
+    def slab_ptrs(self):
+        return self._region(lib().bgr_peer_slab)
+
+    def result(self, nq, k):
+        """(idx (Q,k) int32, d2 (Q,k) float32) CUDA tensors viewing the window's result region"""
+        import torch
+        pi, pd = self._region(lib().bgr_peer_result)
+        dev = self.device if self.device is not None else torch.device("cuda", torch.cuda.current_device())
+        return (torch.as_tensor(_DevView(pi, (nq, k), "<i4"), device=dev),
+                torch.as_tensor(_DevView(pd, (nq, k), "<f4"), device=dev))
+
+    def merge(self, nq, k, stream=0):
+        _check(lib().bgr_peer_merge_dev(self._h, nq, k, C.c_void_p(stream or 0)))
+
+    def status(self, stream=0):
+        e = C.c_int(0)
+        _check(lib().bgr_peer_status(self._h, C.c_void_p(stream or 0), C.byref(e)))
+        return e.value
 
 
 class OccupancyMap:

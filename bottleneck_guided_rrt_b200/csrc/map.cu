@@ -441,7 +441,6 @@ constexpr int kSweepThreads = 256;
 constexpr int kSweepEdges = 256;
 constexpr int kRectMax = 8;
 constexpr int kSqCap = 2048;      // shared-memory queue of ambiguous (edge, leaf) pairs per CTA
-constexpr int kSqFlushAt = 1024;  // flush (filtered by F_DEEP) once the queue is this full
 
 struct SweepEdge {
     double c[3], u[3], h;
@@ -511,11 +510,49 @@ __device__ __forceinline__ void sweep_flush(const Edge2Args& a, const unsigned l
     __syncthreads();
 }
 
-// (ax, b, c) coordinates -> (x, y, z), with b = (ax+1)%3 and c = (ax+2)%3; selects, no local arrays
+// Sweep-plane axes of a dominant axis ax: b = the lower, c = the higher of the two others
+// (ax=0: b=y,c=z; ax=1: b=x,c=z; ax=2: b=x,c=y), so that a brick word yields its 4x4 slice at
+// a fixed ax coordinate with shifts only.  (i, jb, jc) -> (x, y, z); selects, no local arrays.
 __device__ __forceinline__ void unperm(int ax, int i, int jb, int jc, int& x, int& y, int& z) {
-    x = ax == 0 ? i : (ax == 1 ? jc : jb);
+    x = ax == 0 ? i : jb;
     y = ax == 0 ? jb : (ax == 1 ? i : jc);
-    z = ax == 0 ? jc : (ax == 1 ? jb : i);
+    z = ax == 2 ? i : jc;
+}
+
+// Occupancy of the rectangle [b0,b1] x [c0,c1] (<= 8x8 cells) of the plane ax = i, as a 64-bit
+// mask with bit (jc-c0)*8 + (jb-b0): one 64-bit load per 4x4x4 brick the rectangle touches
+// (instead of one per cell); empty bricks cost one load + one test.
+__device__ __forceinline__ unsigned long long rect_occupancy(const LevelGrid& g, int ax, int i, int b0, int b1,
+                                                             int c0, int c1) {
+    const int64_t sy = g.nb[0], sz = (int64_t)g.nb[0] * g.nb[1];
+    const int64_t si = ax == 0 ? 1 : (ax == 1 ? sy : sz), sb = ax == 0 ? sy : 1, sc = ax == 2 ? sy : sz;
+    const int il = i & 3;
+    const unsigned colmask = (1u << (b1 - b0 + 1)) - 1u;
+    // bit offset of row r (c-local) / of the slice inside the word, and the bit stride along b
+    const int row_mul = ax == 2 ? 4 : 16, base_sh = ax == 2 ? 16 * il : (ax == 1 ? 4 * il : il);
+    const uint64_t* base = g.bits + (int64_t)(i >> 2) * si;
+    unsigned long long occ = 0;
+    for (int cb = c0 >> 2; cb <= (c1 >> 2); ++cb)
+        for (int bb = b0 >> 2; bb <= (b1 >> 2); ++bb) {
+            const unsigned long long W = __ldg(base + bb * sb + cb * sc);
+            if (W == 0ull) continue;
+            unsigned E = 0;   // 4 rows (c-local) in 4 bytes, 4 columns (b-local) in the low nibble of each
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const unsigned v = (unsigned)(W >> (base_sh + row_mul * r));
+                // ax=0: the row's cells are 4 bits apart (bit = z<<4 | y<<2 | x): gather them with a multiply
+                const unsigned nib = ax == 0 ? (((v & 0x1111u) * 0x1248u) >> 12) & 0xFu : (v & 0xFu);
+                E |= nib << (8 * r);
+            }
+            const int db = bb * 4 - b0, dc = cb * 4 - c0;
+            const unsigned pre = (db >= 0 ? (colmask >> db) : (colmask << (-db))) & 0xFu;
+            E &= pre * 0x01010101u;
+            E = db >= 0 ? (E << db) : (E >> (-db));
+            occ |= dc >= 0 ? ((unsigned long long)E << (8 * dc)) : ((unsigned long long)E >> (-8 * dc));
+        }
+    const int rows = c1 - c0 + 1;
+    if (rows < 8) occ &= (1ull << (8 * rows)) - 1ull;
+    return occ;
 }
 
 __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a) {
@@ -552,7 +589,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
         s.ax = 0;
         if (fabs(s.u[1]) > fabs(s.u[s.ax])) s.ax = 1;
         if (fabs(s.u[2]) > fabs(s.u[s.ax])) s.ax = 2;
-        const int bx = (s.ax + 1) % 3, cx = (s.ax + 2) % 3;
+        const int bx = s.ax == 0 ? 1 : 0, cx = s.ax == 2 ? 1 : 2;
         const double inv_uax = 1.0 / s.u[s.ax];            // |u[ax]| >= 1/sqrt(3): u is a unit vector
         s.sb = s.u[bx] * inv_uax;
         s.sc = s.u[cx] * inv_uax;
@@ -595,7 +632,6 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
     unsigned long long n_cand = 0;
 
     for (int w0 = 0; w0 < total; w0 += kSweepThreads) {
-        if (__syncthreads_or(tid == 0 && sq_count >= kSqFlushAt)) sweep_flush(a, sq, &sq_count, eflags, e0);
         // ---- one item per thread: occupancy mask of its rectangle
         const int w = w0 + tid;
         unsigned long long occ = 0;
@@ -608,7 +644,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
             }
             const int el = lo;
             const SweepEdge& s = es[el];
-            const int ax = s.ax, bx = (ax + 1) % 3, cx = (ax + 2) % 3;
+            const int ax = s.ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
             const int i = s.i_lo + (w - prefix[el]);
             // the part of the axis segment whose ax coordinate lies in the slab inflated by rm
             // (clamped to the segment: slabs past an end see the end point + the rm margin)
@@ -631,13 +667,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                 none |= lo_b > hi_b;
             }
             if (!none) {
-                for (int jc = r0[1]; jc <= r1[1]; ++jc)
-                    for (int jb = r0[0]; jb <= r1[0]; ++jb) {
-                        int vx, vy, vz;
-                        unperm(ax, i, jb, jc, vx, vy, vz);
-                        if (test_bit(m.lv[0], vx, vy, vz))
-                            occ |= 1ull << ((jc - r0[1]) * kRectMax + (jb - r0[0]));
-                    }
+                occ = rect_occupancy(m.lv[0], ax, i, r0[0], r1[0], r0[1], r1[1]);
                 info_a = el | (i << 8);
                 info_b = r0[0] | (r0[1] << 12);
             }
@@ -679,7 +709,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                 int vx, vy, vz, l[3];
                 unperm(ax, i, vb, vc, vx, vy, vz);
                 const int L = find_leaf(m, vx, vy, vz, l[0], l[1], l[2]);
-                const int lb = ax == 0 ? l[1] : (ax == 1 ? l[2] : l[0]), lc = ax == 0 ? l[2] : (ax == 1 ? l[0] : l[1]);
+                const int lb = ax == 0 ? l[1] : l[0], lc = ax == 2 ? l[1] : l[2];
                 // one representative cell per (item, leaf)
                 if (vb == max(b0, lb) && vc == max(c0, lc)) {
                     ++n_cand;
@@ -727,7 +757,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                     if (slot < kSqCap) {
                         sq[slot] = rec;
                     } else {
-                        // shared queue full (a flush happens at the next item batch): straight to the global queue
+                        // shared queue full: straight to the global queue (not filtered by later deep hits)
                         const unsigned g = atomicAdd(a.qctl, 1u);
                         if (g < a.queue_cap) {
                             NarrowRec r;
@@ -745,7 +775,10 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
         }
     }
     sweep_flush(a, sq, &sq_count, eflags, e0);
-    if (a.stats) atomicAdd(&st_cand, n_cand);
+    if (a.stats) {
+        for (int o = 16; o > 0; o >>= 1) n_cand += __shfl_xor_sync(kFull, n_cand, o);
+        if (lane == 0 && n_cand) atomicAdd(&st_cand, n_cand);
+    }
     __syncthreads();
     if (tid < ne) {
         a.gflags[e0 + tid] = eflags[tid];

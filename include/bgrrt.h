@@ -107,6 +107,29 @@ int bgr_knn_merge_dev(const int32_t* d_idx_GxkxQ, const float* d_d2_GxkxQ, int g
                       int64_t nq, int k, int32_t* d_idx_kxQ, float* d_d2_kxQ,
                       void* cuda_stream);
 
+/* Exchange step of the index-range-sharded search over NVLink peer memory (one process per
+ * GPU; no counterpart in the reference, which is single-process).  Every rank creates a window
+ * of 4 regions of max_entries (>= k*Q) 32-bit words, exports it as a CUDA IPC handle
+ * (bgr_peer_handle_bytes() bytes; the caller ships the handles between processes, e.g. with
+ * torch.distributed.all_gather_object) and opens every peer's handle.  Per search: the local
+ * bgr_nns_knn_dev writes into bgr_peer_slab(); bgr_peer_merge_dev then runs ONE kernel that
+ * waits for the peers' slabs, merges this rank's query slice [r*Q/G,(r+1)*Q/G) from all G slabs
+ * by (d2, index) with peer loads and stores the merged k-lists into every peer's result region,
+ * plus a wait kernel; after it (stream order) bgr_peer_result() holds the full k x Q result on
+ * every rank.  All ranks must call bgr_peer_merge_dev the same number of times with the same
+ * nq and k.  Bounded spins: a peer that never arrives sets *error (bgr_peer_status) instead of
+ * hanging the GPU. */
+typedef struct bgr_peer bgr_peer;
+int bgr_peer_handle_bytes(void);
+int bgr_peer_create(int rank, int world, int64_t max_entries, bgr_peer** out);
+int bgr_peer_export(bgr_peer* peer, void* handle_out);
+int bgr_peer_open(bgr_peer* peer, int peer_rank, const void* handle);
+int bgr_peer_slab(bgr_peer* peer, int32_t** d_idx_kxQ, float** d_d2_kxQ);
+int bgr_peer_result(bgr_peer* peer, int32_t** d_idx_kxQ, float** d_d2_kxQ);
+int bgr_peer_merge_dev(bgr_peer* peer, int64_t nq, int k, void* cuda_stream);
+int bgr_peer_status(bgr_peer* peer, void* cuda_stream, int* error);
+int bgr_peer_destroy(bgr_peer* peer);
+
 /* ------------------------------------------------------------------ occupancy map */
 typedef struct bgr_map bgr_map;
 
