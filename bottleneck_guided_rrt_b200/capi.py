@@ -65,6 +65,7 @@ def lib():
     L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_destroy.argtypes = [vp]
     L.bgr_knn_merge_dev.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
+    L.bgr_knn_merge_strided_dev.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, vp]
     L.bgr_peer_handle_bytes.restype = i32
     L.bgr_peer_create.argtypes = [i32, i32, i64, vp]
     L.bgr_peer_export.argtypes = [vp, vp]
@@ -268,10 +269,12 @@ class NNSearchF:
 
 
 def knn_merge_dev(idx_slabs, d2_slabs, idx_out, d2_out, stream=0):
-    """Merge G per-shard (Q,k) top-k slabs (CUDA tensors (G,Q,k)) into one, by (d2, index)."""
+    """Merge G per-shard (Q,k) top-k slabs (CUDA tensors (G,Q,k), each slab contiguous, any
+    stride between slabs) into one, by (d2, index)."""
     g, nq, k = idx_slabs.shape
-    _check(lib().bgr_knn_merge_dev(_ptr(idx_slabs), _ptr(d2_slabs), g, nq, k, _ptr(idx_out), _ptr(d2_out),
-                                   C.c_void_p(stream or 0)))
+    assert idx_slabs.stride(1) == k and idx_slabs.stride(2) == 1 and idx_slabs.stride() == d2_slabs.stride()
+    _check(lib().bgr_knn_merge_strided_dev(_ptr(idx_slabs), _ptr(d2_slabs), g, idx_slabs.stride(0), nq, k,
+                                           _ptr(idx_out), _ptr(d2_out), C.c_void_p(stream or 0)))
     return idx_out, d2_out
 
 

@@ -218,10 +218,11 @@ __global__ void __launch_bounds__(kBruteThreads, 2) knn_brute_kernel(BruteArgs a
     }
 }
 
-// Merge G slabs (each k x Q ascending, padded with idx=-1,d2=+inf) into one: warp per query.
+// Merge G slabs (each k x Q ascending, padded with idx=-1,d2=+inf; slab s starts at entry
+// s*slab_stride of idx_in / d2_in) into one: warp per query.
 __global__ void __launch_bounds__(256) knn_merge_kernel(const int32_t* __restrict__ idx_in,
                                                         const float* __restrict__ d2_in, int g,
-                                                        int64_t nq, int k,
+                                                        int64_t slab_stride, int64_t nq, int k,
                                                         int32_t* __restrict__ idx_out,
                                                         float* __restrict__ d2_out) {
     const int lane = threadIdx.x & 31;
@@ -233,7 +234,7 @@ __global__ void __launch_bounds__(256) knn_merge_kernel(const int32_t* __restric
     for (int s = 0; s < g; ++s) {
         uint32_t bd = kKeyMax, bi = kKeyMax;
         if (lane < k) {
-            const int64_t o = ((int64_t)s * nq + qi) * k + lane;
+            const int64_t o = (int64_t)s * slab_stride + qi * k + lane;
             const int32_t ii = idx_in[o];
             if (ii >= 0) {
                 bd = __float_as_uint(d2_in[o]);

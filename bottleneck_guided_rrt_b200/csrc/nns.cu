@@ -146,7 +146,7 @@ int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flag
     }
     if (chunks > 1) {
         knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
-                                                                         nq, k, d_idx, d_d2);
+                                                                         nq * k, nq, k, d_idx, d_d2);
         BGR_LAUNCH_CHECK();
     }
     return BGR_OK;
@@ -383,13 +383,19 @@ int bgr_nns_destroy(bgr_nns* h) {
     return BGR_OK;
 }
 
-int bgr_knn_merge_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int64_t nq, int k,
-                      int32_t* d_idx, float* d_d2, void* stream) {
+int bgr_knn_merge_strided_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int64_t slab_stride,
+                              int64_t nq, int k, int32_t* d_idx, float* d_d2, void* stream) {
     BGR_ARG(g >= 1 && nq >= 0 && k >= 1 && k <= 32, "bad merge arguments (k<=32)");
+    BGR_ARG(slab_stride >= nq * k, "slab stride %lld < k*Q", (long long)slab_stride);
     if (nq == 0) return BGR_OK;
-    knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, (cudaStream_t)stream>>>(d_idx_in, d_d2_in, g, nq, k, d_idx, d_d2);
+    knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, (cudaStream_t)stream>>>(d_idx_in, d_d2_in, g, slab_stride, nq, k, d_idx, d_d2);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
+}
+
+int bgr_knn_merge_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int64_t nq, int k,
+                      int32_t* d_idx, float* d_d2, void* stream) {
+    return bgr_knn_merge_strided_dev(d_idx_in, d_d2_in, g, nq * (int64_t)k, nq, k, d_idx, d_d2, stream);
 }
 
 }  // extern "C"

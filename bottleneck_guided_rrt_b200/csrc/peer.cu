@@ -97,18 +97,29 @@ __global__ void __launch_bounds__(256) peer_merge_kernel(PeerView v, int64_t nq,
             WarpList L;
             L.init(kKeyMax);
             L.i = kKeyMax;
-            for (int s = 0; s < v.world; ++s) {
-                const int p = (v.rank + s) % v.world;       // start at home, stagger the remote reads
-                uint32_t bd = kKeyMax, bi = kKeyMax;
-                if (lane < k) {
-                    const int64_t o = qi * k + lane;
-                    const int32_t ii = __ldcg(region_i32(v.win[p], v.cap, 0) + o);
-                    if (ii >= 0) {
-                        bd = (uint32_t)__ldcg(region_i32(v.win[p], v.cap, 1) + o);
-                        bi = (uint32_t)ii;
+            const int64_t o = qi * k + lane;
+            // remote loads are latency bound (NVLink round trip): issue the loads of 4 slabs
+            // (index and d2 independently) before merging any of them
+            for (int s0 = 0; s0 < v.world; s0 += 4) {
+                int32_t ii[4];
+                uint32_t dd[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    ii[u] = -1;
+                    dd[u] = kKeyMax;
+                    if (s0 + u < v.world && lane < k) {
+                        const int p = (v.rank + s0 + u) % v.world;   // start at home, stagger the remote reads
+                        ii[u] = __ldcg(region_i32(v.win[p], v.cap, 0) + o);
+                        dd[u] = (uint32_t)__ldcg(region_i32(v.win[p], v.cap, 1) + o);
                     }
                 }
-                L.merge_sorted(bd, bi, lane);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    if (s0 + u < v.world) {                          // warp-uniform
+                        const bool valid = ii[u] >= 0;
+                        L.merge_sorted(valid ? dd[u] : kKeyMax, valid ? (uint32_t)ii[u] : kKeyMax, lane);
+                    }
+                }
             }
             if (lane < k) {
                 const bool empty = (L.d == kKeyMax);
@@ -235,7 +246,9 @@ int bgr_peer_merge_dev(bgr_peer* h, int64_t nq, int k, void* stream) {
     v.cap = h->cap;
     const unsigned epoch = ++h->epoch;
     const int64_t slice = div_up(nq > 0 ? nq : 1, h->world);
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(2LL * num_sms(), div_up(slice, 8)));
+    // many CTAs in flight hide the NVLink latency; every CTA signals and polls on its own, so the
+    // grid need not be co-resident
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(32LL * num_sms(), div_up(slice, 8)));
     cudaStream_t st = (cudaStream_t)stream;
     peer_merge_kernel<<<grid, 256, 0, st>>>(v, nq, k, epoch);
     BGR_LAUNCH_CHECK();

@@ -17,14 +17,32 @@ def shard_range(n, rank, world):
 
 
 class ShardedNNSearch:
-    def __init__(self, local_points, index_base, group=None, stream=None, nns_factory=None, merge=None):
+    def __init__(self, local_points, index_base, group=None, stream=None, nns_factory=None, merge=None,
+                 exchange="nccl", max_entries=None):
         """local_points: this rank's shard ((n_local,3) float32 host array or CUDA tensor).
-        nns_factory / merge are injectable so the host logic can be tested on CPU (gloo)."""
+        nns_factory / merge are injectable so the host logic can be tested on CPU (gloo).
+        exchange: "nccl" = one all_gather_into_tensor of the packed (idx,d2) slabs + the merge
+        kernel; "peer" = bgr_peer_* (CUDA IPC windows, ONE merge kernel doing peer loads of this
+        rank's query slice and peer stores of the merged lists; needs max_entries >= k*Q)."""
         import torch.distributed as dist
         self.dist = dist
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.exchange = exchange if self.world > 1 else "none"
+        self.stream = stream or 0
+        self.peer = None
+        if self.exchange == "peer":
+            from .capi import PeerExchange
+
+            def ship(mine):
+                allh = [None] * self.world
+                dist.all_gather_object(allh, mine, group=group)
+                return allh
+
+            assert max_entries, "exchange='peer' needs max_entries (>= k*Q)"
+            self.peer = PeerExchange(self.rank, self.world, int(max_entries), ship)
+            dist.barrier(group=group)      # every window is mapped before anyone signals into it
         if nns_factory is None:
             from .capi import NNSearchF
             nns_factory = lambda pts: NNSearchF.createKDTreeLinearHeap(pts, stream=stream)  # noqa: E731
@@ -39,21 +57,28 @@ class ShardedNNSearch:
     def knn(self, query, k, optionFlags=0, maxRadius=float("inf")):
         """query: replicated (Q,3) CUDA tensor.  Returns merged (idx, d2) on every rank."""
         import torch
-        idx, d2, _ = self.nns.knn(query, k, 0.0, optionFlags, maxRadius)
+        nq = query.shape[0]
+        if self.exchange == "peer":
+            pi, pd = self.peer.slab_ptrs()
+            self.nns.knn(query, k, 0.0, optionFlags, maxRadius, indices=pi, dists2=pd)
+            self.peer.merge(nq, k, self.stream)
+            return self.peer.result(nq, k)
         if self.world == 1:
+            idx, d2, _ = self.nns.knn(query, k, 0.0, optionFlags, maxRadius)
             return idx, d2
-        nq = idx.shape[0]
-        key = (nq, k, idx.device)
+        key = (nq, k, query.device)
         if self._slabs is None or self._slabs[0] != key:
+            # packed slab: [0] = indices, [1] = d2 bits, so ONE all-gather moves both
             self._slabs = (key,
-                           torch.empty((self.world, nq, k), dtype=idx.dtype, device=idx.device),
-                           torch.empty((self.world, nq, k), dtype=d2.dtype, device=d2.device),
-                           torch.empty_like(idx), torch.empty_like(d2))
-        _, si, sd, oi, od = self._slabs
-        # concatenated-rows form (G*Q, k): accepted by both NCCL and gloo
-        self.dist.all_gather_into_tensor(si.view(self.world * nq, k), idx.contiguous(), group=self.group)
-        self.dist.all_gather_into_tensor(sd.view(self.world * nq, k), d2.contiguous(), group=self.group)
-        self.merge(si, sd, oi, od)
+                           torch.empty((2, nq, k), dtype=torch.int32, device=query.device),
+                           torch.empty((self.world, 2, nq, k), dtype=torch.int32, device=query.device),
+                           torch.empty((nq, k), dtype=torch.int32, device=query.device),
+                           torch.empty((nq, k), dtype=torch.float32, device=query.device))
+        _, loc, slabs, oi, od = self._slabs
+        self.nns.knn(query, k, 0.0, optionFlags, maxRadius, indices=loc[0], dists2=loc[1].view(torch.float32))
+        # concatenated-rows form (G*2*Q, k): accepted by both NCCL and gloo
+        self.dist.all_gather_into_tensor(slabs.view(self.world * 2 * nq, k), loc.view(2 * nq, k), group=self.group)
+        self.merge(slabs[:, 0], slabs[:, 1].view(torch.float32), oi, od)
         return oi, od
 
 

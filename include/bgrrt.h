@@ -106,6 +106,10 @@ int bgr_nns_destroy(bgr_nns* nns);
 int bgr_knn_merge_dev(const int32_t* d_idx_GxkxQ, const float* d_d2_GxkxQ, int g,
                       int64_t nq, int k, int32_t* d_idx_kxQ, float* d_d2_kxQ,
                       void* cuda_stream);
+/* same, slab s starting at entry s*slab_stride of both inputs (packed all-gather buffers) */
+int bgr_knn_merge_strided_dev(const int32_t* d_idx_in, const float* d_d2_in, int g,
+                              int64_t slab_stride, int64_t nq, int k, int32_t* d_idx_kxQ,
+                              float* d_d2_kxQ, void* cuda_stream);
 
 /* Exchange step of the index-range-sharded search over NVLink peer memory (one process per
  * GPU; no counterpart in the reference, which is single-process).  Every rank creates a window

@@ -39,11 +39,15 @@ def _worker(rank, world, port, n, nq, k, flags, q_out):
             def set_index_base(self, b):
                 self.base = b
 
-            def knn(self, query, kk, eps, fl, max_radius):
+            def knn(self, query, kk, eps, fl, max_radius, indices=None, dists2=None):
                 kq = min(kk, len(self.p) - (0 if fl & 1 else 0))
                 i, d = O.knn_brute(self.p, query.numpy(), kk, fl | 0, max_radius) if len(self.p) > kk else (None, None)
                 assert i is not None and kq == kk
                 i = np.where(i >= 0, i + self.base, -1).astype(np.int32)
+                if indices is not None:          # the sharded search hands in its packed slab
+                    indices.copy_(torch.from_numpy(i))
+                    dists2.copy_(torch.from_numpy(d))
+                    return indices, dists2, 0
                 return torch.from_numpy(i), torch.from_numpy(d), 0
 
         def merge(si, sd, oi, od):
