@@ -79,11 +79,39 @@ __device__ bool wait_all(const unsigned* flags, int world, unsigned epoch, unsig
     return true;
 }
 
-__global__ void __launch_bounds__(256) peer_merge_kernel(PeerView v, int64_t nq, int k, unsigned epoch) {
+
+// flat copy of n 32-bit words, 16 bytes per lane when both sides allow it (all threads of the CTA)
+__device__ __forceinline__ void cta_copy_in(int32_t* __restrict__ dst, const int32_t* __restrict__ src, int n, bool vec) {
+    if (vec) {
+        const int4* s4 = reinterpret_cast<const int4*>(src);
+        int4* d4 = reinterpret_cast<int4*>(dst);
+        for (int e = threadIdx.x; e < (n >> 2); e += blockDim.x) d4[e] = __ldcg(s4 + e);
+        for (int e = (n & ~3) + threadIdx.x; e < n; e += blockDim.x) dst[e] = __ldcg(src + e);
+    } else {
+        for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = __ldcg(src + e);
+    }
+}
+__device__ __forceinline__ void cta_copy_out(int32_t* __restrict__ dst, const int32_t* __restrict__ src, int n, bool vec) {
+    if (vec) {
+        const int4* s4 = reinterpret_cast<const int4*>(src);
+        int4* d4 = reinterpret_cast<int4*>(dst);
+        for (int e = threadIdx.x; e < (n >> 2); e += blockDim.x) d4[e] = s4[e];
+        for (int e = (n & ~3) + threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
+    } else {
+        for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
+    }
+}
+
+// Persistent grid (all CTAs resident).  Per chunk of `chunk` queries of this rank's slice:
+// stage the chunk of every slab in shared memory with wide loads — all of a thread's loads, to
+// all peers, are in flight together, which is what hides the NVLink round trip — merge from
+// shared memory (warp per query), then store the merged chunk to every peer with wide stores.
+__global__ void __launch_bounds__(256) peer_merge_kernel(PeerView v, int64_t nq, int k, unsigned epoch, int chunk) {
+    extern __shared__ __align__(16) int32_t stage[];   // [world][2][chunk*k]; chunk = queries staged per CTA iteration
     __shared__ int ok_s;
-    const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
     PeerFlags* mine = reinterpret_cast<PeerFlags*>(v.win[v.rank]);
-    if (threadIdx.x < v.world) {
+    if (blockIdx.x == 0 && threadIdx.x < v.world) {
         // the local search finished before this kernel started (stream order): publish the slab
         __threadfence_system();
         st_release_sys(&reinterpret_cast<PeerFlags*>(v.win[threadIdx.x])->ready[v.rank], epoch);
@@ -92,45 +120,46 @@ __global__ void __launch_bounds__(256) peer_merge_kernel(PeerView v, int64_t nq,
     __syncthreads();
     if (ok_s) {
         const int64_t q_lo = nq * v.rank / v.world, q_hi = nq * (v.rank + 1) / v.world;
-        for (int64_t qi = q_lo + (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); qi < q_hi;
-             qi += (int64_t)gridDim.x * warps) {
-            WarpList L;
-            L.init(kKeyMax);
-            L.i = kKeyMax;
-            const int64_t o = qi * k + lane;
-            // remote loads are latency bound (NVLink round trip): issue the loads of 4 slabs
-            // (index and d2 independently) before merging any of them
-            for (int s0 = 0; s0 < v.world; s0 += 4) {
-                int32_t ii[4];
-                uint32_t dd[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    ii[u] = -1;
-                    dd[u] = kKeyMax;
-                    if (s0 + u < v.world && lane < k) {
-                        const int p = (v.rank + s0 + u) % v.world;   // start at home, stagger the remote reads
-                        ii[u] = __ldcg(region_i32(v.win[p], v.cap, 0) + o);
-                        dd[u] = (uint32_t)__ldcg(region_i32(v.win[p], v.cap, 1) + o);
-                    }
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (s0 + u < v.world) {                          // warp-uniform
-                        const bool valid = ii[u] >= 0;
-                        L.merge_sorted(valid ? dd[u] : kKeyMax, valid ? (uint32_t)ii[u] : kKeyMax, lane);
-                    }
-                }
+        const int per = chunk * k;
+        for (int64_t q0 = q_lo + (int64_t)blockIdx.x * chunk; q0 < q_hi; q0 += (int64_t)gridDim.x * chunk) {
+            const int nqc = (int)min((int64_t)chunk, q_hi - q0), n = nqc * k;
+            const int64_t o = q0 * k;
+            const bool vec = (o & 3) == 0;
+            for (int s = 0; s < v.world; ++s) {
+                const int p = (v.rank + s) % v.world;               // slot 0 = home, remote reads staggered
+                cta_copy_in(stage + (2 * s) * per, region_i32(v.win[p], v.cap, 0) + o, n, vec);
+                cta_copy_in(stage + (2 * s + 1) * per, region_i32(v.win[p], v.cap, 1) + o, n, vec);
             }
-            if (lane < k) {
-                const bool empty = (L.d == kKeyMax);
-                const int32_t oi = empty ? -1 : (int32_t)L.i;
-                const int32_t od = (int32_t)(empty ? kInfBits : L.d);
+            __syncthreads();
+            for (int ql = warp; ql < nqc; ql += warps) {
+                WarpList L;
+                L.init(kKeyMax);
+                L.i = kKeyMax;
                 for (int s = 0; s < v.world; ++s) {
-                    const int p = (v.rank + s) % v.world;
-                    region_i32(v.win[p], v.cap, 2)[qi * k + lane] = oi;
-                    region_i32(v.win[p], v.cap, 3)[qi * k + lane] = od;
+                    uint32_t bd = kKeyMax, bi = kKeyMax;
+                    if (lane < k) {
+                        const int32_t ii = stage[(2 * s) * per + ql * k + lane];
+                        if (ii >= 0) {
+                            bd = (uint32_t)stage[(2 * s + 1) * per + ql * k + lane];
+                            bi = (uint32_t)ii;
+                        }
+                    }
+                    L.merge_sorted(bd, bi, lane);
+                }
+                __syncwarp();
+                if (lane < k) {                                     // the warp's own entries of slot 0
+                    const bool empty = (L.d == kKeyMax);
+                    stage[ql * k + lane] = empty ? -1 : (int32_t)L.i;
+                    stage[per + ql * k + lane] = (int32_t)(empty ? kInfBits : L.d);
                 }
             }
+            __syncthreads();
+            for (int s = 0; s < v.world; ++s) {
+                const int p = (v.rank + s) % v.world;
+                cta_copy_out(region_i32(v.win[p], v.cap, 2) + o, stage, n, vec);
+                cta_copy_out(region_i32(v.win[p], v.cap, 3) + o, stage + per, n, vec);
+            }
+            __syncthreads();
         }
     }
     // last CTA: all slices this rank owes are written -> tell every peer
@@ -246,11 +275,19 @@ int bgr_peer_merge_dev(bgr_peer* h, int64_t nq, int k, void* stream) {
     v.cap = h->cap;
     const unsigned epoch = ++h->epoch;
     const int64_t slice = div_up(nq > 0 ? nq : 1, h->world);
-    // many CTAs in flight hide the NVLink latency; every CTA signals and polls on its own, so the
-    // grid need not be co-resident
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(32LL * num_sms(), div_up(slice, 8)));
+    int chunk = 64;                                  // more bytes in flight per CTA hide the NVLink round trip
+    while (chunk > 8 && (size_t)h->world * 2 * chunk * k * sizeof(int32_t) > 64 * 1024) chunk >>= 1;
+    const size_t smem = (size_t)h->world * 2 * chunk * k * sizeof(int32_t);
+    static size_t smem_set = 0;
+    if (smem > 48 * 1024 && smem > smem_set) {
+        BGR_CUDA(cudaFuncSetAttribute(peer_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set = smem;
+    }
+    // persistent grid: resident CTAs only (every CTA polls the ready flags before it works)
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (200 * 1024) / std::max<size_t>(smem, 1)));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)per_sm * num_sms(), div_up(slice, chunk)));
     cudaStream_t st = (cudaStream_t)stream;
-    peer_merge_kernel<<<grid, 256, 0, st>>>(v, nq, k, epoch);
+    peer_merge_kernel<<<grid, 256, smem, st>>>(v, nq, k, epoch, chunk);
     BGR_LAUNCH_CHECK();
     peer_wait_kernel<<<1, 32, 0, st>>>(v, epoch);
     BGR_LAUNCH_CHECK();

@@ -62,7 +62,9 @@ class ShardedNNSearch:
             pi, pd = self.peer.slab_ptrs()
             self.nns.knn(query, k, 0.0, optionFlags, maxRadius, indices=pi, dists2=pd)
             self.peer.merge(nq, k, self.stream)
-            return self.peer.result(nq, k)
+            if self._slabs is None or self._slabs[0] != (nq, k):
+                self._slabs = ((nq, k),) + tuple(self.peer.result(nq, k))    # views of the window, made once
+            return self._slabs[1], self._slabs[2]
         if self.world == 1:
             idx, d2, _ = self.nns.knn(query, k, 0.0, optionFlags, maxRadius)
             return idx, d2
