@@ -22,6 +22,8 @@ from .capi import (  # noqa: F401
     lib,
     library_path,
     knn_merge_dev,
+    smoothen_plan,
+    PeerExchange,
     Planner,
     PlannerParams,
     PLAN_EDGE_CHECK,

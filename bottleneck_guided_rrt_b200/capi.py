@@ -87,6 +87,10 @@ def lib():
     L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_last_stats.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
+    L.bgr_map_prune_path.argtypes = [vp, vp, i64, f64, i32, vp, vp, vp]
+    L.bgr_path_smoothen.argtypes = [vp, i64, vp, vp]
+    L.bgr_map_clearance.argtypes = [vp, vp, i64, f64, vp]
+    L.bgr_map_find_labels.argtypes = [vp, vp, i64, f64, i32, vp, vp, vp, vp]
     L.bgr_planner_create.argtypes = [vp, vp, vp, i64, vp, i32, vp]
     L.bgr_planner_set_stream.argtypes = [vp, vp]
     L.bgr_planner_step.argtypes = [vp, vp, vp]
@@ -424,6 +428,32 @@ class OccupancyMap:
         _check(lib().bgr_map_last_stats(self._h, _ptr(s)))
         return {"work_items": int(s[0]), "candidates": int(s[1]), "narrow_tests": int(s[2]), "iter_cap": int(s[3])}
 
+    # ---- path post-processing (PrunePlan MS:562-643, find_labels MS:943-1011)
+    def prune_path(self, path, radius=0.03, shape=SHAPE_CYLINDER):
+        """returns (kept waypoint indices int32, number of consulted in-band edges)"""
+        p = _host_f32(path)
+        keep = np.empty(p.shape[0], dtype=np.int32)
+        nk, nb = C.c_int64(p.shape[0]), C.c_int64(0)
+        _check(lib().bgr_map_prune_path(self._h, _ptr(p), p.shape[0], radius, shape, _ptr(keep), C.byref(nk), C.byref(nb)))
+        return keep[:nk.value].copy(), nb.value
+
+    def clearance(self, pts, radius=0.1):
+        p = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 3)
+        d = np.empty(p.shape[0], dtype=np.float64)
+        _check(lib().bgr_map_clearance(self._h, _ptr(p), p.shape[0], radius, _ptr(d)))
+        return d
+
+    def find_labels(self, final_path, radius=0.1, n_labels=3):
+        """returns (indices into final_path[1:-1], labels (3*n_labels,) float32, clearances float32, ties)"""
+        p = np.ascontiguousarray(final_path, dtype=np.float64).reshape(-1, 3)
+        idx = np.empty(n_labels, dtype=np.int32)
+        lab = np.empty(3 * n_labels, dtype=np.float32)
+        clr = np.empty(max(p.shape[0] - 2, 0), dtype=np.float32)
+        ties = C.c_int(0)
+        _check(lib().bgr_map_find_labels(self._h, _ptr(p), p.shape[0], radius, n_labels, _ptr(idx), _ptr(lab), _ptr(clr),
+                                         C.byref(ties)))
+        return idx, lab, clr, ties.value
+
     # reference-shaped single queries (True = in collision)
     def isStateValid(self, point):
         hit, _ = self.collide_spheres(np.asarray(point, dtype=np.float32).reshape(1, 3), 0.1, want_band=False)
@@ -434,6 +464,16 @@ class OccupancyMap:
                                     np.asarray(point2, dtype=np.float32).reshape(1, 3), 0.03, SHAPE_CYLINDER,
                                     want_band=False)
         return bool(hit[0])
+
+
+def smoothen_plan(path):
+    """SmoothenPlan (MS:645-799): (P,3) float64 waypoints -> (11,3) float64 samples."""
+    p = np.ascontiguousarray(path, dtype=np.float64).reshape(-1, 3)
+    n = C.c_int64(0)
+    _check(lib().bgr_path_smoothen(_ptr(p), p.shape[0], None, C.byref(n)))
+    out = np.empty((n.value, 3), dtype=np.float64)
+    _check(lib().bgr_path_smoothen(_ptr(p), p.shape[0], _ptr(out), C.byref(n)))
+    return out
 
 
 class Planner:

@@ -119,7 +119,7 @@ __device__ __forceinline__ D3 mink_support(const ShapeObj& o, const D3& bc, doub
 }
 
 // returns 1 = intersect, 0 = separate; *capped set when the iteration cap fired
-__device__ __noinline__ int mpr_shape_box(const ShapeObj& o, const D3& bc, double e, double tol, int* capped) {
+static __device__ __noinline__ int mpr_shape_box(const ShapeObj& o, const D3& bc, double e, double tol, int* capped) {
     int it = 0;
     D3 v0 = d3_sub(o.pos, bc), v1, v2, v3, v4, dir, va, vb;
     if (d3_eq0(v0)) v0.x += kCcdEps * 10.0;

@@ -174,6 +174,34 @@ int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* 
 int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
 int bgr_map_destroy(bgr_map* map);
 
+/* ------------------------------------------------------------------ path post-processing */
+/* Replaces PrunePlan(rrt_path) (MS:562-643): greedy shortcutting from the start — from the
+ * current anchor take the FARTHEST waypoint whose isLineValid edge is free.  All P(P-1)/2
+ * anchor-waypoint edges are evaluated in one collide_edges launch; the walk then reads the
+ * answers.  path is P x 3 host floats; keep receives the kept waypoint indices (capacity
+ * *n_keep >= P in, count out); n_band (may be NULL) counts consulted edges whose result is
+ * tolerance-determined.  Reproduced quirk: the walk ends when the last kept waypoint has the
+ * goal's x coordinate (MS:579).  Where the reference would loop forever (no free successor)
+ * this returns BGR_ERR_STATE. */
+int bgr_map_prune_path(bgr_map* map, const float* path_3xP, int64_t p, double radius, int shape,
+                       int32_t* keep, int64_t* n_keep, int64_t* n_band);
+/* Replaces SmoothenPlan(rrt_path) (MS:645-799), arithmetic types as in the reference: P == 3
+ * quadratic Bezier (float t), P > 3 cubic Bezier over the FIRST FOUR waypoints (double t),
+ * P == 2 straight line resampled; 11 samples.  Host arithmetic (33 numbers).  out may be NULL
+ * to query the sample count. */
+int bgr_path_smoothen(const double* path_3xP, int64_t p, double* out_3xS, int64_t* n_out);
+/* Obstacle clearance of find_labels (MS:956-975) / distance_from_obstacle (RD:890-917) for a
+ * batch of points: min over all leaf boxes of fcl::distance(Sphere(radius), Box) in closed
+ * form, -1 when the sphere touches or penetrates a leaf, 1000 when the map is empty (MS:962). */
+int bgr_map_clearance(bgr_map* map, const double* pts_3xM, int64_t m, double radius, double* dist);
+/* Replaces find_labels(final_path) (MS:943-1011) up to the file write: drops the start and the
+ * goal waypoint, takes the n_labels interior waypoints of smallest float clearance (ties by
+ * index; n_ties reports float-equal neighbours in the selection, where std::sort's order is
+ * unspecified) -> idx (into the trimmed path), labels (n_labels x 3 floats), clearance (P-2
+ * floats, may be NULL). */
+int bgr_map_find_labels(bgr_map* map, const double* path_3xP, int64_t p, double radius, int n_labels,
+                        int32_t* idx, float* labels_3xL, float* clearance, int* n_ties);
+
 /* ------------------------------------------------------------------ batched planner step */
 /* The extension loop of rrt_star_milestones.cpp main() (MS:1160-1406; rrt_star.cpp
  * RS:1140-1300 for the 10 % goal-bias sampler) for B candidates per launch, evaluated against
