@@ -23,6 +23,10 @@ from .capi import (  # noqa: F401
     library_path,
     knn_merge_dev,
     smoothen_plan,
+    octree_to_boxes,
+    OCTREE_FULL_DATA,
+    OCTREE_BINARY_DATA,
+    OCTREE_FILE,
     PeerExchange,
     Planner,
     PlannerParams,

@@ -87,6 +87,8 @@ def lib():
     L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_last_stats.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
+    L.bgr_map_refresh_boxes.argtypes = [vp, vp, i64, vp, vp]
+    L.bgr_octree_to_boxes.argtypes = [vp, i64, i32, f64, f64, vp, vp, vp, vp, vp]
     L.bgr_map_prune_path.argtypes = [vp, vp, i64, f64, i32, vp, vp, vp]
     L.bgr_path_smoothen.argtypes = [vp, i64, vp, vp]
     L.bgr_map_clearance.argtypes = [vp, vp, i64, f64, vp]
@@ -374,6 +376,26 @@ class OccupancyMap:
         r = np.ascontiguousarray(remove if remove is not None else np.zeros((0, 6)), dtype=np.float64).reshape(-1, 6)
         _check(lib().bgr_map_update_boxes(self._h, _ptr(a), a.shape[0], _ptr(r), r.shape[0]))
 
+    def refresh_boxes(self, boxes):
+        """map refresh: diff against the current leaf list; returns (n_added, n_removed)"""
+        b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 6)
+        a, r = C.c_int64(0), C.c_int64(0)
+        _check(lib().bgr_map_refresh_boxes(self._h, _ptr(b), b.shape[0], C.byref(a), C.byref(r)))
+        return a.value, r.value
+
+    @classmethod
+    def from_octomap(cls, data, fmt=2, res=0.0, occ_threshold=0.5, stream=None):
+        """OccupancyMap over the bounding box of a serialised Octomap's occupied leaves
+        (origin snapped down to a multiple of 32 cells from the key origin).  Returns (map, boxes)."""
+        boxes, res, lo, hi = octree_to_boxes(data, fmt, res, occ_threshold)
+        blk = 32 * res
+        lo_c = np.floor(np.asarray(lo) / blk + 1e-9).astype(np.int64) * 32
+        hi_c = np.ceil(np.asarray(hi) / res - 1e-9).astype(np.int64)
+        dims = np.maximum(hi_c - lo_c, 1)
+        m = cls(res, lo_c * res, dims, stream=stream)
+        m.set_boxes(boxes)
+        return m, boxes
+
     def occupied_cells(self):
         c = C.c_int64(0)
         _check(lib().bgr_map_occupied_cells(self._h, C.byref(c)))
@@ -464,6 +486,20 @@ class OccupancyMap:
                                     np.asarray(point2, dtype=np.float32).reshape(1, 3), 0.03, SHAPE_CYLINDER,
                                     want_band=False)
         return bool(hit[0])
+
+
+OCTREE_FULL_DATA, OCTREE_BINARY_DATA, OCTREE_FILE = 0, 1, 2
+
+
+def octree_to_boxes(data, fmt=OCTREE_FILE, res=0.0, occ_threshold=0.5):
+    """bgr_octree_to_boxes: serialised Octomap (bytes) -> (boxes (B,6) float64, res, bbox_min, bbox_max)"""
+    buf = bytes(data)
+    nb, r = C.c_int64(0), C.c_double(0.0)
+    lo, hi = np.zeros(3), np.zeros(3)
+    _check(lib().bgr_octree_to_boxes(buf, len(buf), fmt, res, occ_threshold, None, C.byref(nb), C.byref(r), _ptr(lo), _ptr(hi)))
+    boxes = np.empty((nb.value, 6), dtype=np.float64)
+    _check(lib().bgr_octree_to_boxes(buf, len(buf), fmt, res, occ_threshold, _ptr(boxes), C.byref(nb), C.byref(r), _ptr(lo), _ptr(hi)))
+    return boxes, r.value, lo, hi
 
 
 def smoothen_plan(path):

@@ -19,8 +19,10 @@
 // being walked serially per edge (Amanatides-Woo's tMax stepping is inherently sequential).
 // Occupied candidate cells are classified by two closed-form ball tests (deep hit / clear
 // miss, margin 1e-5 m >> MPR tolerance); only ambiguous ones run the exact MPR narrow phase.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <iterator>
 #include <vector>
 #include "mapview.cuh"
 
@@ -822,6 +824,8 @@ struct bgr_map {
     DevBuf<unsigned> eflags, qctl;
     DevBuf<NarrowRec> queue;
     uint64_t last_stats[4] = {0, 0, 0, 0};
+    std::vector<uint64_t> leaf_keys;   // sorted keys (level, z, y, x) of the leaves set through set/refresh_boxes
+    bool keys_valid = false;           // false after update_boxes (the caller manages the diff itself)
 
     MapView view() const {
         MapView v;
@@ -880,6 +884,19 @@ int boxes_to_recs(const bgr_map* h, const double* boxes, int64_t nb, std::vector
         }
     }
     return BGR_OK;
+}
+
+inline uint64_t leaf_key(const LeafRec& r) {
+    return ((uint64_t)r.level << 48) | ((uint64_t)r.z << 32) | ((uint64_t)r.y << 16) | (uint64_t)r.x;
+}
+inline LeafRec key_leaf(uint64_t k) {
+    return {(int32_t)(k & 0xFFFF), (int32_t)((k >> 16) & 0xFFFF), (int32_t)((k >> 32) & 0xFFFF), (int32_t)(k >> 48)};
+}
+void keys_of(const std::vector<LeafRec>& recs, std::vector<uint64_t>& keys) {
+    keys.resize(recs.size());
+    for (size_t i = 0; i < recs.size(); ++i) keys[i] = leaf_key(recs[i]);
+    std::sort(keys.begin(), keys.end());
+    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
 }
 
 int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
@@ -947,7 +964,42 @@ int bgr_map_set_boxes(bgr_map* h, const double* boxes, int64_t nb) {
         h->level_count[L] = counts[L];
     }
     refresh_mask(h);
+    keys_of(recs, h->leaf_keys);
+    h->keys_valid = true;
     return raster(h, recs, 1);
+}
+
+// Map refresh (the octomap server republishes the whole tree; abb_sense.cpp:447-452 resets it
+// every 4 frames): diff the new leaf list against the one currently rasterised and touch only
+// the leaves that changed.  Falls back to a full set_boxes when the current list is unknown.
+int bgr_map_refresh_boxes(bgr_map* h, const double* boxes, int64_t nb, int64_t* n_added, int64_t* n_removed) {
+    BGR_ARG(h != nullptr && nb >= 0 && (nb == 0 || boxes), "bad refresh_boxes arguments");
+    if (n_added) *n_added = 0;
+    if (n_removed) *n_removed = 0;
+    if (!h->keys_valid) {
+        BGR_CHECK(bgr_map_set_boxes(h, boxes, nb));
+        if (n_added) *n_added = (int64_t)h->leaf_keys.size();
+        return BGR_OK;
+    }
+    std::vector<LeafRec> recs;
+    int64_t counts[kMaxLevel + 1] = {0};
+    BGR_CHECK(boxes_to_recs(h, boxes, nb, recs, counts));
+    std::vector<uint64_t> keys, add_k, rem_k;
+    keys_of(recs, keys);
+    std::set_difference(keys.begin(), keys.end(), h->leaf_keys.begin(), h->leaf_keys.end(), std::back_inserter(add_k));
+    std::set_difference(h->leaf_keys.begin(), h->leaf_keys.end(), keys.begin(), keys.end(), std::back_inserter(rem_k));
+    std::vector<LeafRec> add_r(add_k.size()), rem_r(rem_k.size());
+    for (size_t i = 0; i < add_k.size(); ++i) add_r[i] = key_leaf(add_k[i]);
+    for (size_t i = 0; i < rem_k.size(); ++i) rem_r[i] = key_leaf(rem_k[i]);
+    for (const LeafRec& r : rem_r) h->level_count[r.level] = std::max<int64_t>(0, h->level_count[r.level] - 1);
+    for (const LeafRec& r : add_r) h->level_count[r.level] += 1;
+    BGR_CHECK(raster(h, rem_r, 0));     // removals first: a leaf split into children clears, then its children set
+    BGR_CHECK(raster(h, add_r, 1));
+    refresh_mask(h);
+    h->leaf_keys.swap(keys);
+    if (n_added) *n_added = (int64_t)add_k.size();
+    if (n_removed) *n_removed = (int64_t)rem_k.size();
+    return BGR_OK;
 }
 
 int bgr_map_update_boxes(bgr_map* h, const double* add, int64_t n_add, const double* rem, int64_t n_rem) {
@@ -966,6 +1018,7 @@ int bgr_map_update_boxes(bgr_map* h, const double* add, int64_t n_add, const dou
         BGR_CHECK(raster(h, recs, 1));
     }
     refresh_mask(h);
+    h->keys_valid = false;
     return BGR_OK;
 }
 

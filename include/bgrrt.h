@@ -150,6 +150,10 @@ int bgr_map_set_boxes(bgr_map* map, const double* boxes_Bx6, int64_t nb);
 /* incremental refresh: remove then add leaf boxes (same layout) */
 int bgr_map_update_boxes(bgr_map* map, const double* add_Bx6, int64_t n_add,
                          const double* remove_Bx6, int64_t n_remove);
+/* map refresh: the new complete leaf list is diffed against the list set by the last
+ * set_boxes / refresh_boxes and only the changed leaves are rasterised (counts returned) */
+int bgr_map_refresh_boxes(bgr_map* map, const double* boxes_Bx6, int64_t nb, int64_t* n_added,
+                          int64_t* n_removed);
 int bgr_map_occupied_cells(bgr_map* map, int64_t* cells);
 /* copy the occupancy bitmap (one bit per finest cell, 4x4x4 bricks) to host; bytes may be
  * queried with out==NULL */
@@ -173,6 +177,25 @@ int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* 
  * candidate voxels, [2] exact narrow-phase tests, [3] narrow-phase iteration-cap events */
 int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
 int bgr_map_destroy(bgr_map* map);
+
+/* ------------------------------------------------------------------ OcTree ingestion */
+/* Replaces octomap_msgs::fullMsgToMap + fcl::OcTree::toBoxes (MS:279,291): a serialised Octomap
+ * -> the toBoxes rows {x,y,z,size,occupancy,threshold} of its occupied leaves (occupancy >=
+ * occ_threshold, 0.5 in the reference), in leaf-iterator order.  Formats:
+ *   BGR_OCTREE_FULL_DATA    octomap_msgs/Octomap.data with binary=false = the data section of an
+ *                           .ot file (what the reference receives); res from the message
+ *   BGR_OCTREE_BINARY_DATA  Octomap.data with binary=true = the data section of a .bt file
+ *   BGR_OCTREE_FILE         a whole .ot / .bt file with its text header (res is read from it;
+ *                           ids OcTree, ColorOcTree, OcTreeStamped)
+ * boxes may be NULL to query the count (*nb: capacity in, count out).  bbox = metric bounds of
+ * the occupied leaves (size the bgr_map from it; the origin must sit on a multiple of 32 cells
+ * from the key origin so that pruned leaves stay octree-aligned).  Host code (serial stream). */
+#define BGR_OCTREE_FULL_DATA 0
+#define BGR_OCTREE_BINARY_DATA 1
+#define BGR_OCTREE_FILE 2
+int bgr_octree_to_boxes(const void* data, int64_t nbytes, int format, double res, double occ_threshold,
+                        double* boxes_Bx6, int64_t* nb, double* res_out, double bbox_min[3],
+                        double bbox_max[3]);
 
 /* ------------------------------------------------------------------ path post-processing */
 /* Replaces PrunePlan(rrt_path) (MS:562-643): greedy shortcutting from the start — from the

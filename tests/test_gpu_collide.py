@@ -213,3 +213,48 @@ def test_edges_large_map_properties(bgr, oracle):
     sub = slice(0, 400)
     oh, ob = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
     assert not ((oh != h[sub]) & (b[sub] == 0)).any()
+
+
+def test_octomap_ingestion_and_refresh(bgr, oracle):
+    """serialised Octomap (full message data, MS:279) -> toBoxes rows -> bitmap; then a map refresh
+    that rasterises only the changed leaves (bgr_map_refresh_boxes)."""
+    from oracle import octree_io as T
+    occ = oracle.make_map(64, seed=1)
+    res, key0 = 0.05, (T.ORIGIN + 32, T.ORIGIN, T.ORIGIN - 64)
+    root, _ = T.tree_from_grid(occ, key0)
+    m, boxes = bgr.OccupancyMap.from_octomap(T.write_full(root), bgr.OCTREE_FULL_DATA, res)
+    assert m.occupied_cells() == int(occ.sum())
+    off = np.round((np.asarray([(k - T.ORIGIN) * res for k in key0]) - m.origin) / res).astype(int)
+    got = _bits_to_occ(m.download_bitmap(), int(m.dims.max()))[: m.dims[2], : m.dims[1], : m.dims[0]] if len(set(m.dims)) == 1 else None
+    full = np.zeros((m.dims[2], m.dims[1], m.dims[0]), dtype=np.uint8)
+    full[off[2]:off[2] + 64, off[1]:off[1] + 64, off[0]:off[0] + 64] = occ
+    if got is not None:
+        assert np.array_equal(got, full)
+    # collision answers through the ingested map == through the directly flattened grid
+    origin = [(k - T.ORIGIN) * res for k in key0]
+    m2 = bgr.OccupancyMap(res, origin, (64, 64, 64))
+    m2.set_boxes(oracle.grid_to_boxes(occ, res, origin, 2))
+    rng = np.random.default_rng(3)
+    p1 = (rng.uniform(0.2, 3.0, (4000, 3)) + origin).astype(np.float32)
+    p2 = (p1 + rng.normal(0, 0.3, p1.shape)).astype(np.float32)
+    p2 = np.clip(p2, np.asarray(origin, np.float32) + 0.1, np.asarray(origin, np.float32) + 3.1)
+    h1, b1 = m.collide_edges(p1, p2)
+    h2, b2 = m2.collide_edges(p1, p2)
+    same = (b1 == 0) & (b2 == 0)
+    assert np.array_equal(h1[same], h2[same]) and same.mean() > 0.99
+    # refresh: second map differs in a few blobs only
+    occ2 = occ.copy()
+    occ2[10:14, 10:14, 10:14] = 1
+    occ2[40:44, 40:48, 40:44] = 0
+    root2, _ = T.tree_from_grid(occ2, key0)
+    boxes2 = bgr.octree_to_boxes(T.write_full(root2), bgr.OCTREE_FULL_DATA, res)[0]
+    added, removed = m.refresh_boxes(boxes2)
+    assert 0 < added + removed < len(boxes2) // 4
+    assert m.occupied_cells() == int(occ2.sum())
+    fresh = bgr.OccupancyMap(res, m.origin, m.dims)
+    fresh.set_boxes(boxes2)
+    assert np.array_equal(m.download_bitmap(), fresh.download_bitmap())
+    h3, b3 = m.collide_edges(p1, p2)
+    h4, b4 = fresh.collide_edges(p1, p2)
+    assert np.array_equal(h3, h4) and np.array_equal(b3, b4)
+    assert m.refresh_boxes(boxes2) == (0, 0)
