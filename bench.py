@@ -43,6 +43,19 @@ def peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "src": "fallback"}
 
 
+def ncu_traffic(kernel):
+    """per-launch dram__bytes_read.sum + dram__bytes_write.sum of `kernel` from the committed
+    `ncu --set full` capture of this workload (profiles/traffic.json, written by
+    scripts/ncu_traffic.py from the .ncu-rep), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        d = json.load(f)
+    e = d.get(kernel)
+    return float(e["dram_bytes"]) if e else None
+
+
 class ClockSampler:
     """samples SM clock + throttle reasons DURING the timed region (pynvml, else nvidia-smi)."""
 
@@ -237,7 +250,8 @@ def run_ours(args):
                          "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
                          "peak_src": "148 SM x 128 FP32 lanes x %s sm_max_mhz (non-FMA: the bit-exact contract forbids FMA)" % pk["src"],
                          "pairs_evaluated_per_step": pairs_per_step, "flops_per_pair": 8,
-                         "sm_mhz_during_run": sm_mhz, "traffic": None,
+                         "sm_mhz_during_run": sm_mhz,
+                         "traffic": ncu_traffic("grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel"),
                          "hbm": {"algorithmic_bytes": alg_bytes, "achieved_gbs": alg_bytes / (ms_per_step * 1e-3) / 1e9,
                                  "peak_gbs": pk["hbm_gbs"], "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / pk["hbm_gbs"]}},
         })
@@ -273,6 +287,16 @@ def run_ours(args):
             ems = edge_ms / args.steps
             map_bytes = (MAP_N ** 3) / 8
             ebytes = 28.0 * N_EDGES + map_bytes
+            # per-kernel durations: CUDA events recorded by the library between its launches, on its stream
+            omap.set_timing(True)
+            kms = {}
+            for _ in range(args.steps):
+                flush()
+                edge_step()
+                for kname, v in omap.last_kernel_ms().items():
+                    kms[kname] = kms.get(kname, 0.0) + v / args.steps
+            omap.set_timing(False)
+            sweep_ms = kms["edges_sweep_kernel"]
             out["edge_checks"] = {
                 "value": world * N_EDGES / (ems * 1e-3), "unit": "edge checks/s", "ms_per_step": ems,
                 "config": {"workload": "configs[2]: 1,000,000 cylinder edges/GPU (r=0.03, L log-uniform [0.15,3] m) vs 512^3 "
@@ -283,10 +307,18 @@ def run_ours(args):
                         "ms_per_step": edge_e2e_ms / args.steps,
                         "h2d_bytes_per_step": int(24 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
                 "gpu_launches": int(edge_launches * args.steps),
-                "roofline": {"bound": "hbm", "kernel": "collide_edges_kernel", "achieved": ebytes / (ems * 1e-3) / 1e9,
-                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ebytes / (ems * 1e-3) / 1e9 / pk["hbm_gbs"],
-                             "algorithmic_bytes": ebytes, "peak_src": pk["src"], "traffic": None},
+                "roofline": {"bound": "hbm", "kernel": "edges_sweep_kernel", "achieved": ebytes / (sweep_ms * 1e-3) / 1e9,
+                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ebytes / (sweep_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                             "algorithmic_bytes": ebytes, "peak_src": pk["src"], "traffic": ncu_traffic("edges_sweep_kernel"),
+                             "kernel_ms": kms, "kernel_share_of_step": sweep_ms / max(sum(kms.values()), 1e-9),
+                             "note": "the 16 MiB bitmap is L2 resident: the sweep is bound by instruction issue and L2 latency, "
+                                     "not HBM (ncu: profiles/); the HBM figure is the contract of SURVEY 8(d)",
+                             "work_items_per_s": stats["work_items"] / (sweep_ms * 1e-3)},
             }
+
+        # ---------------------------------------------------------------- batched planner (configs[0], configs[3])
+        if not args.skip_planner:
+            out["planner"] = planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier)
 
         # ---------------------------------------------------------------- sharded kNN (N>1)
         if world > 1 and not args.skip_sharded:
@@ -334,6 +366,53 @@ def run_ours(args):
         print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
+
+
+def planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier):
+    """Tree growth of the batched planner (bgr_planner_*): configs[0] = RRT* with 10 % goal bias on a
+    64^3 map to 5,000 nodes, k=10 (batch 1 = the reference's sequential loop, and batch 256);
+    configs[3] = bottleneck-guided RRT* (3 milestones) on a 256^3 narrow-passage map to 200,000 nodes,
+    batch 4096, K=16, edge checks + rewiring.  One independent planning query per GPU (replicas)."""
+    res = {}
+
+    def grow(n_map, seed, walls, door, mode, k, batch, flags, max_nodes, milestones, goal):
+        occ = synth.make_map(n_map, seed, n_walls=walls, wall_thick=2 if n_map == 64 else 4, door_cells=door)
+        boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+        omap = B.OccupancyMap(0.05, (0, 0, 0), (n_map,) * 3, stream=stream.cuda_stream)
+        omap.set_boxes(boxes)
+        ext = n_map * 0.05
+        table = synth.points(9 + rank, 200_000, ext)
+        P = B.PlannerParams((0.2, 0.2, 0.2), goal, mode=mode, k=k, batch=batch, flags=flags | B.PLAN_NO_GOAL, seed=5489 + rank)
+        pl = B.Planner(P, omap, table, milestones, stream=stream.cuda_stream)
+        pl.run(min(max_nodes, 64 * batch + 64), 3)                    # warm-up: first launches, allocations
+        stream.synchronize()
+        barrier()
+        n0, t0 = len(pl), time.perf_counter()
+        pl.run(max_nodes)
+        stream.synchronize()
+        el = max_over_ranks(time.perf_counter() - t0)
+        st = pl.stats()
+        return {"nodes": len(pl), "seconds": el, "nodes_per_s": world * (len(pl) - n0) / el,
+                "candidates_per_s": world * st["candidates"] / el, "batches": st["batches"], "batch": batch, "k": k,
+                "rejected_state": st["rejected_state"], "rejected_edge": st["rejected_edge"], "rewired": st["rewired"],
+                "in_band": st["in_band"], "map": "%d^3 @0.05 m, %d leaf boxes" % (n_map, len(boxes))}
+
+    g64 = (3.0, 3.0, 3.0)
+    res["config0_rrtstar_64_batch1"] = grow(64, 1, 3, 6, B.PLAN_MODE_RS, 10, 1, B.PLAN_QUIRKS, 5000, None, g64)
+    res["config0_rrtstar_64_batch256"] = grow(64, 1, 3, 6, B.PLAN_MODE_RS, 10, 256, 0, 5000, None, g64)
+    # the 3 milestone points = the door centres of the 3 walls (what the CNN is trained to predict)
+    occ3 = synth.make_map(256, 5, n_walls=3, wall_thick=4, door_cells=5)
+    ms = []
+    for w in range(3):
+        x0 = (w + 1) * 256 // 4
+        zz, yy = np.nonzero(occ3[:, :, x0] == 0)
+        ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
+    ms = np.asarray(ms, dtype=np.float32)
+    res["config3_bottleneck_256_batch4096"] = grow(256, 5, 3, 5, B.PLAN_MODE_MS, 16, 4096,
+                                                   B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, 200_000, ms, (12.6, 12.6, 12.6))
+    res["note"] = ("wall clock of bgr_planner_run (host loop + device kernels, one sync per batch); nodes_per_s is the "
+                   "aggregate over %d independent planning queries (one per GPU)" % world)
+    return res
 
 
 # ------------------------------------------------------------------------------ CPU arm
@@ -427,6 +506,7 @@ def main():
     ap.add_argument("--skip-edges", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-sharded", action="store_true")
+    ap.add_argument("--skip-planner", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

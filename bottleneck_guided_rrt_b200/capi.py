@@ -86,6 +86,8 @@ def lib():
     L.bgr_map_collide_edges.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_last_stats.argtypes = [vp, vp]
+    L.bgr_map_set_timing.argtypes = [vp, i32]
+    L.bgr_map_last_kernel_ms.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
     L.bgr_map_refresh_boxes.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_octree_to_boxes.argtypes = [vp, i64, i32, f64, f64, vp, vp, vp, vp, vp]
@@ -444,6 +446,15 @@ class OccupancyMap:
         _check(lib().bgr_map_collide_edges(self._h, _ptr(a), _ptr(b), n, radius, shape, _ptr(hit),
                                            _ptr(band) if want_band else None))
         return hit, band
+
+    def set_timing(self, on=True):
+        _check(lib().bgr_map_set_timing(self._h, 1 if on else 0))
+
+    def last_kernel_ms(self):
+        t = np.zeros(4, dtype=np.float32)
+        _check(lib().bgr_map_last_kernel_ms(self._h, _ptr(t)))
+        return {"edges_sweep_kernel": float(t[0]), "edges_narrow_kernel": float(t[1]),
+                "collide_edges_kernel": float(t[2]), "edges_finalize_kernel": float(t[3])}
 
     def last_stats(self):
         s = np.zeros(4, dtype=np.uint64)

@@ -300,7 +300,7 @@ constexpr int kGridWarps = 8;
 // repeated; after kFastTries the caller falls back to the general ring search.
 constexpr int kFastTries = 3;
 
-__global__ void __launch_bounds__(kGridWarps * 32) grid_knn_kernel(GridKnnArgs a) {
+__global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArgs a) {
     __shared__ unsigned long long cand[kGridWarps][kFastCap];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;

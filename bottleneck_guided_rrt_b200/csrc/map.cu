@@ -824,6 +824,8 @@ struct bgr_map {
     DevBuf<unsigned> eflags, qctl;
     DevBuf<NarrowRec> queue;
     uint64_t last_stats[4] = {0, 0, 0, 0};
+    cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // kernel boundaries of the last collide_edges (timing on)
+    bool timing = false;
     std::vector<uint64_t> leaf_keys;   // sorted keys (level, z, y, x) of the leaves set through set/refresh_boxes
     bool keys_valid = false;           // false after update_boxes (the caller manages the diff itself)
 
@@ -1085,6 +1087,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     // fast path needs the swept hull of one slab to fit a kRectMax x kRectMax cell rectangle:
     // extent <= res (slope <= 1 on the dominant axis) + 2*(radius+margin) + 2*(radius+margin)
     const bool fast = (h->res + 4.0 * (radius + kSweepMargin)) / h->res + 1.0 <= (double)kRectMax;
+    if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[0], h->stream));
     if (fast) {
         const int64_t cap = std::max<int64_t>(1 << 16, 4 * n);
         BGR_CHECK(h->queue.reserve(cap, h->stream, false));
@@ -1096,17 +1099,22 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.qctl = h->qctl.p; a.stats = h->stats.p; a.hit = d_hit; a.band = d_band;
         edges_sweep_kernel<<<(unsigned)div_up(n, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
         BGR_LAUNCH_CHECK();
+        if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
         const int nblk = (int)std::min<int64_t>(4LL * num_sms(), std::max<int64_t>(1, div_up(cap, 128)));
         edges_narrow_kernel<<<nblk, 128, 0, h->stream>>>(a);
         BGR_LAUNCH_CHECK();
         ma.only_overflow = 1;   // no-op unless the queue overflowed
     } else {
         ma.only_overflow = 0;
+        if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
     }
+    if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[2], h->stream));
     collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(ma);
     BGR_LAUNCH_CHECK();
+    if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[3], h->stream));
     edges_finalize_kernel<<<(unsigned)div_up(n, 256), 256, 0, h->stream>>>(h->eflags.p, n, d_hit, d_band);
     BGR_LAUNCH_CHECK();
+    if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[4], h->stream));
     return BGR_OK;
 }
 
@@ -1128,6 +1136,21 @@ int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t 
     return BGR_OK;
 }
 
+int bgr_map_set_timing(bgr_map* h, int on) {
+    BGR_ARG(h != nullptr, "null map");
+    if (on && !h->tev[0])
+        for (int i = 0; i < 5; ++i) BGR_CUDA(cudaEventCreate(&h->tev[i]));
+    h->timing = on != 0;
+    return BGR_OK;
+}
+
+int bgr_map_last_kernel_ms(bgr_map* h, float out[4]) {
+    BGR_ARG(h != nullptr && out != nullptr && h->tev[0] != nullptr, "timing was never enabled on this map");
+    BGR_CUDA(cudaEventSynchronize(h->tev[4]));
+    for (int i = 0; i < 4; ++i) BGR_CUDA(cudaEventElapsedTime(&out[i], h->tev[i], h->tev[i + 1]));
+    return BGR_OK;
+}
+
 int bgr_map_last_stats(bgr_map* h, uint64_t out[4]) {
     BGR_ARG(h != nullptr && out, "bad arguments");
     if (!h->stats.p) { out[0] = out[1] = out[2] = out[3] = 0; return BGR_OK; }
@@ -1144,6 +1167,8 @@ int bgr_map_destroy(bgr_map* h) {
     for (int L = 0; L <= kMaxLevel; ++L) h->bits[L].release();
     h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
     h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
+    for (int i = 0; i < 5; ++i)
+        if (h->tev[i]) cudaEventDestroy(h->tev[i]);
     delete h;
     return BGR_OK;
 }

@@ -40,6 +40,8 @@ struct PlanDev {                 // device view shared by the kernels
     float *e1, *e2;
     uint8_t *ehit, *eband;
     float* costs;                // [B][K+1], slot K = via the Nearest node
+    float* psis;                 // [B][K+1] full path length (root edge included) via that slot, see chain_cost
+    float* psi;                  // [B] full path length of the accepted candidate via its committed parent
     uint8_t* ok;
     int32_t *parent, *new_index;
     float* cost;
@@ -186,17 +188,22 @@ __global__ void plan_edges_kernel(PlanDev d) {                 // edge list for 
 
 // cost_wiring(tree, tree[P], child) MS:802-831: f32 accumulation from the child upwards; the
 // walk ends at index <= 0, so the edge into the root is never added.
-__device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, float cz) {
+// *psi (optional) = the same sum PLUS that skipped root edge: the true path length root -> child.
+// It never increases along a parent pointer (float addition is monotone), which is what keeps
+// batched rewiring acyclic (rewire_proposal).
+__device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, float cz, float* psi = nullptr) {
     const float px = d.x[P], py = d.y[P], pz = d.z[P];
     float cost = __fadd_rn(0.f, norm_ref(px, py, pz, cx, cy, cz));
     int cur = d.par[P];
     float lx = px, ly = py, lz = pz;                           // previous node on the walk (P first)
-    while (cur > 0) {
+    int64_t guard = d.n + d.B + 2;                             // a tree walk visits every node at most once
+    while (cur > 0 && guard-- > 0) {
         const float qx = d.x[cur], qy = d.y[cur], qz = d.z[cur];
         cost = __fadd_rn(cost, norm_ref(qx, qy, qz, lx, ly, lz));
         lx = qx; ly = qy; lz = qz;
         cur = d.par[cur];
     }
+    if (psi) *psi = cur == 0 ? __fadd_rn(cost, norm_ref(d.x[0], d.y[0], d.z[0], lx, ly, lz)) : cost;
     return cost;
 }
 
@@ -207,7 +214,7 @@ __global__ void plan_cost_kernel(PlanDev d) {
     if (d.hit[c]) return;
     const int32_t ind = slot_node(d, c, j);
     if (ind < 0) return;
-    d.costs[t] = chain_cost(d, ind, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]);
+    d.costs[t] = chain_cost(d, ind, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2], &d.psis[t]);
 }
 
 __global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS:838-853 + MS:1322-1323
@@ -226,21 +233,25 @@ __global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS
     int32_t parent_index = d.near[c];
     float lowest = d.costs[(size_t)c * K1 + d.K];             // current_cost MS:1316
     float mycost = lowest;
+    int slot = d.K, pslot = d.K;
     if (d.have_knn) {
         int32_t pc = -5;
         for (int j = 0; j < d.K; ++j) {
             if (edge_check && d.ehit[(size_t)c * K1 + j]) continue;
             const float temp = d.costs[(size_t)c * K1 + j];
-            if (temp < lowest) { pc = d.knn_idx[(size_t)c * d.K + j]; lowest = temp; }
+            if (temp < lowest) { pc = d.knn_idx[(size_t)c * d.K + j]; lowest = temp; pslot = j; }
         }
         if (pc > 0) {
             parent_index = pc;
             mycost = lowest;
+            slot = pslot;
             atomicAdd((unsigned long long*)&d.counters[6], 1ull);
         }
     }
-    d.parent[c] = (quirks && d.found[c]) ? d.near[c] : parent_index;
+    const bool keep_near = quirks && d.found[c];
+    d.parent[c] = keep_near ? d.near[c] : parent_index;
     d.cost[c] = mycost;
+    d.psi[c] = d.psis[(size_t)c * K1 + (keep_near ? d.K : slot)];   // follows the pointer actually committed
     d.ok[c] = 1;
 }
 
@@ -308,6 +319,12 @@ __global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, 
 // rewiring (beyond reference): neighbour `ind` adopts the new node when
 // cost(new) + Norm(tree[ind], new) < cost(ind) (and the edge is free); one proposal per node
 // survives: the smallest (new cost bits, new index) key.
+// Acyclicity: the reference's cost skips the edge into the root (cost_wiring stops at index <= 0),
+// so a depth-1 node can look more expensive than its own descendants, and proposals of one batch
+// are applied together.  A proposal must therefore also lower the TRUE path length:
+// psi(new) < psi(ind), both on the tree as it stands before this batch's rewires.  psi never
+// increases along any kept pointer and strictly decreases along every rewired one, so no set of
+// simultaneously applied proposals can close a cycle.
 __device__ __forceinline__ bool rewire_proposal(const PlanDev& d, int t, int32_t* ind_out, unsigned long long* key) {
     const int c = t / d.K, j = t % d.K;
     const int32_t ni = d.new_index[c];
@@ -317,8 +334,10 @@ __device__ __forceinline__ bool rewire_proposal(const PlanDev& d, int t, int32_t
     if ((d.p.flags & BGR_PLAN_EDGE_CHECK) && d.ehit[(size_t)c * (d.K + 1) + j]) return false;
     const float ix = d.x[ind], iy = d.y[ind], iz = d.z[ind];
     const float nc = __fadd_rn(d.cost[c], norm_ref(ix, iy, iz, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]));
-    const float oc = chain_cost(d, d.par[ind], ix, iy, iz);
+    float psi_ind;
+    const float oc = chain_cost(d, d.par[ind], ix, iy, iz, &psi_ind);
     if (!(nc < oc)) return false;
+    if (!(d.psi[c] < psi_ind)) return false;
     *ind_out = ind;
     *key = ((unsigned long long)__float_as_uint(nc) << 32) | (unsigned)ni;
     return true;
@@ -369,7 +388,7 @@ struct bgr_planner {
     int goal_reached = 0;
     int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, -1};
     DevBuf<uint32_t> mt_state, words;
-    DevBuf<float> table, milestones, prand, pnew, near_dist, knn_d2, e1, e2, costs, cost;
+    DevBuf<float> table, milestones, prand, pnew, near_dist, knn_d2, e1, e2, costs, cost, psis, psi;
     DevBuf<uint8_t> found, hit, band, ehit, eband, ok;
     DevBuf<int32_t> par, near, knn_idx, parent, new_index;
     DevBuf<unsigned long long> rkey;
@@ -386,7 +405,7 @@ int bgr_planner_destroy(bgr_planner* pl) {
     if (pl->nns) bgr_nns_destroy(pl->nns);
     pl->mt_state.release(); pl->words.release(); pl->table.release(); pl->milestones.release();
     pl->prand.release(); pl->pnew.release(); pl->near_dist.release(); pl->knn_d2.release();
-    pl->e1.release(); pl->e2.release(); pl->costs.release(); pl->cost.release();
+    pl->e1.release(); pl->e2.release(); pl->costs.release(); pl->cost.release(); pl->psis.release(); pl->psi.release();
     pl->found.release(); pl->hit.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
     pl->ok.release(); pl->par.release(); pl->near.release(); pl->knn_idx.release(); pl->parent.release();
     pl->new_index.release(); pl->rkey.release(); pl->counters.release(); pl->host_counters.release();
@@ -484,6 +503,8 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_CHECK(pl->knn_idx.reserve((int64_t)B * K, st, false));
     BGR_CHECK(pl->knn_d2.reserve((int64_t)B * K, st, false));
     BGR_CHECK(pl->costs.reserve((int64_t)B * K1, st, false));
+    BGR_CHECK(pl->psis.reserve((int64_t)B * K1, st, false));
+    BGR_CHECK(pl->psi.reserve(B, st, false));
     if (edge_check) {
         BGR_CHECK(pl->e1.reserve(3 * (int64_t)B * K1, st, false));
         BGR_CHECK(pl->e2.reserve(3 * (int64_t)B * K1, st, false));
@@ -510,7 +531,7 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     d.prand = pl->prand.p; d.pnew = pl->pnew.p; d.found = pl->found.p; d.near = pl->near.p;
     d.hit = pl->hit.p; d.band = pl->band.p; d.knn_idx = pl->knn_idx.p;
     d.e1 = pl->e1.p; d.e2 = pl->e2.p; d.ehit = pl->ehit.p; d.eband = pl->eband.p;
-    d.costs = pl->costs.p; d.ok = pl->ok.p; d.parent = pl->parent.p; d.new_index = pl->new_index.p;
+    d.costs = pl->costs.p; d.psis = pl->psis.p; d.psi = pl->psi.p; d.ok = pl->ok.p; d.parent = pl->parent.p; d.new_index = pl->new_index.p;
     d.cost = pl->cost.p; d.rkey = pl->rkey.p; d.counters = pl->counters.p;
 
     const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);

@@ -176,6 +176,11 @@ int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* 
 /* counters of the last collide_edges call: [0] work items (edge,slab), [1] occupied
  * candidate voxels, [2] exact narrow-phase tests, [3] narrow-phase iteration-cap events */
 int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
+/* measurement aid: with timing on, collide_edges records CUDA events between its kernels on the
+ * map's stream; last_kernel_ms returns the durations of the last call: [0] edges_sweep_kernel,
+ * [1] edges_narrow_kernel, [2] collide_edges_kernel (general / overflow path), [3] finalize */
+int bgr_map_set_timing(bgr_map* map, int on);
+int bgr_map_last_kernel_ms(bgr_map* map, float out[4]);
 int bgr_map_destroy(bgr_map* map);
 
 /* ------------------------------------------------------------------ OcTree ingestion */

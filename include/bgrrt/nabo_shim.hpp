@@ -206,6 +206,50 @@ public:
                       uint8_t* in_band = nullptr) const {
         check(bgr_map_collide_edges(h_, p1, p2, m, radius, shape, hit, in_band), "collide_edges");
     }
+    // map refresh: only the leaves that differ from the current list are rasterised
+    void refreshBoxes(const std::vector<Box>& boxes, int64_t* added = nullptr, int64_t* removed = nullptr) {
+        check(bgr_map_refresh_boxes(h_, boxes.empty() ? nullptr : boxes[0].data(), (int64_t)boxes.size(), added, removed),
+              "refresh_boxes");
+    }
+    // octomap_msgs::fullMsgToMap + fcl::OcTree::toBoxes (MS:279,291) without octomap/FCL: the
+    // message's data bytes (binary == msg.binary, res == msg.resolution) -> toBoxes rows
+    static std::vector<Box> boxesFromOctomapMsg(const int8_t* data, size_t n, bool binary, double res,
+                                                double occ_threshold = 0.5, double bbox_min[3] = nullptr,
+                                                double bbox_max[3] = nullptr) {
+        int64_t nb = 0;
+        const int fmt = binary ? BGR_OCTREE_BINARY_DATA : BGR_OCTREE_FULL_DATA;
+        check(bgr_octree_to_boxes(data, (int64_t)n, fmt, res, occ_threshold, nullptr, &nb, nullptr, nullptr, nullptr), "octree_to_boxes");
+        std::vector<Box> boxes((size_t)nb);
+        check(bgr_octree_to_boxes(data, (int64_t)n, fmt, res, occ_threshold, nb ? boxes[0].data() : nullptr, &nb, nullptr,
+                                  bbox_min, bbox_max), "octree_to_boxes");
+        return boxes;
+    }
+    // std::vector<Pose> PrunePlan(std::vector<Pose> rrt_path)  MS:562 — waypoints as x,y,z triples;
+    // returns the kept waypoint indices (all anchor-waypoint edges checked in one launch)
+    std::vector<int32_t> PrunePlan(const std::vector<float>& path_xyz, double radius = 0.03,
+                                   int shape = BGR_SHAPE_CYLINDER, int64_t* in_band = nullptr) const {
+        const int64_t p = (int64_t)path_xyz.size() / 3;
+        std::vector<int32_t> keep((size_t)p);
+        int64_t nk = p;
+        check(bgr_map_prune_path(h_, path_xyz.data(), p, radius, shape, keep.data(), &nk, in_band), "prune_path");
+        keep.resize((size_t)nk);
+        return keep;
+    }
+    // void find_labels(std::vector<Pose> final_path)  MS:943 — the 3 interior waypoints closest to the
+    // obstacles as 9 floats (the CNN's training label); Sphere(0.1) clearance as in MS:958
+    std::vector<float> find_labels(const std::vector<double>& final_path_xyz, double radius = 0.1, int n_labels = 3,
+                                   std::vector<int32_t>* indices = nullptr) const {
+        std::vector<float> labels((size_t)(3 * n_labels));
+        std::vector<int32_t> idx((size_t)n_labels);
+        check(bgr_map_find_labels(h_, final_path_xyz.data(), (int64_t)final_path_xyz.size() / 3, radius, n_labels, idx.data(),
+                                  labels.data(), nullptr, nullptr), "find_labels");
+        if (indices) *indices = idx;
+        return labels;
+    }
+    // fcl::distance(Sphere(radius), every leaf) minimum per point (MS:956-975, RD:890-917); -1 = touching
+    void clearance(const double* pts_xyz, int64_t m, double radius, double* dist) const {
+        check(bgr_map_clearance(h_, pts_xyz, m, radius, dist), "clearance");
+    }
     bgr_map* handle() const { return h_; }
 
 private:
@@ -213,6 +257,15 @@ private:
     CollisionWorld& operator=(const CollisionWorld&);
     bgr_map* h_;
 };
+
+// std::vector<Pose> SmoothenPlan(std::vector<Pose> rrt_path)  MS:645 — x,y,z triples in, 11 samples out
+inline std::vector<double> SmoothenPlan(const std::vector<double>& path_xyz) {
+    int64_t ns = 0;
+    check(bgr_path_smoothen(path_xyz.data(), (int64_t)path_xyz.size() / 3, nullptr, &ns), "path_smoothen");
+    std::vector<double> out((size_t)(3 * ns));
+    check(bgr_path_smoothen(path_xyz.data(), (int64_t)path_xyz.size() / 3, out.data(), &ns), "path_smoothen");
+    return out;
+}
 
 }  // namespace bgrrt
 

@@ -34,11 +34,13 @@ namespace {
 
 // cost_wiring(tree, tree[P], child) MS:802-831: float accumulation from the child upwards;
 // the walk stops at index <= 0, so the edge into the root is never added.
-float chain_cost(const orc_planner* pl, int32_t P, const float* child) {
+// *psi (optional): the same sum plus that skipped root edge = the true path length root -> child
+// (used only by the beyond-reference rewiring, to keep it acyclic).
+float chain_cost(const orc_planner* pl, int32_t P, const float* child, float* psi = nullptr) {
     const float* V = pl->xyz.data();
     float cost = 0;
     cost = cost + orc_norm(V + 3 * P, child);
-    int cur = pl->par[P], l = 0, prev = 0;
+    int cur = pl->par[P], l = 0, prev = P;
     while (cur > 0) {
         if (l == 0) {
             cost = cost + orc_norm(V + 3 * cur, V + 3 * P);
@@ -48,6 +50,11 @@ float chain_cost(const orc_planner* pl, int32_t P, const float* child) {
         }
         prev = cur;
         cur = pl->par[cur];
+    }
+    if (psi) {
+        float full = cost;
+        if (cur == 0) full = full + orc_norm(V, V + 3 * prev);
+        *psi = full;
     }
     return cost;
 }
@@ -126,7 +133,7 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
     for (int c = 0; c < B; ++c) pl->stats[6] += band[c];
     // ---- kNN + choose parent
     std::vector<int32_t> knn_idx((size_t)B * K, -1), parent(B);
-    std::vector<float> knn_d2((size_t)B * K), cost(B);
+    std::vector<float> knn_d2((size_t)B * K), cost(B), psi(B);
     const bool have_knn = N > K;                                                    // MS:1273 V.size() > 5 (K = 5)
     if (have_knn) orc_knn_brute(pl->xyz.data(), N, pnew.data(), B, K, 0, INFINITY, nullptr, knn_idx.data(), knn_d2.data(), 0);
     // candidate edges for the optional edge check: j < K neighbours, j == K the nearest node
@@ -158,25 +165,29 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
         if (hit[c]) { pl->stats[2]++; continue; }
         if (edge_check && ehit[(size_t)c * (K + 1) + K]) { pl->stats[3]++; continue; }
         int32_t parent_index = near[c];
-        float lowest = chain_cost(pl, near[c], &pnew[3 * c]);                       // current_cost MS:1316
+        float psi_near = 0, psi_low = 0, psi_tmp = 0;
+        float lowest = chain_cost(pl, near[c], &pnew[3 * c], &psi_near);            // current_cost MS:1316
         cost[c] = lowest;
+        psi[c] = psi_near;
         if (have_knn) {
             int32_t pc = -5;                                                         // extend_tree MS:838-853
             for (int d = 0; d < K; ++d) {
                 const int32_t ind = knn_idx[(size_t)c * K + d];
                 if (edge_check && ehit[(size_t)c * (K + 1) + d]) continue;
-                const float temp = chain_cost(pl, ind, &pnew[3 * c]);
-                if (temp < lowest) { pc = ind; lowest = temp; }
+                const float temp = chain_cost(pl, ind, &pnew[3 * c], &psi_tmp);
+                if (temp < lowest) { pc = ind; lowest = temp; psi_low = psi_tmp; }
             }
             if (pc > 0) {                                                            // MS:1322-1323
                 parent_index = pc;
                 cost[c] = lowest;
+                psi[c] = psi_low;
                 pl->stats[4]++;
             }
         }
         // MS:1236-1238: in the `found` branch the row already carries the Nearest index in
         // column 3 before the final push_back, so BuildPlan/cost_wiring keep reading THAT.
         parent[c] = (quirks && found[c]) ? near[c] : parent_index;
+        if (quirks && found[c]) psi[c] = psi_near;                                   // psi follows the committed pointer
         ok[c] = 1;
     }
     // ---- append in candidate order; goal test MS:1340 cuts the batch
@@ -205,8 +216,12 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
                 const int32_t ind = knn_idx[(size_t)c * K + d];
                 if (ind <= 0 || ind == pl->par[new_index[c]]) continue;
                 const float nc = cost[c] + orc_norm(&pl->xyz[3 * (size_t)ind], &pnew[3 * c]);
-                const float oc = chain_cost(pl, pl->par[ind], &pl->xyz[3 * (size_t)ind]);
+                float psi_ind = 0;
+                const float oc = chain_cost(pl, pl->par[ind], &pl->xyz[3 * (size_t)ind], &psi_ind);
                 if (!(nc < oc)) continue;
+                // acyclicity (the reference's cost skips the root edge, and a batch applies its
+                // proposals together): the true path length must drop too, on the pre-batch tree
+                if (!(psi[c] < psi_ind)) continue;
                 if (edge_check && ehit[(size_t)c * (K + 1) + d]) continue;
                 props.push_back({ind, new_index[c], nc});
             }

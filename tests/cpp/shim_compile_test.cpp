@@ -5,6 +5,7 @@
 // exit 0: ran on a GPU and matched a scalar check; exit 3: no CUDA device and the shim threw.
 #include <cfloat>
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <vector>
 
@@ -81,7 +82,34 @@ int main() {
         const bool in_free = world.isStateValid({2.0f, 2.0f, 2.0f});
         const bool line_hit = world.isLineValid({0.5f, 1.025f, 1.025f}, {1.5f, 1.025f, 1.025f});
         const bool line_free = world.isLineValid({0.5f, 2.0f, 2.0f}, {1.5f, 2.0f, 2.0f});
-        const bool ok = bad == 0 && threw == 3 && ni == N && nrm == 0.f && in_hit && !in_free && line_hit && !line_free;
+        // path post-processing the way main() uses it (MS:1352-1356): PrunePlan -> SmoothenPlan -> find_labels
+        std::vector<float> path = {0.5f, 2.0f, 2.0f, 0.9f, 2.1f, 2.0f, 1.2f, 2.0f, 2.2f, 1.5f, 2.0f, 2.0f, 2.5f, 2.2f, 2.1f};
+        const std::vector<int32_t> kept = world.PrunePlan(path);               // free space: start -> goal
+        std::vector<double> pd(path.begin(), path.end());
+        const std::vector<double> smooth = bgrrt::SmoothenPlan(pd);             // > 3 waypoints: cubic over the first four
+        std::vector<int32_t> lab_idx;
+        const std::vector<float> labels = world.find_labels(pd, 0.1, 3, &lab_idx);
+        // one occupied depth-16 leaf at key (32768+20, 32768+20, 32768+20) as a full-message stream
+        std::vector<int8_t> msg;
+        auto put = [&](float v, unsigned char mask) {
+            const unsigned char* b = reinterpret_cast<const unsigned char*>(&v);
+            for (int i = 0; i < 4; ++i) msg.push_back((int8_t)b[i]);
+            msg.push_back((int8_t)mask);
+        };
+        put(1.f, 1u << 7);                                                       // root -> +x+y+z octant
+        for (int d = 1; d < 16; ++d) {
+            const int bit = (20 >> (15 - d)) & 1;                                // key offset 20 = 0b10100 from the octant's corner
+            put(1.f, (unsigned char)(1u << (bit ? 7 : 0)));
+        }
+        put(1.f, 0);
+        const std::vector<bgrrt::CollisionWorld::Box> mb = bgrrt::CollisionWorld::boxesFromOctomapMsg(msg.data(), msg.size(), false, 0.05);
+        world.refreshBoxes(mb);
+        const bool msg_hit = world.isStateValid({1.025f, 1.025f, 1.025f});
+        const bool old_gone = !world.isStateValid({1.3f, 1.3f, 1.3f});
+        const bool post_ok = kept.size() == 2 && kept[0] == 0 && kept[1] == 4 && smooth.size() == 33 && smooth[0] == 0.5 &&
+                             labels.size() == 9 && lab_idx.size() == 3 && mb.size() == 1 && std::fabs(mb[0][0] - 1.025) < 1e-12 &&
+                             msg_hit && old_gone;
+        const bool ok = bad == 0 && threw == 3 && ni == N && nrm == 0.f && in_hit && !in_free && line_hit && !line_free && post_ok;
         std::printf("shim test: knn mismatches=%d threw=%d nearest=%d hit=%d/%d line=%d/%d -> %s\n", bad, threw, ni,
                     (int)in_hit, (int)in_free, (int)line_hit, (int)line_free, ok ? "ok" : "FAIL");
         return ok ? 0 : 1;

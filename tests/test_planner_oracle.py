@@ -61,3 +61,32 @@ def test_sequential_loop_literal(oracle, bgr):
     assert len(xyz) == len(opar)
     assert np.array_equal(np.stack(xyz).view(np.uint32), oxyz.view(np.uint32))
     assert par == opar.tolist()
+
+
+def test_batched_rewiring_stays_a_tree(oracle, bgr):
+    """beyond-reference rewiring, many proposals applied per batch: the reference's cost skips the
+    edge into the root (cost_wiring stops at index <= 0), so cost alone would let a depth-1 node
+    adopt its own descendant, and two proposals of one batch could close a loop between them.  The
+    psi rule (true path length must drop too) keeps every batch acyclic: every node still reaches
+    the root, in fewer steps than there are nodes."""
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(64, 1, occupancy=0.0)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    table = synth.points(9, 20000, 3.2)
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_RS, k=12, batch=512,
+                          flags=bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL, seed=5)
+    op = oracle.Planner(P, boxes, table)
+    op.run(12000, 60)
+    xyz, par = op.tree()
+    st = op.stats()
+    assert st["rewired"] > 100 and par[0] == -1
+    depth = np.zeros(len(par), dtype=np.int64)
+    cur = np.arange(len(par))
+    for _ in range(len(par)):
+        alive = cur > 0
+        if not alive.any():
+            break
+        depth[alive] += 1
+        cur = np.where(alive, par[np.maximum(cur, 0)], cur)
+    assert not (cur > 0).any(), "a parent chain does not reach the root: rewiring closed a cycle"
+    assert depth.max() < len(par)
