@@ -87,6 +87,8 @@ def lib():
     L.bgr_map_collide_edges_dev.argtypes = [vp, vp, vp, i64, f64, i32, vp, vp]
     L.bgr_map_last_stats.argtypes = [vp, vp]
     L.bgr_map_set_timing.argtypes = [vp, i32]
+    L.bgr_map_set_gate.argtypes = [vp, i32]
+    L.bgr_map_last_gate_stats.argtypes = [vp, vp]
     L.bgr_map_last_kernel_ms.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
     L.bgr_map_refresh_boxes.argtypes = [vp, vp, i64, vp, vp]
@@ -460,6 +462,15 @@ class OccupancyMap:
         s = np.zeros(4, dtype=np.uint64)
         _check(lib().bgr_map_last_stats(self._h, _ptr(s)))
         return {"work_items": int(s[0]), "candidates": int(s[1]), "narrow_tests": int(s[2]), "iter_cap": int(s[3])}
+
+    def set_gate(self, on):
+        """sweep gate of collide_edges on/off (results are identical; measurement / test aid)"""
+        _check(lib().bgr_map_set_gate(self._h, 1 if on else 0))
+
+    def gate_stats(self):
+        s = np.zeros(2, dtype=np.uint64)
+        _check(lib().bgr_map_last_gate_stats(self._h, _ptr(s)))
+        return {"rect_items": int(s[0]), "dilation_cells": int(s[1])}
 
     # ---- path post-processing (PrunePlan MS:562-643, find_labels MS:943-1011)
     def prune_path(self, path, radius=0.03, shape=SHAPE_CYLINDER):

@@ -417,10 +417,44 @@ struct Edge2Args {
     NarrowRec* queue;
     unsigned queue_cap;
     unsigned* qctl;              // [0] queue fill, [1] edges that overflowed the queue
-    unsigned long long* stats;   // [4]
+    unsigned long long* stats;   // [6]: [4] = items that reached the rectangle phase
     uint8_t* hit;
     uint8_t* band;
+    LevelGrid dil;               // level 0 dilated by gate_d cells (Chebyshev), same brick layout
+    int gate_d;                  // 0 = gate off (every slab runs the rectangle phase)
 };
+
+// ------------------------------------------------------------------ dilated occupancy (sweep gate)
+// One separable pass: out = in OR-ed with its copies shifted by -d..+d cells along `axis`
+// (d <= 3), computed on whole 4x4x4 brick words: the cells that leave a brick on one side come
+// in from the neighbouring brick on the other.  x, y, z passes in turn give the box dilation.
+__device__ __forceinline__ uint64_t axis_mask_eq(int axis, int v) {
+    return axis == 0 ? (0x1111111111111111ull << v) : axis == 1 ? (0x000F000F000F000Full << (4 * v)) : (0xFFFFull << (16 * v));
+}
+__global__ void dilate_axis_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int nbx, int nby,
+                                   int nbz, int axis, int d) {
+    const int64_t total = (int64_t)nbx * nby * nbz;
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= total) return;
+    const int bx = (int)(w % nbx), by = (int)((w / nbx) % nby), bz = (int)(w / ((int64_t)nbx * nby));
+    const int pos = axis == 0 ? bx : (axis == 1 ? by : bz), n = axis == 0 ? nbx : (axis == 1 ? nby : nbz);
+    const int64_t stride = axis == 0 ? 1 : (axis == 1 ? nbx : (int64_t)nbx * nby);
+    const int unit = axis == 0 ? 1 : (axis == 1 ? 4 : 16);
+    const uint64_t W = in[w], Wm = pos > 0 ? in[w - stride] : 0ull, Wp = pos + 1 < n ? in[w + stride] : 0ull;
+    uint64_t r = W;
+    for (int s = 1; s <= d; ++s) {
+        uint64_t lt = 0, ge = 0;   // cells with coordinate < 4-s / >= s along the axis
+        for (int v = 0; v < 4; ++v) {
+            if (v < 4 - s) lt |= axis_mask_eq(axis, v);
+            if (v >= s) ge |= axis_mask_eq(axis, v);
+        }
+        r |= (W & lt) << (unit * s);
+        r |= (Wm & ~lt) >> (unit * (4 - s));
+        r |= (W & ge) >> (unit * s);
+        r |= (Wp & ~ge) << (unit * (4 - s));
+    }
+    out[w] = r;
+}
 
 // CTA-wide: move the shared-memory queue to the global queue, dropping the pairs of edges
 // that already hold a deep-hit certificate (all pairs of an edge come from its own CTA, so the
@@ -509,25 +543,103 @@ __device__ __forceinline__ unsigned long long rect_occupancy(const LevelGrid& g,
     return occ;
 }
 
+// Closed-form certificates of one (edge, leaf) pair: 0 = clear miss, 1 = deep hit, 2 = ambiguous
+// (needs the exact narrow phase).  Margin kCertMargin >> MPR tolerance on both sides.
+__device__ __forceinline__ int classify_leaf(const SweepEdge& s, double radius, int shape, const D3& bc, double e) {
+    const double sqrt3 = 1.7320508075688772;
+    const double wx = bc.x - s.c[0], wy = bc.y - s.c[1], wz = bc.z - s.c[2];
+    const double al = wx * s.u[0] + wy * s.u[1] + wz * s.u[2];
+    double g_out2;
+    const double rc = e * sqrt3 * (1.0 + 1e-9);
+    bool deep;
+    if (shape == BGR_SHAPE_CAPSULE) {
+        const double t = fmax(-s.h, fmin(s.h, al));
+        const double ex = wx - t * s.u[0], ey = wy - t * s.u[1], ez = wz - t * s.u[2];
+        const double dseg = sqrt(ex * ex + ey * ey + ez * ez);
+        const double go = dseg - (radius + kCertMargin);
+        g_out2 = go > 0 ? go * go : 0.0;
+        deep = dseg - (radius - kCertMargin) < e;
+    } else {
+        const double ex = wx - al * s.u[0], ey = wy - al * s.u[1], ez = wz - al * s.u[2];
+        const double rho = sqrt(ex * ex + ey * ey + ez * ez);
+        const double dao = fmax(0.0, fabs(al) - (s.h + kCertMargin)), dqo = fmax(0.0, rho - (radius + kCertMargin));
+        g_out2 = dao * dao + dqo * dqo;
+        const double dai = fmax(0.0, fabs(al) - (s.h - kCertMargin)), dqi = fmax(0.0, rho - (radius - kCertMargin));
+        deep = (dai * dai + dqi * dqi < e * e) && s.h > kCertMargin && radius > kCertMargin;
+    }
+    if (g_out2 > rc * rc) return 0;
+    return deep ? 1 : 2;
+}
+
+// CTA-wide exclusive prefix of one int per thread: prefix[t] = sum of val[0..t), prefix[nthreads] = total
+__device__ __forceinline__ void cta_prefix(int val, int* prefix, int* warp_sums) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int inc = val;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(kFull, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < kSweepThreads / 32 ? warp_sums[lane] : 0;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(kFull, w, o);
+            if (lane >= o) w += t;
+        }
+        if (lane < kSweepThreads / 32) warp_sums[lane] = w;
+    }
+    __syncthreads();
+    const int off = warp ? warp_sums[warp - 1] : 0;
+    prefix[tid + 1] = off + inc;
+    if (tid == 0) prefix[0] = 0;
+    __syncthreads();
+}
+
+__device__ __forceinline__ int nth_set_bit64(unsigned long long v, int r) {   // r-th (0-based) set bit
+    const unsigned lo32 = (unsigned)v, hi32 = (unsigned)(v >> 32);
+    const int clo = __popc(lo32);
+    return r < clo ? (int)__fns(lo32, 0, r + 1) : 32 + (int)__fns(hi32, 0, r - clo + 1);
+}
+
+constexpr int kGateSlabs = 128;   // slabs per edge the gate tracks (longer edges run every slab)
+constexpr float kGateSlop = 2e-3f;   // cells: covers the f32 rounding of the gate walk
+
+// The kernel has two item passes over the (edge, slab) work items of the CTA's 256 edges.
+//   gate pass      : an item looks only at the cells the AXIS LINE crosses inside its slab
+//                    (<= 2x2, slope <= 1) in the dilated map (level 0 grown by d = ceil(rm/res)
+//                    cells).  No dilated cell on the whole axis  =>  every leaf is farther than
+//                    rm from every axis point: clear miss, the edge is finished.  An occupied
+//                    level-0 cell on the axis whose leaf holds a deep-hit certificate finishes
+//                    the edge as a hit.  Otherwise the item sets its bit in the edge's slab mask.
+//   rectangle pass : only slabs within d of a set bit (any leaf within rm of the axis has a cell
+//                    in such a slab), of edges that are not finished: the rm-inflated <= 8x8
+//                    rectangle, candidates processed densely as before.
 __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a) {
     __shared__ SweepEdge es[kSweepEdges];
     __shared__ unsigned long long sq[kSqCap];
-    __shared__ int prefix[kSweepEdges + 1];
+    __shared__ unsigned long long emask[kSweepEdges][2];
+    __shared__ int prefix[kSweepEdges + 1];    // over all slabs
+    __shared__ int prefix2[kSweepEdges + 1];   // over the slabs the rectangle pass runs
     __shared__ unsigned eflags[kSweepEdges];
     __shared__ int warp_sums[kSweepThreads / 32];
+    __shared__ int hist[kGateSlabs + 1];
+    __shared__ unsigned char order[kSweepEdges];
     __shared__ int sq_count;
     __shared__ unsigned long long st_cand;
 
     const MapView& m = a.m;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int64_t e0 = (int64_t)blockIdx.x * kSweepEdges;
     const int ne = (int)min((int64_t)kSweepEdges, a.n - e0);
     const double rm = a.radius + kSweepMargin;
+    const bool gate = a.gate_d > 0;
     if (tid == 0) { st_cand = 0; sq_count = 0; }
 
     // ---- phase 0: per-edge frame (thread per edge)
     int myslabs = 0;
     eflags[tid] = 0;
+    emask[tid][0] = emask[tid][1] = 0ull;
     if (tid < ne) {
         const int64_t e = e0 + tid;
         const float p1[3] = {a.p1[3 * e], a.p1[3 * e + 1], a.p1[3 * e + 2]};
@@ -559,47 +671,142 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
         if (!isfinite(s.c[0] + s.c[1] + s.c[2] + s.h)) myslabs = 0;
         es[tid] = s;
     }
-    {
-        int inc = myslabs;
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(kFull, inc, o);
-            if (lane >= o) inc += t;
-        }
-        if (lane == 31) warp_sums[warp] = inc;
-        __syncthreads();
-        if (warp == 0) {
-            int w = lane < kSweepThreads / 32 ? warp_sums[lane] : 0;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(kFull, w, o);
-                if (lane >= o) w += t;
-            }
-            if (lane < kSweepThreads / 32) warp_sums[lane] = w;
-        }
-        __syncthreads();
-        const int off = warp ? warp_sums[warp - 1] : 0;
-        prefix[tid + 1] = off + inc;
-        if (tid == 0) prefix[0] = 0;
-    }
-    __syncthreads();
+    cta_prefix(myslabs, prefix, warp_sums);
     const int total = prefix[kSweepEdges];
-    const double sqrt3 = 1.7320508075688772;
     unsigned long long n_cand = 0;
 
-    for (int w0 = 0; w0 < total; w0 += kSweepThreads) {
+    // ---- gate pass: one thread walks one edge slab by slab (edges ordered by slab count so the
+    // lanes of a warp run similar trip counts); all arithmetic in f32 cell units relative to the
+    // edge's first slab (|values| <= 4096, error < 5e-4 cell, covered by kGateSlop)
+    if (gate) {
+        if (tid <= kGateSlabs) hist[tid] = 0;
+        __syncthreads();
+        const int bin = min(myslabs, kGateSlabs);
+        const int rank = atomicAdd(&hist[bin], 1);
+        __syncthreads();
+        cta_prefix(tid <= kGateSlabs ? hist[tid] : 0, prefix2, warp_sums);
+        order[prefix2[bin] + rank] = (unsigned char)tid;
+        __syncthreads();
+        const int el = order[tid];
+        const int nsl = min(prefix[el + 1] - prefix[el], kGateSlabs);
+        if (nsl > 0) {
+            const SweepEdge& s = es[el];
+            const int ax = s.ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
+            const int i_lo = s.i_lo, dim_a = m.dims[ax], dim_b = m.dims[bx], dim_c = m.dims[cx];
+            const double t_ref = (s.c[ax] - m.origin[ax]) * m.inv_res - (double)i_lo;   // centre, slab units from i_lo
+            const float tlo = (float)((s.xlo - m.origin[ax]) * m.inv_res - (double)i_lo);
+            const float thi = (float)((s.xhi - m.origin[ax]) * m.inv_res - (double)i_lo);
+            const float sbf = (float)s.sb, scf = (float)s.sc;
+            const float beta_b = (float)((s.c[bx] - m.origin[bx]) * m.inv_res - t_ref * s.sb);
+            const float beta_c = (float)((s.c[cx] - m.origin[cx]) * m.inv_res - t_ref * s.sc);
+            const float rm_c = (float)(rm * m.inv_res) + kGateSlop;
+            // brick strides / bit units of the permuted axes
+            const int64_t nbx = a.dil.nb[0], nbxy = (int64_t)a.dil.nb[0] * a.dil.nb[1];
+            const int64_t Si = ax == 0 ? 1 : (ax == 1 ? nbx : nbxy), Sb = bx == 0 ? 1 : nbx, Sc = cx == 1 ? nbx : nbxy;
+            const int Ui = ax == 0 ? 0 : (ax == 1 ? 2 : 4), Ub = bx == 0 ? 0 : 2, Uc = cx == 1 ? 2 : 4;   // log2 of the bit unit
+            // deep-hit certificate on an axis cell needs a ball of radius >= 1e-3 m around the axis
+            // point inside the shape: radius >= 1e-3 and the point >= 0.05 cell from both ends
+            const bool allow_deep = a.radius >= 1e-3 && m.res >= 0.02;
+            unsigned long long ml = 0ull, mh = 0ull;
+            bool deep = false;
+            for (int k = 0; k < nsl; ++k) {
+                const int i = i_lo + k;
+                const float t0 = i == 0 ? (float)k - rm_c : (float)k;
+                const float t1 = i == dim_a - 1 ? (float)(k + 1) + rm_c : (float)(k + 1);
+                const float ta = fminf(fmaxf(t0, tlo), thi), tb = fminf(fmaxf(t1, tlo), thi);
+                const float ba = fmaf(sbf, ta, beta_b), bb = fmaf(sbf, tb, beta_b);
+                const float ca = fmaf(scf, ta, beta_c), cb = fmaf(scf, tb, beta_c);
+                int b0 = (int)floorf(fminf(ba, bb) - kGateSlop), b1 = (int)floorf(fmaxf(ba, bb) + kGateSlop);
+                int c0 = (int)floorf(fminf(ca, cb) - kGateSlop), c1 = (int)floorf(fmaxf(ca, cb) + kGateSlop);
+                // axis points up to d cells outside the map still see the border cells' dilation
+                if (b1 < -a.gate_d || b0 > dim_b - 1 + a.gate_d || c1 < -a.gate_d || c0 > dim_c - 1 + a.gate_d) continue;
+                b0 = min(max(b0, 0), dim_b - 1); b1 = min(max(b1, 0), dim_b - 1);
+                c0 = min(max(c0, 0), dim_c - 1); c1 = min(max(c1, 0), dim_c - 1);
+                bool fired = (b1 - b0 > 1) || (c1 - c0 > 1);   // wider than the 2x2 corner probes: keep the slab
+                if (!fired) {
+                    const int64_t wi = (int64_t)(i >> 2) * Si;
+                    const int bi = (i & 3) << Ui;
+                    const int64_t wb0 = (int64_t)(b0 >> 2) * Sb, wb1 = (int64_t)(b1 >> 2) * Sb;
+                    const int64_t wc0 = (int64_t)(c0 >> 2) * Sc, wc1 = (int64_t)(c1 >> 2) * Sc;
+                    const int bb0 = (b0 & 3) << Ub, bb1 = (b1 & 3) << Ub, bc0 = (c0 & 3) << Uc, bc1 = (c1 & 3) << Uc;
+                    const uint64_t W00 = __ldg(a.dil.bits + wi + wb0 + wc0), W10 = __ldg(a.dil.bits + wi + wb1 + wc0);
+                    const uint64_t W01 = __ldg(a.dil.bits + wi + wb0 + wc1), W11 = __ldg(a.dil.bits + wi + wb1 + wc1);
+                    const uint64_t any = (W00 >> (bi + bb0 + bc0)) | (W10 >> (bi + bb1 + bc0)) | (W01 >> (bi + bb0 + bc1)) |
+                                         (W11 >> (bi + bb1 + bc1));
+                    fired = (any & 1ull) != 0ull;
+                }
+                if (!fired) continue;
+                if (k < 64) ml |= 1ull << k; else mh |= 1ull << (k - 64);
+                if (allow_deep) {
+                    // the cells holding the axis at the two ends of the slab portion (pulled 0.05 cell
+                    // inside the segment): occupied  =>  the shapes overlap by ~radius: deep hit
+                    const float ua = fmaxf(fmaxf(ta, (float)k), tlo + 0.05f), ub = fminf(fminf(tb, (float)(k + 1)), thi - 0.05f);
+                    if (ua <= ub) {
+#pragma unroll
+                        for (int q = 0; q < 2; ++q) {
+                            const float u = q ? ub : ua;
+                            const int jb = (int)floorf(fmaf(sbf, u, beta_b)), jc = (int)floorf(fmaf(scf, u, beta_c));
+                            if (jb >= 0 && jb < dim_b && jc >= 0 && jc < dim_c) {
+                                const uint64_t W = __ldg(m.lv[0].bits + (int64_t)(i >> 2) * Si + (int64_t)(jb >> 2) * Sb + (int64_t)(jc >> 2) * Sc);
+                                deep |= ((W >> (((i & 3) << Ui) + ((jb & 3) << Ub) + ((jc & 3) << Uc))) & 1ull) != 0ull;
+                            }
+                        }
+                        if (deep) break;
+                    }
+                }
+            }
+            if (deep) eflags[el] = F_HIT | F_DEEP;
+            emask[el][0] = ml;
+            emask[el][1] = mh;
+        }
+        __syncthreads();
+        // slabs of the rectangle pass: within d of a fired slab; none for finished edges
+        int cnt = myslabs;
+        if (eflags[tid] & F_DEEP) {
+            cnt = 0;
+        } else if (myslabs <= kGateSlabs) {
+            unsigned long long lo = emask[tid][0], hi = emask[tid][1];
+            unsigned long long rl = lo, rh = hi;
+            for (int sft = 1; sft <= a.gate_d; ++sft) {
+                rl |= (lo << sft) | (lo >> sft) | (hi << (64 - sft));
+                rh |= (hi << sft) | (hi >> sft) | (lo >> (64 - sft));
+            }
+            if (myslabs < 64) { rl &= (1ull << myslabs) - 1ull; rh = 0ull; }
+            else if (myslabs < 128) rh &= (1ull << (myslabs - 64)) - 1ull;
+            emask[tid][0] = rl;
+            emask[tid][1] = rh;
+            cnt = __popcll(rl) + __popcll(rh);
+        }
+        cta_prefix(cnt, prefix2, warp_sums);
+    } else {
+        prefix2[tid + 1] = prefix[tid + 1];
+        if (tid == 0) prefix2[0] = 0;
+        __syncthreads();
+    }
+    const int total2 = prefix2[kSweepEdges];
+
+    // ---- rectangle pass
+    for (int w0 = 0; w0 < total2; w0 += kSweepThreads) {
         // ---- one item per thread: occupancy mask of its rectangle
         const int w = w0 + tid;
         unsigned long long occ = 0;
         int info_a = 0, info_b = 0;   // el | slab<<8 ; b0 | c0<<12
-        if (w < total) {
+        if (w < total2) {
             int lo = 0, hi = kSweepEdges;
             while (hi - lo > 1) {
                 const int mid = (lo + hi) >> 1;
-                if (prefix[mid] <= w) lo = mid; else hi = mid;
+                if (prefix2[mid] <= w) lo = mid; else hi = mid;
             }
             const int el = lo;
             const SweepEdge& s = es[el];
             const int ax = s.ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
-            const int i = s.i_lo + (w - prefix[el]);
+            int k = w - prefix2[el];
+            if (gate && prefix[el + 1] - prefix[el] <= kGateSlabs) {
+                const unsigned long long ml = emask[el][0];
+                const int cl = __popcll(ml);
+                k = k < cl ? nth_set_bit64(ml, k) : 64 + nth_set_bit64(emask[el][1], k - cl);
+            }
+            const int i = s.i_lo + k;
             // the part of the axis segment whose ax coordinate lies in the slab inflated by rm
             // (clamped to the segment: slabs past an end see the end point + the rm margin)
             const double x0 = m.origin[ax] + (double)i * m.res - rm, x1 = m.origin[ax] + (double)(i + 1) * m.res + rm;
@@ -607,17 +814,17 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
             int r0[2], r1[2];
             bool none = false;
 #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                const int b = k ? cx : bx;
-                const double sl = k ? s.sc : s.sb;
+            for (int q = 0; q < 2; ++q) {
+                const int b = q ? cx : bx;
+                const double sl = q ? s.sc : s.sb;
                 const double pa = s.c[b] + xa * sl, pb = s.c[b] + xb * sl;
                 int lo_b = (int)floor((fmin(pa, pb) - rm - m.origin[b]) * m.inv_res);
                 int hi_b = (int)floor((fmax(pa, pb) + rm - m.origin[b]) * m.inv_res);
                 lo_b = max(lo_b, 0);
                 hi_b = min(hi_b, m.dims[b] - 1);
                 hi_b = min(hi_b, lo_b + kRectMax - 1);   // host guarantees the hull fits kRectMax cells
-                r0[k] = lo_b;
-                r1[k] = hi_b;
+                r0[q] = lo_b;
+                r1[q] = hi_b;
                 none |= lo_b > hi_b;
             }
             if (!none) {
@@ -651,10 +858,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
             unsigned long long rec = 0;
             int el = 0;
             if (active) {
-                const int rank = j - (s_incl - s_cnt);
-                const unsigned lo32 = (unsigned)s_occ, hi32 = (unsigned)(s_occ >> 32);
-                const int clo = __popc(lo32);
-                const int bit = rank < clo ? (int)__fns(lo32, 0, rank + 1) : 32 + (int)__fns(hi32, 0, rank - clo + 1);
+                const int bit = nth_set_bit64(s_occ, j - (s_incl - s_cnt));
                 el = s_a & 255;
                 const int i = s_a >> 8, b0 = s_b & 4095, c0 = s_b >> 12;
                 const SweepEdge& s = es[el];
@@ -670,31 +874,10 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                     D3 bc;
                     double e;
                     leaf_box(m, L, l[0], l[1], l[2], bc, e);
-                    const double wx = bc.x - s.c[0], wy = bc.y - s.c[1], wz = bc.z - s.c[2];
-                    const double al = wx * s.u[0] + wy * s.u[1] + wz * s.u[2];
-                    double g_out2, g_in, rc = e * sqrt3 * (1.0 + 1e-9);
-                    bool deep;
-                    if (a.shape == BGR_SHAPE_CAPSULE) {
-                        const double t = fmax(-s.h, fmin(s.h, al));
-                        const double ex = wx - t * s.u[0], ey = wy - t * s.u[1], ez = wz - t * s.u[2];
-                        const double dseg = sqrt(ex * ex + ey * ey + ez * ez);
-                        const double go = dseg - (a.radius + kCertMargin);
-                        g_out2 = go > 0 ? go * go : 0.0;
-                        g_in = dseg - (a.radius - kCertMargin);
-                        deep = g_in < e;
-                    } else {
-                        const double ex = wx - al * s.u[0], ey = wy - al * s.u[1], ez = wz - al * s.u[2];
-                        const double rho = sqrt(ex * ex + ey * ey + ez * ez);
-                        const double dao = fmax(0.0, fabs(al) - (s.h + kCertMargin)), dqo = fmax(0.0, rho - (a.radius + kCertMargin));
-                        g_out2 = dao * dao + dqo * dqo;
-                        const double dai = fmax(0.0, fabs(al) - (s.h - kCertMargin)), dqi = fmax(0.0, rho - (a.radius - kCertMargin));
-                        deep = (dai * dai + dqi * dqi < e * e) && s.h > kCertMargin && a.radius > kCertMargin;
-                    }
-                    if (g_out2 > rc * rc) {
-                        // clear miss
-                    } else if (deep) {
+                    const int cls = classify_leaf(s, a.radius, a.shape, bc, e);
+                    if (cls == 1) {
                         atomicOr(&eflags[el], F_HIT | F_DEEP);
-                    } else {
+                    } else if (cls == 2) {
                         ambiguous = !(eflags[el] & F_DEEP);
                         rec = ((unsigned long long)el << 40) | ((unsigned long long)L << 36) |
                               ((unsigned long long)l[0] << 24) | ((unsigned long long)l[1] << 12) | (unsigned long long)l[2];
@@ -741,6 +924,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
     if (a.stats && tid == 0) {
         atomicAdd(a.stats + 0, (unsigned long long)total);
         atomicAdd(a.stats + 1, st_cand);
+        atomicAdd(a.stats + 4, (unsigned long long)total2);
     }
 }
 
@@ -823,6 +1007,10 @@ struct bgr_map {
     DevBuf<unsigned long long> stats;
     DevBuf<unsigned> eflags, qctl;
     DevBuf<NarrowRec> queue;
+    DevBuf<uint64_t> dil, dil_tmp;     // level 0 dilated by dil_d cells: the sweep gate (rebuilt lazily)
+    int dil_d = 0;
+    bool dil_dirty = true;
+    bool gate_on = true;
     uint64_t last_stats[4] = {0, 0, 0, 0};
     cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // kernel boundaries of the last collide_edges (timing on)
     bool timing = false;
@@ -902,12 +1090,32 @@ void keys_of(const std::vector<LeafRec>& recs, std::vector<uint64_t>& keys) {
 }
 
 int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
+    h->dil_dirty = true;
     if (recs.empty()) return BGR_OK;
     BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
     BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
     raster_kernel<<<(unsigned)div_up((int64_t)recs.size(), 256), 256, 0, h->stream>>>(h->view(), h->recs.p, (int64_t)recs.size(), set);
     BGR_LAUNCH_CHECK();
     BGR_CUDA(cudaStreamSynchronize(h->stream));   // recs is a host temporary
+    return BGR_OK;
+}
+
+// level 0 grown by d cells in every direction (three separable brick-word passes); lazily
+// rebuilt after a map change or when the query radius asks for another d
+int ensure_dilated(bgr_map* h, int d) {
+    if (!h->dil_dirty && h->dil_d == d) return BGR_OK;
+    const int64_t w = h->words[0];
+    BGR_CHECK(h->dil.reserve(w, h->stream, false));
+    BGR_CHECK(h->dil_tmp.reserve(w, h->stream, false));
+    const unsigned nblk = (unsigned)div_up(w, 256);
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->bits[0].p, h->dil.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 0, d);
+    BGR_LAUNCH_CHECK();
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil.p, h->dil_tmp.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 1, d);
+    BGR_LAUNCH_CHECK();
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil_tmp.p, h->dil.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 2, d);
+    BGR_LAUNCH_CHECK();
+    h->dil_d = d;
+    h->dil_dirty = false;
     return BGR_OK;
 }
 
@@ -1068,6 +1276,12 @@ int bgr_map_collide_spheres(bgr_map* h, const float* c, int64_t n, double radius
     return BGR_OK;
 }
 
+// fast path needs the swept hull of one slab to fit a kRectMax x kRectMax cell rectangle:
+// extent <= res (slope <= 1 on the dominant axis) + 2*(radius+margin) + 2*(radius+margin)
+static bool fast_ok(const bgr_map* h, double radius) {
+    return (h->res + 4.0 * (radius + kSweepMargin)) / h->res + 1.0 <= (double)kRectMax;
+}
+
 int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, int64_t n, double radius,
                               int shape, uint8_t* d_hit, uint8_t* d_band) {
     BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_edges arguments");
@@ -1075,18 +1289,21 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     BGR_ARG(radius + kSweepMargin < 64 * h->res, "radius too large for the sweep (>= 64 cells)");
     BGR_ARG(n < ((int64_t)1 << 31), "too many edges in one call");
     if (n == 0) return BGR_OK;
-    BGR_CHECK(h->stats.reserve(4, h->stream, false));
+    BGR_CHECK(h->stats.reserve(6, h->stream, false));
     BGR_CHECK(h->eflags.reserve(n, h->stream, false));
     BGR_CHECK(h->qctl.reserve(2, h->stream, false));
-    BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 4 * sizeof(unsigned long long), h->stream));
+    BGR_CUDA(cudaMemsetAsync(h->stats.p, 0, 6 * sizeof(unsigned long long), h->stream));
     BGR_CUDA(cudaMemsetAsync(h->qctl.p, 0, 2 * sizeof(unsigned), h->stream));
     EdgeArgs ma;
     ma.m = h->view();
     ma.p1 = d_p1; ma.p2 = d_p2; ma.n = n; ma.radius = radius; ma.shape = shape;
     ma.want_band = d_band != nullptr; ma.gflags = h->eflags.p; ma.stats = h->stats.p;
-    // fast path needs the swept hull of one slab to fit a kRectMax x kRectMax cell rectangle:
-    // extent <= res (slope <= 1 on the dominant axis) + 2*(radius+margin) + 2*(radius+margin)
-    const bool fast = (h->res + 4.0 * (radius + kSweepMargin)) / h->res + 1.0 <= (double)kRectMax;
+    const bool fast = fast_ok(h, radius);
+    // sweep gate: level 0 dilated by d = ceil(rm / res) cells (built outside the timed kernels:
+    // it belongs to the map, not to the query batch)
+    const int gate_d = (int)std::ceil((radius + kSweepMargin) / h->res + 1e-9);
+    const bool gate = fast_ok(h, radius) && h->gate_on && gate_d >= 1 && gate_d <= 3;
+    if (gate) BGR_CHECK(ensure_dilated(h, gate_d));
     if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[0], h->stream));
     if (fast) {
         const int64_t cap = std::max<int64_t>(1 << 16, 4 * n);
@@ -1097,6 +1314,9 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.want_band = ma.want_band; a.gflags = h->eflags.p;
         a.queue = h->queue.p; a.queue_cap = (unsigned)std::min<int64_t>(cap, 0x7fffffff);
         a.qctl = h->qctl.p; a.stats = h->stats.p; a.hit = d_hit; a.band = d_band;
+        a.gate_d = gate ? gate_d : 0;
+        a.dil.bits = gate ? h->dil.p : nullptr;
+        for (int ax = 0; ax < 3; ++ax) a.dil.nb[ax] = h->nb[0][ax];
         edges_sweep_kernel<<<(unsigned)div_up(n, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
         BGR_LAUNCH_CHECK();
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
@@ -1161,12 +1381,31 @@ int bgr_map_last_stats(bgr_map* h, uint64_t out[4]) {
     return BGR_OK;
 }
 
+int bgr_map_set_gate(bgr_map* h, int on) {
+    BGR_ARG(h != nullptr, "null map");
+    h->gate_on = on != 0;
+    return BGR_OK;
+}
+
+int bgr_map_last_gate_stats(bgr_map* h, uint64_t out[2]) {
+    BGR_ARG(h != nullptr && out, "bad arguments");
+    out[0] = 0;
+    out[1] = (uint64_t)(h->dil_dirty ? 0 : h->dil_d);
+    if (!h->stats.p || h->stats.cap < 6) return BGR_OK;
+    unsigned long long s = 0;
+    BGR_CUDA(cudaMemcpyAsync(&s, h->stats.p + 4, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    out[0] = s;
+    return BGR_OK;
+}
+
 int bgr_map_destroy(bgr_map* h) {
     if (!h) return BGR_OK;
     cudaStreamSynchronize(h->stream);
     for (int L = 0; L <= kMaxLevel; ++L) h->bits[L].release();
     h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
     h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
+    h->dil.release(); h->dil_tmp.release();
     for (int i = 0; i < 5; ++i)
         if (h->tev[i]) cudaEventDestroy(h->tev[i]);
     delete h;

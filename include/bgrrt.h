@@ -176,6 +176,15 @@ int bgr_map_collide_edges_dev(bgr_map* map, const float* d_p1_3xM, const float* 
 /* counters of the last collide_edges call: [0] work items (edge,slab), [1] occupied
  * candidate voxels, [2] exact narrow-phase tests, [3] narrow-phase iteration-cap events */
 int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
+/* sweep gate of collide_edges (isLineValid MS:385-471 has no counterpart: the reference loops
+ * over every leaf): level 0 dilated by d = ceil((radius + 1e-4) / res) cells decides, from the
+ * cells the edge's AXIS crosses alone, the edges that are certainly clear and (with a deep-hit
+ * certificate on an axis cell) certainly colliding; only slabs next to a dilated cell run the
+ * rectangle phase.  Results are identical with the gate off (set_gate(map, 0): measurement /
+ * test aid).  last_gate_stats: [0] (edge,slab) items that ran the rectangle phase in the last
+ * call, [1] d of the dilated map currently built (0 = none). */
+int bgr_map_set_gate(bgr_map* map, int on);
+int bgr_map_last_gate_stats(bgr_map* map, uint64_t out[2]);
 /* measurement aid: with timing on, collide_edges records CUDA events between its kernels on the
  * map's stream; last_kernel_ms returns the durations of the last call: [0] edges_sweep_kernel,
  * [1] edges_narrow_kernel, [2] collide_edges_kernel (general / overflow path), [3] finalize */

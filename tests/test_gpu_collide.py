@@ -215,6 +215,48 @@ def test_edges_large_map_properties(bgr, oracle):
     assert not ((oh != h[sub]) & (b[sub] == 0)).any()
 
 
+@pytest.mark.parametrize("shape", [0, 1])
+@pytest.mark.parametrize("radius", [0.03, 0.0499, 0.07])
+def test_edges_gate_is_exact(bgr, oracle, radius, shape):
+    """the dilated-map gate of the sweep (d = 1 and 2 cells here) never changes hit / in_band:
+    gate on == gate off, including edges that leave the map, hug its border, are shorter than
+    a cell or longer than the 128 slabs the gate tracks, and after an incremental map update."""
+    occ = oracle.make_map(192, seed=12, n_walls=3, wall_thick=3, door_cells=5)
+    boxes = oracle.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (192, 192, 192))
+    m.set_boxes(boxes)
+    n = 60000
+    p1, p2 = _edges(oracle, occ, n, 91, lo=0.01, hi=4.0, extent=9.6)
+    mt = oracle.MT(92)
+    # a third of the edges start up to 0.1 m outside the map / on its border planes
+    shift = (mt.real(3 * n).reshape(n, 3) * 0.25 - 0.1).astype(np.float32)
+    side = mt.real(n)
+    k = n // 3
+    p1[:k] = np.where(side[:k, None] < 0.5, shift[:k], 9.6 - shift[:k] * 0.5) * np.array([1, 0, 0], np.float32) + p1[:k] * np.array([0, 1, 1], np.float32)
+    # very long edges (> 128 slabs)
+    p2[k:k + 2000] = (p1[k:k + 2000] + (p2[k:k + 2000] - p1[k:k + 2000]) * 3.0).astype(np.float32)
+    m.set_gate(True)
+    h1, b1 = m.collide_edges(p1, p2, radius, shape)
+    g = m.gate_stats()
+    st = m.last_stats()
+    assert g["dilation_cells"] in {0.03: (1,), 0.0499: (1, 2), 0.07: (2,)}[radius]
+    assert 0 < g["rect_items"] < st["work_items"]
+    m.set_gate(False)
+    h0, b0 = m.collide_edges(p1, p2, radius, shape)
+    assert m.gate_stats()["rect_items"] == m.last_stats()["work_items"]
+    assert np.array_equal(h1, h0) and np.array_equal(b1, b0)
+    assert 0.05 < h0.mean() < 0.95
+    # incremental update: the dilated map must follow the level-0 change
+    add = np.array([[4.825 + 0.05 * i, 4.825, 4.825, 0.05, 1.0, 0.5] for i in range(4)])
+    rem = boxes[:5000]
+    m.update_boxes(add, rem)
+    h0u, b0u = m.collide_edges(p1, p2, radius, shape)
+    m.set_gate(True)
+    h1u, b1u = m.collide_edges(p1, p2, radius, shape)
+    assert np.array_equal(h1u, h0u) and np.array_equal(b1u, b0u)
+    assert not np.array_equal(h0u, h0)
+
+
 def test_octomap_ingestion_and_refresh(bgr, oracle):
     """serialised Octomap (full message data, MS:279) -> toBoxes rows -> bitmap; then a map refresh
     that rasterises only the changed leaves (bgr_map_refresh_boxes)."""
