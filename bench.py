@@ -275,6 +275,7 @@ def run_ours(args):
             stream.synchronize()
             edge_launches = L.bgr_launch_count() - l1
             stats = omap.last_stats()
+            stats.update(omap.gate_stats())
             edge_ms = max_over_ranks(timed_steps(torch, stream, edge_step, args.steps, args.warmup, flush, barrier))
             p1h, p2h = torch.from_numpy(p1).pin_memory(), torch.from_numpy(p2).pin_memory()
             hh, bh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()

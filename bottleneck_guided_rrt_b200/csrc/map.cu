@@ -394,7 +394,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
 constexpr int kSweepThreads = 256;
 constexpr int kSweepEdges = 256;
 constexpr int kRectMax = 8;
-constexpr int kSqCap = 2048;      // shared-memory queue of ambiguous (edge, leaf) pairs per CTA
+constexpr int kSqCap = 1024;      // shared-memory queue of ambiguous (edge, leaf) pairs per CTA
 
 struct SweepEdge {
     double c[3], u[3], h;
@@ -604,6 +604,11 @@ __device__ __forceinline__ int nth_set_bit64(unsigned long long v, int r) {   //
 
 constexpr int kGateSlabs = 128;   // slabs per edge the gate tracks (longer edges run every slab)
 constexpr float kGateSlop = 2e-3f;   // cells: covers the f32 rounding of the gate walk
+constexpr int kGateSeg = 8;           // slabs one thread walks (64 % kGateSeg == 0)
+struct GateEdge {                     // the axis line in cell units relative to the edge's first slab
+    float tlo, thi;                   // extent of the segment along ax
+    float sb, sc, beta_b, beta_c;     // lateral cell coordinate = beta + slope * t
+};
 
 // The kernel has two item passes over the (edge, slab) work items of the CTA's 256 edges.
 //   gate pass      : an item looks only at the cells the AXIS LINE crosses inside its slab
@@ -615,7 +620,7 @@ constexpr float kGateSlop = 2e-3f;   // cells: covers the f32 rounding of the ga
 //   rectangle pass : only slabs within d of a set bit (any leaf within rm of the axis has a cell
 //                    in such a slab), of edges that are not finished: the rm-inflated <= 8x8
 //                    rectangle, candidates processed densely as before.
-__global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a) {
+__global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args a) {
     __shared__ SweepEdge es[kSweepEdges];
     __shared__ unsigned long long sq[kSqCap];
     __shared__ unsigned long long emask[kSweepEdges][2];
@@ -623,8 +628,7 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
     __shared__ int prefix2[kSweepEdges + 1];   // over the slabs the rectangle pass runs
     __shared__ unsigned eflags[kSweepEdges];
     __shared__ int warp_sums[kSweepThreads / 32];
-    __shared__ int hist[kGateSlabs + 1];
-    __shared__ unsigned char order[kSweepEdges];
+    __shared__ GateEdge ge[kSweepEdges];
     __shared__ int sq_count;
     __shared__ unsigned long long st_cand;
 
@@ -670,52 +674,62 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
         myslabs = max(0, hi - lo + 1);
         if (!isfinite(s.c[0] + s.c[1] + s.c[2] + s.h)) myslabs = 0;
         es[tid] = s;
+        if (gate) {
+            GateEdge g;
+            const double t_ref = (s.c[s.ax] - m.origin[s.ax]) * m.inv_res - (double)lo;   // centre, slab units from i_lo
+            g.tlo = (float)((s.xlo - m.origin[s.ax]) * m.inv_res - (double)lo);
+            g.thi = (float)((s.xhi - m.origin[s.ax]) * m.inv_res - (double)lo);
+            g.sb = (float)s.sb;
+            g.sc = (float)s.sc;
+            g.beta_b = (float)((s.c[bx] - m.origin[bx]) * m.inv_res - t_ref * s.sb);
+            g.beta_c = (float)((s.c[cx] - m.origin[cx]) * m.inv_res - t_ref * s.sc);
+            ge[tid] = g;
+        }
     }
     cta_prefix(myslabs, prefix, warp_sums);
     const int total = prefix[kSweepEdges];
     unsigned long long n_cand = 0;
 
-    // ---- gate pass: one thread walks one edge slab by slab (edges ordered by slab count so the
-    // lanes of a warp run similar trip counts); all arithmetic in f32 cell units relative to the
-    // edge's first slab (|values| <= 4096, error < 5e-4 cell, covered by kGateSlop)
+    // ---- gate pass: items = (edge, segment of kGateSeg consecutive slabs), one per thread, walked
+    // serially in f32 cell units relative to the edge's first slab (|values| <= 4096, error
+    // < 5e-4 cell, covered by kGateSlop).  Short equal-length chains keep the lanes of a warp in
+    // step and the CTA barrier that follows short.
     if (gate) {
-        if (tid <= kGateSlabs) hist[tid] = 0;
-        __syncthreads();
-        const int bin = min(myslabs, kGateSlabs);
-        const int rank = atomicAdd(&hist[bin], 1);
-        __syncthreads();
-        cta_prefix(tid <= kGateSlabs ? hist[tid] : 0, prefix2, warp_sums);
-        order[prefix2[bin] + rank] = (unsigned char)tid;
-        __syncthreads();
-        const int el = order[tid];
-        const int nsl = min(prefix[el + 1] - prefix[el], kGateSlabs);
-        if (nsl > 0) {
-            const SweepEdge& s = es[el];
-            const int ax = s.ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
-            const int i_lo = s.i_lo, dim_a = m.dims[ax], dim_b = m.dims[bx], dim_c = m.dims[cx];
-            const double t_ref = (s.c[ax] - m.origin[ax]) * m.inv_res - (double)i_lo;   // centre, slab units from i_lo
-            const float tlo = (float)((s.xlo - m.origin[ax]) * m.inv_res - (double)i_lo);
-            const float thi = (float)((s.xhi - m.origin[ax]) * m.inv_res - (double)i_lo);
-            const float sbf = (float)s.sb, scf = (float)s.sc;
-            const float beta_b = (float)((s.c[bx] - m.origin[bx]) * m.inv_res - t_ref * s.sb);
-            const float beta_c = (float)((s.c[cx] - m.origin[cx]) * m.inv_res - t_ref * s.sc);
-            const float rm_c = (float)(rm * m.inv_res) + kGateSlop;
-            // brick strides / bit units of the permuted axes
-            const int64_t nbx = a.dil.nb[0], nbxy = (int64_t)a.dil.nb[0] * a.dil.nb[1];
-            const int64_t Si = ax == 0 ? 1 : (ax == 1 ? nbx : nbxy), Sb = bx == 0 ? 1 : nbx, Sc = cx == 1 ? nbx : nbxy;
-            const int Ui = ax == 0 ? 0 : (ax == 1 ? 2 : 4), Ub = bx == 0 ? 0 : 2, Uc = cx == 1 ? 2 : 4;   // log2 of the bit unit
-            // deep-hit certificate on an axis cell needs a ball of radius >= 1e-3 m around the axis
-            // point inside the shape: radius >= 1e-3 and the point >= 0.05 cell from both ends
-            const bool allow_deep = a.radius >= 1e-3 && m.res >= 0.02;
-            unsigned long long ml = 0ull, mh = 0ull;
+        const int nseg_mine = (min(myslabs, kGateSlabs) + kGateSeg - 1) / kGateSeg;
+        cta_prefix(nseg_mine, prefix2, warp_sums);
+        const int total_seg = prefix2[kSweepEdges];
+        const unsigned nbx = (unsigned)a.dil.nb[0], nbxy = (unsigned)a.dil.nb[0] * (unsigned)a.dil.nb[1];
+        // deep-hit certificate on an axis cell needs a ball of radius >= 1e-3 m around the axis
+        // point inside the shape: radius >= 1e-3 and the point >= 0.05 cell (res >= 0.02) from both ends
+        const bool allow_deep = a.radius >= 1e-3 && m.res >= 0.02;
+        const float rm_c = (float)(rm * m.inv_res) + kGateSlop;
+        for (int w0 = 0; w0 < total_seg; w0 += kSweepThreads) {
+            const int w = w0 + tid;
+            if (w >= total_seg) break;
+            int lo = 0, hi = kSweepEdges;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (prefix2[mid] <= w) lo = mid; else hi = mid;
+            }
+            const int el = lo;
+            if (eflags[el] & F_DEEP) continue;
+            const int k0 = (w - prefix2[el]) * kGateSeg;
+            const int k1 = min(k0 + kGateSeg, min(prefix[el + 1] - prefix[el], kGateSlabs));
+            const GateEdge g = ge[el];
+            const int ax = es[el].ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
+            const int i_lo = es[el].i_lo, dim_a = m.dims[ax], dim_b = m.dims[bx], dim_c = m.dims[cx];
+            // brick strides / log2 bit units of the permuted axes
+            const unsigned Si = ax == 0 ? 1u : (ax == 1 ? nbx : nbxy), Sb = bx == 0 ? 1u : nbx, Sc = cx == 1 ? nbx : nbxy;
+            const int Ui = ax == 0 ? 0 : (ax == 1 ? 2 : 4), Ub = bx == 0 ? 0 : 2, Uc = cx == 1 ? 2 : 4;
+            unsigned fired_mask = 0;
             bool deep = false;
-            for (int k = 0; k < nsl; ++k) {
+            for (int k = k0; k < k1; ++k) {
                 const int i = i_lo + k;
                 const float t0 = i == 0 ? (float)k - rm_c : (float)k;
                 const float t1 = i == dim_a - 1 ? (float)(k + 1) + rm_c : (float)(k + 1);
-                const float ta = fminf(fmaxf(t0, tlo), thi), tb = fminf(fmaxf(t1, tlo), thi);
-                const float ba = fmaf(sbf, ta, beta_b), bb = fmaf(sbf, tb, beta_b);
-                const float ca = fmaf(scf, ta, beta_c), cb = fmaf(scf, tb, beta_c);
+                const float ta = fminf(fmaxf(t0, g.tlo), g.thi), tb = fminf(fmaxf(t1, g.tlo), g.thi);
+                const float ba = fmaf(g.sb, ta, g.beta_b), bb = fmaf(g.sb, tb, g.beta_b);
+                const float ca = fmaf(g.sc, ta, g.beta_c), cb = fmaf(g.sc, tb, g.beta_c);
                 int b0 = (int)floorf(fminf(ba, bb) - kGateSlop), b1 = (int)floorf(fmaxf(ba, bb) + kGateSlop);
                 int c0 = (int)floorf(fminf(ca, cb) - kGateSlop), c1 = (int)floorf(fmaxf(ca, cb) + kGateSlop);
                 // axis points up to d cells outside the map still see the border cells' dilation
@@ -723,41 +737,37 @@ __global__ void __launch_bounds__(kSweepThreads) edges_sweep_kernel(Edge2Args a)
                 b0 = min(max(b0, 0), dim_b - 1); b1 = min(max(b1, 0), dim_b - 1);
                 c0 = min(max(c0, 0), dim_c - 1); c1 = min(max(c1, 0), dim_c - 1);
                 bool fired = (b1 - b0 > 1) || (c1 - c0 > 1);   // wider than the 2x2 corner probes: keep the slab
+                const unsigned wi = (unsigned)(i >> 2) * Si;
+                const int bi = (i & 3) << Ui;
                 if (!fired) {
-                    const int64_t wi = (int64_t)(i >> 2) * Si;
-                    const int bi = (i & 3) << Ui;
-                    const int64_t wb0 = (int64_t)(b0 >> 2) * Sb, wb1 = (int64_t)(b1 >> 2) * Sb;
-                    const int64_t wc0 = (int64_t)(c0 >> 2) * Sc, wc1 = (int64_t)(c1 >> 2) * Sc;
+                    const unsigned wb0 = (unsigned)(b0 >> 2) * Sb, wb1 = (unsigned)(b1 >> 2) * Sb;
+                    const unsigned wc0 = (unsigned)(c0 >> 2) * Sc, wc1 = (unsigned)(c1 >> 2) * Sc;
                     const int bb0 = (b0 & 3) << Ub, bb1 = (b1 & 3) << Ub, bc0 = (c0 & 3) << Uc, bc1 = (c1 & 3) << Uc;
-                    const uint64_t W00 = __ldg(a.dil.bits + wi + wb0 + wc0), W10 = __ldg(a.dil.bits + wi + wb1 + wc0);
-                    const uint64_t W01 = __ldg(a.dil.bits + wi + wb0 + wc1), W11 = __ldg(a.dil.bits + wi + wb1 + wc1);
+                    const uint64_t W00 = __ldg(a.dil.bits + (wi + wb0 + wc0)), W10 = __ldg(a.dil.bits + (wi + wb1 + wc0));
+                    const uint64_t W01 = __ldg(a.dil.bits + (wi + wb0 + wc1)), W11 = __ldg(a.dil.bits + (wi + wb1 + wc1));
                     const uint64_t any = (W00 >> (bi + bb0 + bc0)) | (W10 >> (bi + bb1 + bc0)) | (W01 >> (bi + bb0 + bc1)) |
                                          (W11 >> (bi + bb1 + bc1));
                     fired = (any & 1ull) != 0ull;
                 }
                 if (!fired) continue;
-                if (k < 64) ml |= 1ull << k; else mh |= 1ull << (k - 64);
+                fired_mask |= 1u << (k - k0);
                 if (allow_deep) {
-                    // the cells holding the axis at the two ends of the slab portion (pulled 0.05 cell
-                    // inside the segment): occupied  =>  the shapes overlap by ~radius: deep hit
-                    const float ua = fmaxf(fmaxf(ta, (float)k), tlo + 0.05f), ub = fminf(fminf(tb, (float)(k + 1)), thi - 0.05f);
+                    // the cell holding the axis at the middle of the slab portion (kept 0.05 cell inside
+                    // the segment and inside the slab): occupied => the shapes overlap by ~radius: deep hit
+                    const float ua = fmaxf(fmaxf(ta, (float)k), g.tlo + 0.05f), ub = fminf(fminf(tb, (float)(k + 1)), g.thi - 0.05f);
                     if (ua <= ub) {
-#pragma unroll
-                        for (int q = 0; q < 2; ++q) {
-                            const float u = q ? ub : ua;
-                            const int jb = (int)floorf(fmaf(sbf, u, beta_b)), jc = (int)floorf(fmaf(scf, u, beta_c));
-                            if (jb >= 0 && jb < dim_b && jc >= 0 && jc < dim_c) {
-                                const uint64_t W = __ldg(m.lv[0].bits + (int64_t)(i >> 2) * Si + (int64_t)(jb >> 2) * Sb + (int64_t)(jc >> 2) * Sc);
-                                deep |= ((W >> (((i & 3) << Ui) + ((jb & 3) << Ub) + ((jc & 3) << Uc))) & 1ull) != 0ull;
-                            }
+                        const float um = 0.5f * (ua + ub);
+                        const int jb = (int)floorf(fmaf(g.sb, um, g.beta_b)), jc = (int)floorf(fmaf(g.sc, um, g.beta_c));
+                        if (jb >= 0 && jb < dim_b && jc >= 0 && jc < dim_c) {
+                            const uint64_t W = __ldg(m.lv[0].bits + (wi + (unsigned)(jb >> 2) * Sb + (unsigned)(jc >> 2) * Sc));
+                            deep = ((W >> (bi + ((jb & 3) << Ub) + ((jc & 3) << Uc))) & 1ull) != 0ull;
                         }
                         if (deep) break;
                     }
                 }
             }
-            if (deep) eflags[el] = F_HIT | F_DEEP;
-            emask[el][0] = ml;
-            emask[el][1] = mh;
+            if (deep) atomicOr(&eflags[el], F_HIT | F_DEEP);
+            else if (fired_mask) atomicOr(&emask[el][k0 >> 6], (unsigned long long)fired_mask << (k0 & 63));
         }
         __syncthreads();
         // slabs of the rectangle pass: within d of a fired slab; none for finished edges
