@@ -141,6 +141,7 @@ struct EdgeArgs {
     int shape;
     int want_band;
     int only_overflow;           // process only edges whose narrow-phase queue overflowed
+    const unsigned* n_overflow;  // with only_overflow: number of such edges (0: every CTA returns at once)
     unsigned* gflags;            // per-edge result flags (F_*), consumed by edges_finalize_kernel
     unsigned long long* stats;   // [4]
 };
@@ -174,6 +175,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t e0 = (int64_t)blockIdx.x * kEdgesPerCta;
     const int ne = (int)min((int64_t)kEdgesPerCta, a.n - e0);
+    if (a.only_overflow && a.n_overflow && __ldg(a.n_overflow) == 0u) return;
     const bool mine = tid < ne && (!a.only_overflow || (a.gflags[e0 + tid] & F_OVERFLOW));
     if (!__syncthreads_or(mine)) return;
     if (tid == 0) { qcount = 0; st_items = st_cand = st_mpr = st_cap = 0; }
@@ -544,31 +546,61 @@ __device__ __forceinline__ unsigned long long rect_occupancy(const LevelGrid& g,
 }
 
 // Closed-form certificates of one (edge, leaf) pair: 0 = clear miss, 1 = deep hit, 2 = ambiguous
-// (needs the exact narrow phase).  Margin kCertMargin >> MPR tolerance on both sides.
+// (needs the exact narrow phase).  Both certificates hold a margin kCertMargin >> MPR tolerance:
+//   clear miss : a unit direction n separates the shapes by more than the margin (support
+//                functions of the cylinder / capsule and of the box along n); tried for the box
+//                face normals, the cylinder axis and the direction between the closest points
+//                found by a few alternating projections (axis segment <-> box);
+//   deep hit   : a point of the box lies inside the shape shrunk by the margin, so the shapes
+//                overlap by at least the margin.
+// Any n and any box point give a valid certificate; the projections only pick good candidates.
 __device__ __forceinline__ int classify_leaf(const SweepEdge& s, double radius, int shape, const D3& bc, double e) {
-    const double sqrt3 = 1.7320508075688772;
-    const double wx = bc.x - s.c[0], wy = bc.y - s.c[1], wz = bc.z - s.c[2];
-    const double al = wx * s.u[0] + wy * s.u[1] + wz * s.u[2];
-    double g_out2;
-    const double rc = e * sqrt3 * (1.0 + 1e-9);
-    bool deep;
-    if (shape == BGR_SHAPE_CAPSULE) {
-        const double t = fmax(-s.h, fmin(s.h, al));
-        const double ex = wx - t * s.u[0], ey = wy - t * s.u[1], ez = wz - t * s.u[2];
-        const double dseg = sqrt(ex * ex + ey * ey + ez * ez);
-        const double go = dseg - (radius + kCertMargin);
-        g_out2 = go > 0 ? go * go : 0.0;
-        deep = dseg - (radius - kCertMargin) < e;
-    } else {
-        const double ex = wx - al * s.u[0], ey = wy - al * s.u[1], ez = wz - al * s.u[2];
-        const double rho = sqrt(ex * ex + ey * ey + ez * ez);
-        const double dao = fmax(0.0, fabs(al) - (s.h + kCertMargin)), dqo = fmax(0.0, rho - (radius + kCertMargin));
-        g_out2 = dao * dao + dqo * dqo;
-        const double dai = fmax(0.0, fabs(al) - (s.h - kCertMargin)), dqi = fmax(0.0, rho - (radius - kCertMargin));
-        deep = (dai * dai + dqi * dqi < e * e) && s.h > kCertMargin && radius > kCertMargin;
+    const double mg = kCertMargin;
+    const bool caps = shape == BGR_SHAPE_CAPSULE;
+    const double w[3] = {bc.x - s.c[0], bc.y - s.c[1], bc.z - s.c[2]};
+    const double u[3] = {s.u[0], s.u[1], s.u[2]};
+    // box face normals
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double supp = s.h * fabs(u[k]) + (caps ? radius : radius * sqrt(fmax(0.0, 1.0 - u[k] * u[k])));
+        if (fabs(w[k]) - supp - e > mg) return 0;
     }
-    if (g_out2 > rc * rc) return 0;
-    return deep ? 1 : 2;
+    // cylinder axis
+    const double al = w[0] * u[0] + w[1] * u[1] + w[2] * u[2];
+    const double box_u = e * (fabs(u[0]) + fabs(u[1]) + fabs(u[2]));
+    if (fabs(al) - s.h - (caps ? radius : 0.0) - box_u > mg) return 0;
+    // alternating projections between the axis segment (pulled 2 margins inside the caps, so an
+    // axis point inside the box certifies a flat-capped cylinder too) and the box
+    const double hs = fmax(0.0, s.h - 2.0 * mg);
+    double t = fmax(-hs, fmin(hs, al));
+    double q[3];
+#pragma unroll
+    for (int it = 0; it < 3; ++it) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) q[k] = fmax(w[k] - e, fmin(w[k] + e, t * u[k]));
+        t = fmax(-hs, fmin(hs, q[0] * u[0] + q[1] * u[1] + q[2] * u[2]));
+    }
+    const double d[3] = {q[0] - t * u[0], q[1] - t * u[1], q[2] - t * u[2]};
+    const double dn2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+    const double rin = radius - mg;
+    if (radius > mg && s.h > 2.0 * mg) {
+        if (caps) {
+            if (dn2 < rin * rin) return 1;
+        } else {
+            const double aq = q[0] * u[0] + q[1] * u[1] + q[2] * u[2];
+            const double ex = q[0] - aq * u[0], ey = q[1] - aq * u[1], ez = q[2] - aq * u[2];
+            if (fabs(aq) <= s.h - mg && ex * ex + ey * ey + ez * ez < rin * rin) return 1;
+        }
+    }
+    if (dn2 > 1e-24) {
+        const double inv = 1.0 / sqrt(dn2);
+        const double n[3] = {d[0] * inv, d[1] * inv, d[2] * inv};
+        const double un = u[0] * n[0] + u[1] * n[1] + u[2] * n[2];
+        const double supp_c = s.h * fabs(un) + (caps ? radius : radius * sqrt(fmax(0.0, 1.0 - un * un)));
+        const double supp_b = e * (fabs(n[0]) + fabs(n[1]) + fabs(n[2]));
+        if (w[0] * n[0] + w[1] * n[1] + w[2] * n[2] - supp_c - supp_b > mg) return 0;
+    }
+    return 2;
 }
 
 // CTA-wide exclusive prefix of one int per thread: prefix[t] = sum of val[0..t), prefix[nthreads] = total
@@ -1334,8 +1366,10 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         edges_narrow_kernel<<<nblk, 128, 0, h->stream>>>(a);
         BGR_LAUNCH_CHECK();
         ma.only_overflow = 1;   // no-op unless the queue overflowed
+        ma.n_overflow = h->qctl.p + 1;
     } else {
         ma.only_overflow = 0;
+        ma.n_overflow = nullptr;
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
     }
     if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[2], h->stream));
