@@ -781,20 +781,25 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
                                          (W11 >> (bi + bb1 + bc1));
                     fired = (any & 1ull) != 0ull;
                 }
-                if (!fired) continue;
-                fired_mask |= 1u << (k - k0);
-                if (allow_deep) {
-                    // the cell holding the axis at the middle of the slab portion (kept 0.05 cell inside
-                    // the segment and inside the slab): occupied => the shapes overlap by ~radius: deep hit
-                    const float ua = fmaxf(fmaxf(ta, (float)k), g.tlo + 0.05f), ub = fminf(fminf(tb, (float)(k + 1)), g.thi - 0.05f);
+                if (fired) fired_mask |= 1u << (k - k0);
+            }
+            // deep-hit probe of the fired slabs (after the walk, so that the lanes that fired run it
+            // together): the cell holding the axis at the middle of the slab portion (kept 0.05 cell
+            // inside the segment and inside the slab) is occupied => the shapes overlap by ~radius
+            if (allow_deep) {
+                unsigned fm = fired_mask;
+                while (fm && !deep) {
+                    const int k = k0 + __ffs(fm) - 1;
+                    fm &= fm - 1;
+                    const int i = i_lo + k;
+                    const float ua = fmaxf((float)k, g.tlo + 0.05f), ub = fminf((float)(k + 1), g.thi - 0.05f);
                     if (ua <= ub) {
                         const float um = 0.5f * (ua + ub);
                         const int jb = (int)floorf(fmaf(g.sb, um, g.beta_b)), jc = (int)floorf(fmaf(g.sc, um, g.beta_c));
                         if (jb >= 0 && jb < dim_b && jc >= 0 && jc < dim_c) {
-                            const uint64_t W = __ldg(m.lv[0].bits + (wi + (unsigned)(jb >> 2) * Sb + (unsigned)(jc >> 2) * Sc));
-                            deep = ((W >> (bi + ((jb & 3) << Ub) + ((jc & 3) << Uc))) & 1ull) != 0ull;
+                            const uint64_t W = __ldg(m.lv[0].bits + ((unsigned)(i >> 2) * Si + (unsigned)(jb >> 2) * Sb + (unsigned)(jc >> 2) * Sc));
+                            deep = ((W >> (((i & 3) << Ui) + ((jb & 3) << Ub) + ((jc & 3) << Uc))) & 1ull) != 0ull;
                         }
-                        if (deep) break;
                     }
                 }
             }
