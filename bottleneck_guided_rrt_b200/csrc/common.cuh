@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <cstdio>
 #include <cstdarg>
+#include <cstdlib>
 #include <string>
 #include "../../include/bgrrt.h"
 
@@ -90,6 +91,44 @@ struct DevBuf {
         cap = 0;
     }
 };
+
+// Side streams + events of the host-pointer entry points: a batch is cut into chunks so that
+// the H2D copy of chunk c+1 and the D2H copy of chunk c-1 overlap the kernels of chunk c
+// (the caller's buffers must be pinned for the copies to be asynchronous; pageable memory is
+// still correct, just serialised by the driver).
+struct CopyPipe {
+    static constexpr int kMaxChunks = 8;
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[kMaxChunks] = {}, ev_out[kMaxChunks] = {}, ev_start = nullptr;
+    int init() {
+        if (s_in) return BGR_OK;
+        BGR_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+        BGR_CUDA(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+        BGR_CUDA(cudaEventCreateWithFlags(&ev_start, cudaEventDisableTiming));
+        for (int i = 0; i < kMaxChunks; ++i) {
+            BGR_CUDA(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+            BGR_CUDA(cudaEventCreateWithFlags(&ev_out[i], cudaEventDisableTiming));
+        }
+        return BGR_OK;
+    }
+    void release() {
+        if (!s_in) return;
+        cudaStreamDestroy(s_in);
+        cudaStreamDestroy(s_out);
+        cudaEventDestroy(ev_start);
+        for (int i = 0; i < kMaxChunks; ++i) {
+            cudaEventDestroy(ev_in[i]);
+            cudaEventDestroy(ev_out[i]);
+        }
+        s_in = s_out = nullptr;
+    }
+};
+
+// measurement aid: BGR_NO_PIPE=1 in the environment turns the chunked overlap off (read per call)
+inline bool pipe_disabled() {
+    const char* e = getenv("BGR_NO_PIPE");
+    return e && e[0] == '1';
+}
 
 // pinned host staging buffer
 struct PinBuf {

@@ -424,6 +424,7 @@ struct Edge2Args {
     uint8_t* band;
     LevelGrid dil;               // level 0 dilated by gate_d cells (Chebyshev), same brick layout
     int gate_d;                  // 0 = gate off (every slab runs the rectangle phase)
+    int64_t e_begin;             // first edge of this launch (n = one past its last edge): chunked host calls
 };
 
 // ------------------------------------------------------------------ dilated occupancy (sweep gate)
@@ -666,7 +667,7 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
 
     const MapView& m = a.m;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int64_t e0 = (int64_t)blockIdx.x * kSweepEdges;
+    const int64_t e0 = a.e_begin + (int64_t)blockIdx.x * kSweepEdges;
     const int ne = (int)min((int64_t)kSweepEdges, a.n - e0);
     const double rm = a.radius + kSweepMargin;
     const bool gate = a.gate_d > 0;
@@ -1058,6 +1059,9 @@ struct bgr_map {
     int dil_d = 0;
     bool dil_dirty = true;
     bool gate_on = true;
+    int pipe_chunks = 0;               // > 1: the sweep of chunk c waits for pipe.ev_in[c] (host-pointer call)
+    int64_t pipe_per = 0;
+    CopyPipe pipe;                     // side streams of the host-pointer collide_edges
     uint64_t last_stats[4] = {0, 0, 0, 0};
     cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // kernel boundaries of the last collide_edges (timing on)
     bool timing = false;
@@ -1364,8 +1368,20 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.gate_d = gate ? gate_d : 0;
         a.dil.bits = gate ? h->dil.p : nullptr;
         for (int ax = 0; ax < 3; ++ax) a.dil.nb[ax] = h->nb[0][ax];
-        edges_sweep_kernel<<<(unsigned)div_up(n, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
-        BGR_LAUNCH_CHECK();
+        // one sweep launch per chunk of a chunked host call (each waits for its H2D copy), one
+        // narrow / finalize pass over the whole batch
+        const int nch = h->pipe_chunks > 1 ? h->pipe_chunks : 1;
+        const int64_t per = nch > 1 ? h->pipe_per : n;
+        for (int c = 0; c < nch; ++c) {
+            a.e_begin = (int64_t)c * per;
+            a.n = std::min<int64_t>(n, a.e_begin + per);
+            if (a.n <= a.e_begin) break;
+            if (nch > 1) BGR_CUDA(cudaStreamWaitEvent(h->stream, h->pipe.ev_in[c], 0));
+            edges_sweep_kernel<<<(unsigned)div_up(a.n - a.e_begin, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
+            BGR_LAUNCH_CHECK();
+        }
+        a.e_begin = 0;
+        a.n = n;
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
         const int nblk = (int)std::min<int64_t>(4LL * num_sms(), std::max<int64_t>(1, div_up(cap, 128)));
         edges_narrow_kernel<<<nblk, 128, 0, h->stream>>>(a);
@@ -1373,6 +1389,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         ma.only_overflow = 1;   // no-op unless the queue overflowed
         ma.n_overflow = h->qctl.p + 1;
     } else {
+        for (int c = 0; c < h->pipe_chunks; ++c) BGR_CUDA(cudaStreamWaitEvent(h->stream, h->pipe.ev_in[c], 0));
         ma.only_overflow = 0;
         ma.n_overflow = nullptr;
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
@@ -1395,14 +1412,44 @@ int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t 
     BGR_CHECK(h->p2_dev.reserve(3 * n, h->stream, false));
     BGR_CHECK(h->hit_dev.reserve(n, h->stream, false));
     BGR_CHECK(h->band_dev.reserve(n, h->stream, false));
-    BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, p1, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p, p2, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    BGR_CHECK(bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
-                                        band ? h->band_dev.p : nullptr));
-    BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
-    if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    // large batches are cut into chunks: the H2D copy of chunk c+1 and the D2H copy of chunk c-1
+    // overlap the kernels of chunk c (edges are independent, so chunking cannot change results)
+    const int chunks = pipe_disabled() ? 1 : (int)std::min<int64_t>(4, n / 65536);
+    if (chunks <= 1) {
+        BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, p1, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p, p2, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        BGR_CHECK(bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
+                                            band ? h->band_dev.p : nullptr));
+        BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+        if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaStreamSynchronize(h->stream));
+        return BGR_OK;
+    }
+    BGR_CHECK(h->pipe.init());
+    CopyPipe& P = h->pipe;
+    // the staging buffers may still be read by earlier work on the map's stream
+    BGR_CUDA(cudaEventRecord(P.ev_start, h->stream));
+    BGR_CUDA(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
+    const int64_t per = round_up(div_up(n, chunks), 256);
+    for (int c = 0; c < chunks; ++c) {
+        const int64_t s0 = (int64_t)c * per, m = std::min<int64_t>(per, n - s0);
+        if (m <= 0) break;
+        BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p + 3 * s0, p1 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+        BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p + 3 * s0, p2 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+        BGR_CUDA(cudaEventRecord(P.ev_in[c], P.s_in));
+    }
+    h->pipe_chunks = chunks;
+    h->pipe_per = per;
+    const int rc = bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
+                                             band ? h->band_dev.p : nullptr);
+    h->pipe_chunks = 0;
+    if (rc == BGR_OK) {
+        cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+        if (band) cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+    }
+    cudaStreamSynchronize(P.s_in);
     BGR_CUDA(cudaStreamSynchronize(h->stream));
-    return BGR_OK;
+    return rc;
 }
 
 int bgr_map_set_timing(bgr_map* h, int on) {
@@ -1455,6 +1502,7 @@ int bgr_map_destroy(bgr_map* h) {
     h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
     h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
     h->dil.release(); h->dil_tmp.release();
+    h->pipe.release();
     for (int i = 0; i < 5; ++i)
         if (h->tev[i]) cudaEventDestroy(h->tev[i]);
     delete h;

@@ -27,6 +27,7 @@ struct bgr_nns {
     DevBuf<int32_t> idx_dev, part_idx;
     DevBuf<unsigned long long> counter;
     GridIndex grid;
+    CopyPipe pipe;               // side streams of the host-pointer kNN (chunked D2H overlap)
 };
 
 namespace {
@@ -323,10 +324,35 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
         BGR_CUDA(cudaMemcpyAsync(h->radii_dev.p, max_radii, (size_t)nq * sizeof(float), cudaMemcpyHostToDevice, h->stream));
         d_radii = h->radii_dev.p;
     }
-    BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
-                              h->d2_dev.p, touched));
-    BGR_CUDA(cudaMemcpyAsync(idx, h->idx_dev.p, (size_t)nq * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-    BGR_CUDA(cudaMemcpyAsync(d2, h->d2_dev.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    // grid search of a large batch: cut it into chunks so the D2H copy of chunk c overlaps the
+    // kernel of chunk c+1 (results are per query, so chunking cannot change them)
+    int method = h->method;
+    if (method == BGR_METHOD_AUTO) method = (h->n >= 16384) ? BGR_METHOD_GRID : BGR_METHOD_BRUTE;
+    const bool want_stats = (h->create_flags & BGR_TOUCH_STATISTICS) && touched;
+    int chunks = 1;
+    if ((method == BGR_METHOD_GRID || method == BGR_METHOD_GRID_GENERAL) && !want_stats && !pipe_disabled())
+        chunks = (int)std::min<int64_t>(4, nq / 8192);
+    if (chunks <= 1) {
+        BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
+                                  h->d2_dev.p, touched));
+        BGR_CUDA(cudaMemcpyAsync(idx, h->idx_dev.p, (size_t)nq * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaMemcpyAsync(d2, h->d2_dev.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaStreamSynchronize(h->stream));
+        return BGR_OK;
+    }
+    BGR_CHECK(h->pipe.init());
+    const int64_t per = round_up(div_up(nq, chunks), 8);
+    for (int c = 0; c < chunks; ++c) {
+        const int64_t s0 = (int64_t)c * per, m = std::min<int64_t>(per, nq - s0);
+        if (m <= 0) break;
+        BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p + 3 * s0, m, k, eps, flags, max_radius, d_radii ? d_radii + s0 : nullptr,
+                                  h->idx_dev.p + s0 * k, h->d2_dev.p + s0 * k, nullptr));
+        BGR_CUDA(cudaEventRecord(h->pipe.ev_out[c], h->stream));
+        BGR_CUDA(cudaStreamWaitEvent(h->pipe.s_out, h->pipe.ev_out[c], 0));
+        BGR_CUDA(cudaMemcpyAsync(idx + s0 * k, h->idx_dev.p + s0 * k, (size_t)m * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->pipe.s_out));
+        BGR_CUDA(cudaMemcpyAsync(d2 + s0 * k, h->d2_dev.p + s0 * k, (size_t)m * k * sizeof(float), cudaMemcpyDeviceToHost, h->pipe.s_out));
+    }
+    BGR_CUDA(cudaStreamSynchronize(h->pipe.s_out));
     BGR_CUDA(cudaStreamSynchronize(h->stream));
     return BGR_OK;
 }
@@ -379,6 +405,7 @@ int bgr_nns_destroy(bgr_nns* h) {
     h->stage_f.release(); h->q_dev.release(); h->radii_dev.release(); h->d2_dev.release();
     h->part_d2.release(); h->idx_dev.release(); h->part_idx.release(); h->counter.release();
     grid_release(h->grid);
+    h->pipe.release();
     delete h;
     return BGR_OK;
 }

@@ -257,6 +257,25 @@ def test_edges_gate_is_exact(bgr, oracle, radius, shape):
     assert not np.array_equal(h0u, h0)
 
 
+def test_edges_chunked_host_call_equals_device_call(bgr, oracle):
+    """a large host-pointer batch is cut into chunks whose H2D copies overlap the sweep of the
+    previous chunk: same hit / in_band bytes and same counters as the one-launch device call."""
+    import torch
+    occ, boxes, m = _map(bgr, oracle, 128, 3, 2, n_walls=3, wall_thick=3, door_cells=5)
+    p1, p2 = _edges(oracle, occ, 200001, 61, lo=0.05, hi=2.0, extent=6.4)
+    h0, b0 = m.collide_edges(p1, p2)
+    st0 = m.last_stats()
+    d1, d2 = torch.from_numpy(p1).cuda(), torch.from_numpy(p2).cuda()
+    h1, b1 = m.collide_edges(d1, d2)
+    torch.cuda.synchronize()
+    st1 = m.last_stats()
+    assert np.array_equal(h0, h1.cpu().numpy()) and np.array_equal(b0, b1.cpu().numpy())
+    assert st0["work_items"] == st1["work_items"] and st0["candidates"] == st1["candidates"]
+    hp = torch.from_numpy(p1).pin_memory().numpy(), torch.from_numpy(p2).pin_memory().numpy()
+    h2, b2 = m.collide_edges(hp[0], hp[1])
+    assert np.array_equal(h0, h2) and np.array_equal(b0, b2)
+
+
 def test_octomap_ingestion_and_refresh(bgr, oracle):
     """serialised Octomap (full message data, MS:279) -> toBoxes rows -> bitmap; then a map refresh
     that rasterises only the changed leaves (bgr_map_refresh_boxes)."""

@@ -197,3 +197,10 @@ def test_knn_full_size_properties(bgr, oracle):
     d = q[:, None, :] - pts[gi]
     r = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) + d[..., 2] * d[..., 2]
     assert np.array_equal(r.astype(np.float32).view(np.uint32), gd.view(np.uint32))
+    # the host call above was chunked (D2H of chunk c overlaps the kernel of chunk c+1): the
+    # one-launch device call returns the same bytes
+    import torch
+    nns.set_method(bgr.METHOD_GRID)
+    di, dd, _ = nns.knn(torch.from_numpy(q).cuda(), k)
+    torch.cuda.synchronize()
+    assert np.array_equal(di.cpu().numpy(), gi) and np.array_equal(dd.cpu().numpy().view(np.uint32), gd.view(np.uint32))
