@@ -40,6 +40,9 @@ struct GridIndex {
     DevBuf<int32_t> cursor;       // per cell (build scratch)
     DevBuf<int32_t> block_sums;
     DevBuf<float> partial;        // bbox partials
+    DevBuf<double> sumsq;         // build scratch
+    double crowd = 0.0;           // sum(cell count^2) / n: the occupancy of the cell an average NODE sits in
+                                  // (~kPtsPerCell+1 for a uniform cloud, thousands for a piled-up tree)
 };
 
 __device__ __forceinline__ int cell_coord(float v, float mn, float inv_cs, int g) {
@@ -148,6 +151,16 @@ __global__ void scatter_kernel(const float* __restrict__ x, const float* __restr
     pts[pos] = make_float4(x[i], y[i], z[i], __int_as_float((int)i));
 }
 
+__global__ void cell_sumsq_kernel(const int32_t* __restrict__ cell_start, int64_t ncells, double* __restrict__ out) {
+    double acc = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < ncells; i += (int64_t)gridDim.x * blockDim.x) {
+        const double c = (double)(cell_start[i + 1] - cell_start[i]);
+        acc += c * c;
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(kFull, acc, o);
+    if ((threadIdx.x & 31) == 0 && acc != 0.0) atomicAdd(out, acc);
+}
+
 inline int exclusive_scan(int32_t* d, int64_t n, DevBuf<int32_t>& sums, cudaStream_t st) {
     // recursive over levels; the sums of level L live at offset in `sums`
     std::vector<int64_t> sizes;
@@ -245,6 +258,15 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
     BGR_CHECK(exclusive_scan(G.cell_start.p, ncells + 1, G.block_sums, st));
     scatter_kernel<<<(unsigned)div_up(n, 256), 256, 0, st>>>(x, y, z, n, G.cell_id.p, G.cell_start.p, G.cursor.p, G.pts.p);
     BGR_LAUNCH_CHECK();
+    // crowding statistic for the AUTO method choice (nns.cu)
+    BGR_CHECK(G.sumsq.reserve(1, st, false));
+    BGR_CUDA(cudaMemsetAsync(G.sumsq.p, 0, sizeof(double), st));
+    cell_sumsq_kernel<<<256, 256, 0, st>>>(G.cell_start.p, ncells, G.sumsq.p);
+    BGR_LAUNCH_CHECK();
+    double ss = 0.0;
+    BGR_CUDA(cudaMemcpyAsync(&ss, G.sumsq.p, sizeof(double), cudaMemcpyDeviceToHost, st));
+    BGR_CUDA(cudaStreamSynchronize(st));
+    G.crowd = ss / (double)n;
     G.geom = gm;
     G.n_indexed = n;
     return BGR_OK;
@@ -252,7 +274,7 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
 
 inline void grid_release(GridIndex& G) {
     G.pts.release(); G.cell_start.release(); G.cell_id.release(); G.cursor.release();
-    G.block_sums.release(); G.partial.release();
+    G.block_sums.release(); G.partial.release(); G.sumsq.release();
     G.n_indexed = 0;
 }
 
@@ -521,6 +543,168 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
         a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
     }
     if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+}
+
+// ---------------------------------------------------------------- grid Nearest (MS:138-154)
+// Same index, the reference's 1-NN: Norm = float(sqrt(double(dx^2+dy^2+dz^2))) with dx = x2-x1
+// in float, `<=` scan => the LAST index among nodes with equal float Norm.  One warp per
+// query, ring by ring; a ring ends the search when the best Norm is strictly below the
+// nearest unscanned cell face (shrunk by the cell-rounding slack and 1e-6 relative), so no
+// unscanned node can beat or tie it: the result equals the brute-force scan's.
+struct GridNearestArgs {
+    GridGeom gm;
+    const float4* pts;
+    const int32_t* cell_start;
+    int64_t n_indexed;
+    const float* x;
+    const float* y;
+    const float* z;
+    int64_t n;
+    const float* q;
+    int64_t nq;
+    int32_t* idx;
+    float* dist;
+    int64_t index_base;
+};
+
+__global__ void __launch_bounds__(kGridWarps * 32) grid_nearest_kernel(GridNearestArgs a) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    if (qi >= a.nq) return;
+    const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
+    const GridGeom& gm = a.gm;
+    const double kInfD = __longlong_as_double(0x7ff0000000000000LL);
+    float best_f = __uint_as_float(kInfBits);
+    int32_t best_i = -1;
+    double T = kInfD;
+    auto consider = [&](float px, float py, float pz, int32_t pidx, bool valid) {
+        const double dx = (double)__fsub_rn(qx, px), dy = (double)__fsub_rn(qy, py), dz = (double)__fsub_rn(qz, pz);
+        const double sq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        if (valid && sq <= T) {   // NaN never passes
+            const float f = __double2float_rn(__dsqrt_rn(sq));
+            if (f < best_f || (f == best_f && pidx > best_i)) {
+                best_f = f;
+                best_i = pidx;
+                T = f < __uint_as_float(kInfBits) ? (double)__uint_as_float(__float_as_uint(f) + 1u) * (double)__uint_as_float(__float_as_uint(f) + 1u) : kInfD;
+            }
+        }
+    };
+    // ---- unsorted tail [n_indexed, n)
+    for (int64_t base = a.n_indexed; base < a.n; base += 32) {
+        const int64_t j = base + lane;
+        const bool valid = j < a.n;
+        consider(valid ? a.x[j] : 0.f, valid ? a.y[j] : 0.f, valid ? a.z[j] : 0.f, (int32_t)j, valid);
+    }
+    const bool finite_q = (qx - qx == 0.f) && (qy - qy == 0.f) && (qz - qz == 0.f);
+    if (a.n_indexed > 0 && !finite_q) {
+        // infinite / NaN query: no geometry to prune with; scan the whole index like the plain loop
+        for (int64_t base = 0; base < a.n_indexed; base += 32) {
+            const int64_t j = base + lane;
+            const bool valid = j < a.n_indexed;
+            float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (valid) p = __ldg(a.pts + j);
+            consider(p.x, p.y, p.z, __float_as_int(p.w), valid);
+        }
+    }
+    if (a.n_indexed > 0 && finite_q) {
+        const int cx = cell_coord(qx, gm.mn[0], gm.inv_cs, gm.g[0]);
+        const int cy = cell_coord(qy, gm.mn[1], gm.inv_cs, gm.g[1]);
+        const int cz = cell_coord(qz, gm.mn[2], gm.inv_cs, gm.g[2]);
+        const int gmax = max(gm.g[0], max(gm.g[1], gm.g[2]));
+        for (int ring = 1; ring <= gmax; ++ring) {
+            const int side = 2 * ring + 1;
+            const int nitems = 2 * side * side;
+            for (int t0 = 0; t0 < nitems; t0 += 32) {
+                const int t = t0 + lane;
+                int s = 0, e = 0;
+                if (t < nitems) {
+                    const int row = t >> 1, which = t & 1;
+                    const int dy = row % side - ring, dz = row / side - ring;
+                    const int yy = cy + dy, zz = cz + dz;
+                    if (yy >= 0 && yy < gm.g[1] && zz >= 0 && zz < gm.g[2]) {
+                        const bool shell_row = (ring == 1) || abs(dy) == ring || abs(dz) == ring;
+                        int x0, x1;   // inclusive cell range
+                        if (shell_row) {
+                            x0 = which == 0 ? cx - ring : 1;
+                            x1 = which == 0 ? cx + ring : 0;
+                        } else {
+                            x0 = x1 = which == 0 ? cx - ring : cx + ring;
+                            if (x0 < 0 || x0 >= gm.g[0]) { x0 = 1; x1 = 0; }
+                        }
+                        x0 = max(x0, 0);
+                        x1 = min(x1, gm.g[0] - 1);
+                        if (x0 <= x1) {
+                            const int64_t rb = ((int64_t)zz * gm.g[1] + yy) * gm.g[0];
+                            s = __ldg(a.cell_start + rb + x0);
+                            e = __ldg(a.cell_start + rb + x1 + 1);
+                        }
+                    }
+                }
+                unsigned nonempty = __ballot_sync(kFull, e > s);
+                while (nonempty) {
+                    const int src = __ffs(nonempty) - 1;
+                    nonempty &= nonempty - 1;
+                    const int rs = __shfl_sync(kFull, s, src), re = __shfl_sync(kFull, e, src);
+                    for (int b = rs; b < re; b += 32) {
+                        const int j = b + lane;
+                        const bool valid = j < re;
+                        float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (valid) p = __ldg(a.pts + j);
+                        consider(p.x, p.y, p.z, __float_as_int(p.w), valid);
+                    }
+                }
+            }
+            // ---- termination: nearest unscanned face
+            float bw = best_f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) bw = fminf(bw, __shfl_xor_sync(kFull, bw, o));
+            if (bw < __uint_as_float(kInfBits)) {   // lanes only need candidates that can still win or tie
+                const float nu = __uint_as_float(__float_as_uint(bw) + 1u);
+                T = fmin(T, (double)nu * (double)nu);
+            }
+            float b = __uint_as_float(kInfBits);
+            const float qv[3] = {qx, qy, qz};
+            const int cc[3] = {cx, cy, cz};
+#pragma unroll
+            for (int ax = 0; ax < 3; ++ax) {
+                if (cc[ax] - ring > 0) b = fminf(b, qv[ax] - (gm.mn[ax] + (float)(cc[ax] - ring) * gm.cs));
+                if (cc[ax] + ring + 1 < gm.g[ax]) b = fminf(b, (gm.mn[ax] + (float)(cc[ax] + ring + 1) * gm.cs) - qv[ax]);
+            }
+            if (b == __uint_as_float(kInfBits)) break;                       // whole grid scanned
+            const float bs = fmaxf(0.f, b - 2e-3f * gm.cs) * (1.f - 1e-6f);
+            if (bw < bs) break;
+        }
+    }
+    // ---- warp reduce: min Norm, then max index
+    float f = best_f;
+    int32_t i = best_i;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float of = __shfl_xor_sync(kFull, f, o);
+        const int32_t oi = __shfl_xor_sync(kFull, i, o);
+        if (oi >= 0 && (i < 0 || of < f || (of == f && oi > i))) {
+            f = of;
+            i = oi;
+        }
+    }
+    if (lane == 0) {
+        a.idx[qi] = i < 0 ? -1 : (int32_t)(i + a.index_base);
+        if (a.dist) a.dist[qi] = f;
+    }
+}
+
+inline int grid_nearest(GridIndex& G, const float* x, const float* y, const float* z, int64_t n, const float* d_q,
+                        int64_t nq, int32_t* d_idx, float* d_dist, int64_t index_base, cudaStream_t st) {
+    GridNearestArgs a;
+    a.gm = G.geom;
+    a.pts = G.pts.p;
+    a.cell_start = G.cell_start.p;
+    a.n_indexed = G.n_indexed;
+    a.x = x; a.y = y; a.z = z; a.n = n;
+    a.q = d_q; a.nq = nq; a.idx = d_idx; a.dist = d_dist; a.index_base = index_base;
+    grid_nearest_kernel<<<(unsigned)div_up(nq, kGridWarps), kGridWarps * 32, 0, st>>>(a);
+    BGR_LAUNCH_CHECK();
+    return BGR_OK;
 }
 
 inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,

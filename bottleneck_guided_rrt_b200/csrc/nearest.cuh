@@ -1,9 +1,12 @@
 // Batched Nearest() — reference MS:138-154 with Norm() MS:130-134:
 //   Norm = float( pow( pow(dx,2)+pow(dy,2)+pow(dz,2), 0.5 ) ),  dx = x2-x1 in float,
 //   squares / sum / root in double;  `if (temp <= min)` => LAST index among equal floats.
-// Same tile pipeline as knn_brute.cuh.  Per (query,node): 3 FSUB, 3 F2D, 3 DMUL, 2 DADD and
-// one DSETP against T = nextup(best)^2 (a superset test: float(sqrt(s)) <= best implies
-// s < nextup(best)^2); the DSQRT only runs for candidates that pass it.
+// Same tile pipeline as knn_brute.cuh.  Per (query,node): an f32 FILTER first — 3 FSUB, FMUL,
+// 2 FFMA, one FSETP against Tf — and only for its survivors the reference's arithmetic:
+// 3 F2D, 3 DMUL, 2 DADD, one DSETP against T = nextup(best)^2 (a superset test:
+// float(sqrt(s)) <= best implies s < nextup(best)^2) and the DSQRT for candidates that pass.
+// The filter cannot drop a candidate: the f32 sum of squares of the same float differences is
+// within 2e-7 relative of the double one, and Tf = T * (1 + 1e-6) rounded up.
 #pragma once
 #include "knn_brute.cuh"
 
@@ -65,7 +68,7 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
     }
 
     const int64_t q0 = ((int64_t)blockIdx.x * kConsumerWarps + warp) * R;
-    float qx[R], qy[R], qz[R], best_f[R];
+    float qx[R], qy[R], qz[R], best_f[R], Tf[R];
     int32_t best_i[R];
     double T[R];
 #pragma unroll
@@ -77,6 +80,7 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
         best_f[r] = __uint_as_float(kInfBits);
         best_i[r] = -1;
         T[r] = __longlong_as_double(0x7ff0000000000000LL);
+        Tf[r] = __uint_as_float(kInfBits);
     }
     for (int t = 0; t < ntiles; ++t) {
         const int s = t % kStages;
@@ -90,15 +94,18 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
             const float px = sx[j], py = sy[j], pz = sz[j];
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                const double dx = (double)__fsub_rn(qx[r], px), dy = (double)__fsub_rn(qy[r], py),
-                             dz = (double)__fsub_rn(qz[r], pz);
-                const double sq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-                if (sq <= T[r]) {   // NaN padding never passes
-                    const float f = __double2float_rn(__dsqrt_rn(sq));
-                    if (f <= best_f[r]) {   // j increases within a lane: `<=` keeps the last
-                        best_f[r] = f;
-                        best_i[r] = (int32_t)(tile_base + j);
-                        T[r] = nextup_sq(f);
+                const float fx = __fsub_rn(qx[r], px), fy = __fsub_rn(qy[r], py), fz = __fsub_rn(qz[r], pz);
+                if (fmaf(fz, fz, fmaf(fy, fy, fx * fx)) <= Tf[r]) {   // f32 filter; NaN padding never passes
+                    const double dx = (double)fx, dy = (double)fy, dz = (double)fz;
+                    const double sq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+                    if (sq <= T[r]) {
+                        const float f = __double2float_rn(__dsqrt_rn(sq));
+                        if (f <= best_f[r]) {   // j increases within a lane: `<=` keeps the last
+                            best_f[r] = f;
+                            best_i[r] = (int32_t)(tile_base + j);
+                            T[r] = nextup_sq(f);
+                            Tf[r] = __double2float_ru(T[r] * (1.0 + 1e-6));
+                        }
                     }
                 }
             }

@@ -174,6 +174,38 @@ def test_nearest_last_index_wins_ties(bgr, oracle):
     assert idx.tolist() == oi.tolist() == [4, 3, 4]
 
 
+@pytest.mark.parametrize("method", [2, 3])
+def test_nearest_grid_equals_plain_scan(bgr, oracle, method):
+    """the grid Nearest (large trees) returns the plain scan's answer bit for bit: random and
+    clustered trees, lattice points with equal float Norms (last index wins), duplicated nodes,
+    queries outside the cloud / infinite / NaN, and an unsorted tail after appends."""
+    mt = oracle.MT(71)
+    uni = oracle.points(2, 60000, 25.6)
+    clus = (np.array([5.0, 6.0, 7.0]) + (mt.real(3 * 30000).reshape(-1, 3) - 0.5) * 0.3).astype(np.float32)
+    lat = np.stack(np.meshgrid(np.arange(20), np.arange(20), np.arange(20), indexing="ij"), -1).reshape(-1, 3).astype(np.float32)
+    pts = np.concatenate([uni, clus, lat, lat[:500], uni[:1000]])
+    q = np.concatenate([oracle.points(3, 3000, 25.6), clus[:500] + 0.01, lat[:300] + 0.5, lat[:300],
+                        np.array([[-50, 3, 3], [1e6, 1e6, 1e6], [np.inf, 0, 0], [np.nan, 1, 1]], dtype=np.float32)]).astype(np.float32)
+    ref = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    ref.set_method(bgr.METHOD_BRUTE)
+    ri, rd = ref.nearest(q)
+    oi, od = oracle.nearest(pts, q[:600])
+    assert np.array_equal(ri[:600], oi) and np.array_equal(rd[:600].view(np.uint32), od.view(np.uint32))
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts[:80000])
+    nns.set_method(method)
+    nns.build_index()
+    nns.append(pts[80000:])                      # unsorted tail: a small batch does not trigger a rebuild
+    sub = np.r_[0:40, 3000:3020, len(q) - 8:len(q)]
+    si, sd = nns.nearest(q[sub])
+    assert np.array_equal(si, ri[sub]) and np.array_equal(sd.view(np.uint32), rd[sub].view(np.uint32))
+    gi, gd = nns.nearest(q)
+    assert np.array_equal(gi, ri), np.nonzero(gi != ri)[0][:10]
+    assert np.array_equal(gd.view(np.uint32), rd.view(np.uint32))
+    nns.build_index()
+    gi, gd = nns.nearest(q)
+    assert np.array_equal(gi, ri) and np.array_equal(gd.view(np.uint32), rd.view(np.uint32))
+
+
 def test_knn_full_size_properties(bgr, oracle):
     """BASELINE config 2 (1M nodes, 64k queries, k=16): grid == brute on the GPU, and an
     oracle check on a 256-query subsample; sortedness; distances recomputed on the host."""
