@@ -42,6 +42,7 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
     const int64_t n_pad = (a.n + kTile - 1) / kTile * kTile;
     const int64_t chunk_end = min(chunk_begin + a.chunk_nodes, n_pad);
     const int ntiles = (int)((chunk_end - chunk_begin) / kTile);
+    const int tstride = tile_stride(ntiles);   // scrambled tile order: see knn_brute.cuh
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
                 const int s = t % kStages;
                 if (t >= kStages) mbar_wait(&empty_bar[s], ((t / kStages) - 1) & 1);
                 float* dst = tiles + s * 3 * kTile;
-                const int64_t off = chunk_begin + (int64_t)t * kTile;
+                const int64_t off = chunk_begin + (int64_t)tile_perm(t, tstride, ntiles) * kTile;
                 mbar_expect_tx(&full_bar[s], 3 * kTile * sizeof(float));
                 bulk_g2s(dst, a.x + off, kTile * sizeof(float), &full_bar[s]);
                 bulk_g2s(dst + kTile, a.y + off, kTile * sizeof(float), &full_bar[s]);
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
         const float* sx = tiles + s * 3 * kTile;
         const float* sy = sx + kTile;
         const float* sz = sy + kTile;
-        const int64_t tile_base = chunk_begin + (int64_t)t * kTile;
+        const int64_t tile_base = chunk_begin + (int64_t)tile_perm(t, tstride, ntiles) * kTile;
 #pragma unroll 2
         for (int j = lane; j < kTile; j += 32) {
             const float px = sx[j], py = sy[j], pz = sz[j];
@@ -100,9 +101,10 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
                     const double sq = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
                     if (sq <= T[r]) {
                         const float f = __double2float_rn(__dsqrt_rn(sq));
-                        if (f <= best_f[r]) {   // j increases within a lane: `<=` keeps the last
+                        const int32_t ci = (int32_t)(tile_base + j);
+                        if (f < best_f[r] || (f == best_f[r] && ci > best_i[r])) {   // equal Norm: the last index wins
                             best_f[r] = f;
-                            best_i[r] = (int32_t)(tile_base + j);
+                            best_i[r] = ci;
                             T[r] = nextup_sq(f);
                             Tf[r] = __double2float_ru(T[r] * (1.0 + 1e-6));
                         }
