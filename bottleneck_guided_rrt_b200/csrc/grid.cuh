@@ -299,6 +299,7 @@ struct GridKnnArgs {
     int64_t index_base;
     unsigned long long* counter;
     int fast;            // enable the one-pass ring-1 path
+    const uint8_t* skip; // optional per-query flag: non-zero = leave this query's rows untouched
     float fast_target;   // expected survivors the a-priori threshold aims at (k + ~2.5 sqrt k)
 };
 
@@ -327,6 +328,7 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
     if (qi >= a.nq) return;
+    if (a.skip && __ldg(a.skip + qi)) return;
     const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
     const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
     const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
@@ -710,7 +712,7 @@ inline int grid_nearest(GridIndex& G, const float* x, const float* y, const floa
 inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,
                     const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
                     const float* d_radii, int32_t* d_idx, float* d_d2, int64_t index_base,
-                    unsigned long long* counter, int fast, cudaStream_t st) {
+                    unsigned long long* counter, int fast, cudaStream_t st, const uint8_t* d_skip = nullptr) {
     GridKnnArgs a;
     a.gm = G.geom;
     a.pts = G.pts.p;
@@ -721,6 +723,7 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     a.max_radius = max_radius; a.max_radii = d_radii;
     a.idx = d_idx; a.d2 = d_d2; a.index_base = index_base; a.counter = counter;
     a.fast = fast;
+    a.skip = d_skip;
     a.fast_target = (float)k + 2.5f * sqrtf((float)k) + 1.f;
     grid_knn_kernel<<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();

@@ -310,9 +310,9 @@ static int pick_method(bgr_nns* h, int64_t nq, bool for_nearest, int* method) {
     return BGR_OK;
 }
 
-int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, unsigned flags,
-                    float max_radius, const float* d_radii, int32_t* d_idx, float* d_d2,
-                    uint64_t* touched) {
+static int knn_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, unsigned flags,
+                        float max_radius, const float* d_radii, int32_t* d_idx, float* d_d2,
+                        uint64_t* touched, const uint8_t* d_skip) {
     BGR_CHECK(check_knn_args(h, nq, k, eps, flags, max_radius));
     if (touched) *touched = 0;
     if (nq == 0) return BGR_OK;
@@ -327,7 +327,7 @@ int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, 
             BGR_CUDA(cudaMemsetAsync(h->counter.p, 0, sizeof(unsigned long long), h->stream));
         }
         BGR_CHECK(grid_knn(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, k, flags, max_radius, d_radii,
-                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, grid_fast, h->stream));
+                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, grid_fast, h->stream, d_skip));
         if (stats) {
             unsigned long long c = 0;
             BGR_CUDA(cudaMemcpyAsync(&c, h->counter.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
@@ -339,6 +339,17 @@ int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, 
     BGR_CHECK(knn_brute_dev(h, d_q, nq, k, flags, max_radius, d_radii, d_idx, d_d2));
     if (touched) *touched = (uint64_t)nq * (uint64_t)h->n;
     return BGR_OK;
+}
+
+int bgr_nns_knn_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, float eps, unsigned flags,
+                    float max_radius, const float* d_radii, int32_t* d_idx, float* d_d2,
+                    uint64_t* touched) {
+    return knn_dev_impl(h, d_q, nq, k, eps, flags, max_radius, d_radii, d_idx, d_d2, touched, nullptr);
+}
+
+int bgr_nns_knn_skip_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flags, const uint8_t* d_skip,
+                         int32_t* d_idx, float* d_d2) {
+    return knn_dev_impl(h, d_q, nq, k, 0.f, flags, INFINITY, nullptr, d_idx, d_d2, nullptr, d_skip);
 }
 
 int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsigned flags,

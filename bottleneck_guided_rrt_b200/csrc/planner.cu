@@ -545,7 +545,8 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_LAUNCH_CHECK();
     BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
     if (have_knn)
-        BGR_CHECK(bgr_nns_knn_dev(pl->nns, pl->pnew.p, B, K, 0.f, 0u, INFINITY, nullptr, pl->knn_idx.p, pl->knn_d2.p, nullptr));
+        // candidates the state check rejected never read their neighbour rows: skip their search
+        BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->hit.p, pl->knn_idx.p, pl->knn_d2.p));
     if (edge_check) {
         plan_edges_kernel<<<gbk1, 256, 0, st>>>(d);
         BGR_LAUNCH_CHECK();

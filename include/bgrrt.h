@@ -92,6 +92,12 @@ int bgr_nns_knn(bgr_nns* nns, const float* q_3xQ, int64_t nq, int k, float eps,
 int bgr_nns_knn_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, float eps,
                     unsigned flags, float max_radius, const float* d_max_radii,
                     int32_t* d_idx_kxQ, float* d_d2_kxQ, uint64_t* touched);
+/* the same search (eps = 0, no radius limit) with a per-query skip flag on the device: rows of
+ * queries with d_skip[q] != 0 are left untouched (grid method: their warps exit at once; the
+ * plain scan computes them anyway).  The batched planner passes the state-check result
+ * (isStateValid MS:1270 comes before the knn MS:1312: rejected candidates never search). */
+int bgr_nns_knn_skip_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, unsigned flags,
+                         const uint8_t* d_skip, int32_t* d_idx_kxQ, float* d_d2_kxQ);
 
 /* Replaces Nearest(V, x) (MS:138-154) for a batch of x: Norm in the reference's mixed
  * precision (f32 differences, f64 squares/sum/sqrt, f32 result), `<=` so the LAST index
