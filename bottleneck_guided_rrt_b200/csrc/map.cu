@@ -84,10 +84,21 @@ __global__ void popcount_kernel(const uint64_t* __restrict__ bits, int64_t n, un
 __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const float* __restrict__ c3,
                                                               int64_t n, double radius,
                                                               uint8_t* __restrict__ hit,
-                                                              uint8_t* __restrict__ band) {
+                                                              uint8_t* __restrict__ band, LevelGrid dil) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
+    if (dil.bits) {
+        // gate: level 0 dilated by ceil((radius + 1e-4) / res) cells.  The centre's cell clear in it =>
+        // no leaf within radius + 1e-4 of the centre: free, and not a tolerance-band contact.
+        const int gx = (int)floor((c[0] - m.origin[0]) * m.inv_res), gy = (int)floor((c[1] - m.origin[1]) * m.inv_res),
+                  gz = (int)floor((c[2] - m.origin[2]) * m.inv_res);
+        if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2] && !test_bit(dil, gx, gy, gz)) {
+            hit[i] = 0;
+            if (band) band[i] = 0;
+            return;
+        }
+    }
     int lo[3], hi[3];
     bool empty = false;
 #pragma unroll
@@ -99,8 +110,8 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
     }
     double gmin = 1e300;
     if (!empty)
-        for (int z = lo[2]; z <= hi[2]; ++z)
-            for (int y = lo[1]; y <= hi[1]; ++y)
+        for (int z = lo[2]; z <= hi[2] && gmin >= -kBandTol; ++z)      // gmin < -tol: a hit outside the band, decided
+            for (int y = lo[1]; y <= hi[1] && gmin >= -kBandTol; ++y)
                 for (int x = lo[0]; x <= hi[0]; ++x) {
                     if (!test_bit(m.lv[0], x, y, z)) continue;
                     int lx, ly, lz;
@@ -1055,9 +1066,10 @@ struct bgr_map {
     DevBuf<unsigned long long> stats;
     DevBuf<unsigned> eflags, qctl;
     DevBuf<NarrowRec> queue;
-    DevBuf<uint64_t> dil, dil_tmp;     // level 0 dilated by dil_d cells: the sweep gate (rebuilt lazily)
-    int dil_d = 0;
-    bool dil_dirty = true;
+    DevBuf<uint64_t> dil[2], dil_tmp;  // level 0 dilated by dil_cells[s] cells (0 = stale): the gate maps of the
+    int dil_cells[2] = {0, 0};         // edge sweep and of the sphere check, rebuilt lazily after a map change
+    int dil_next = 0;
+    int last_gate_d = 0;
     bool gate_on = true;
     int pipe_chunks = 0;               // > 1: the sweep of chunk c waits for pipe.ev_in[c] (host-pointer call)
     int64_t pipe_per = 0;
@@ -1141,7 +1153,7 @@ void keys_of(const std::vector<LeafRec>& recs, std::vector<uint64_t>& keys) {
 }
 
 int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
-    h->dil_dirty = true;
+    h->dil_cells[0] = h->dil_cells[1] = 0;
     if (recs.empty()) return BGR_OK;
     BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
     BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
@@ -1153,20 +1165,24 @@ int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
 
 // level 0 grown by d cells in every direction (three separable brick-word passes); lazily
 // rebuilt after a map change or when the query radius asks for another d
-int ensure_dilated(bgr_map* h, int d) {
-    if (!h->dil_dirty && h->dil_d == d) return BGR_OK;
+int ensure_dilated(bgr_map* h, int d, const uint64_t** out) {
+    for (int k = 0; k < 2; ++k)
+        if (h->dil_cells[k] == d) { *out = h->dil[k].p; return BGR_OK; }
+    const int k = h->dil_cells[0] == 0 ? 0 : (h->dil_cells[1] == 0 ? 1 : h->dil_next);
+    h->dil_next = k ^ 1;
+    h->dil_cells[k] = 0;
     const int64_t w = h->words[0];
-    BGR_CHECK(h->dil.reserve(w, h->stream, false));
+    BGR_CHECK(h->dil[k].reserve(w, h->stream, false));
     BGR_CHECK(h->dil_tmp.reserve(w, h->stream, false));
     const unsigned nblk = (unsigned)div_up(w, 256);
-    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->bits[0].p, h->dil.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 0, d);
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->bits[0].p, h->dil[k].p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 0, d);
     BGR_LAUNCH_CHECK();
-    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil.p, h->dil_tmp.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 1, d);
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil[k].p, h->dil_tmp.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 1, d);
     BGR_LAUNCH_CHECK();
-    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil_tmp.p, h->dil.p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 2, d);
+    dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil_tmp.p, h->dil[k].p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 2, d);
     BGR_LAUNCH_CHECK();
-    h->dil_d = d;
-    h->dil_dirty = false;
+    h->dil_cells[k] = d;
+    *out = h->dil[k].p;
     return BGR_OK;
 }
 
@@ -1308,7 +1324,16 @@ int bgr_map_download_bitmap(bgr_map* h, uint64_t* out, int64_t* n_words) {
 int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double radius, uint8_t* d_hit, uint8_t* d_band) {
     BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_spheres arguments");
     if (n == 0) return BGR_OK;
-    collide_spheres_kernel<<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band);
+    LevelGrid dil;
+    dil.bits = nullptr;
+    for (int a = 0; a < 3; ++a) dil.nb[a] = h->nb[0][a];
+    const int gate_d = (int)std::ceil((radius + kSweepMargin) / h->res + 1e-9);
+    if (h->gate_on && gate_d >= 1 && gate_d <= 3) {
+        const uint64_t* bits = nullptr;
+        BGR_CHECK(ensure_dilated(h, gate_d, &bits));
+        dil.bits = const_cast<uint64_t*>(bits);
+    }
+    collide_spheres_kernel<<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
@@ -1354,7 +1379,9 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     // it belongs to the map, not to the query batch)
     const int gate_d = (int)std::ceil((radius + kSweepMargin) / h->res + 1e-9);
     const bool gate = fast_ok(h, radius) && h->gate_on && gate_d >= 1 && gate_d <= 3;
-    if (gate) BGR_CHECK(ensure_dilated(h, gate_d));
+    const uint64_t* dil_bits = nullptr;
+    if (gate) BGR_CHECK(ensure_dilated(h, gate_d, &dil_bits));
+    h->last_gate_d = gate ? gate_d : 0;
     if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[0], h->stream));
     if (fast) {
         const int64_t cap = std::max<int64_t>(1 << 16, 4 * n);
@@ -1366,7 +1393,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.queue = h->queue.p; a.queue_cap = (unsigned)std::min<int64_t>(cap, 0x7fffffff);
         a.qctl = h->qctl.p; a.stats = h->stats.p; a.hit = d_hit; a.band = d_band;
         a.gate_d = gate ? gate_d : 0;
-        a.dil.bits = gate ? h->dil.p : nullptr;
+        a.dil.bits = const_cast<uint64_t*>(dil_bits);
         for (int ax = 0; ax < 3; ++ax) a.dil.nb[ax] = h->nb[0][ax];
         // one sweep launch per chunk of a chunked host call (each waits for its H2D copy), one
         // narrow / finalize pass over the whole batch
@@ -1486,7 +1513,7 @@ int bgr_map_set_gate(bgr_map* h, int on) {
 int bgr_map_last_gate_stats(bgr_map* h, uint64_t out[2]) {
     BGR_ARG(h != nullptr && out, "bad arguments");
     out[0] = 0;
-    out[1] = (uint64_t)(h->dil_dirty ? 0 : h->dil_d);
+    out[1] = (uint64_t)h->last_gate_d;
     if (!h->stats.p || h->stats.cap < 6) return BGR_OK;
     unsigned long long s = 0;
     BGR_CUDA(cudaMemcpyAsync(&s, h->stats.p + 4, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
@@ -1501,7 +1528,7 @@ int bgr_map_destroy(bgr_map* h) {
     for (int L = 0; L <= kMaxLevel; ++L) h->bits[L].release();
     h->recs.release(); h->p1_dev.release(); h->p2_dev.release(); h->hit_dev.release(); h->band_dev.release();
     h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
-    h->dil.release(); h->dil_tmp.release();
+    h->dil[0].release(); h->dil[1].release(); h->dil_tmp.release();
     h->pipe.release();
     for (int i = 0; i < 5; ++i)
         if (h->tev[i]) cudaEventDestroy(h->tev[i]);

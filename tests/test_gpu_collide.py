@@ -257,6 +257,28 @@ def test_edges_gate_is_exact(bgr, oracle, radius, shape):
     assert not np.array_equal(h0u, h0)
 
 
+@pytest.mark.parametrize("radius", [0.03, 0.1, 0.149])
+def test_spheres_gate_is_exact(bgr, oracle, radius):
+    """the dilated-map gate of the sphere check never changes hit / in_band (gate on == off),
+    including centres outside the map and after an incremental update."""
+    occ, boxes, m = _map(bgr, oracle, 96, 5, 3, n_walls=2, wall_thick=3, door_cells=5)
+    mt = oracle.MT(55)
+    pts = np.concatenate([_points_near_obstacles(oracle, occ, 40000, 56, 0.6),
+                          (mt.real(3 * 20000).reshape(-1, 3) * 5.2 - 0.2).astype(np.float32)])
+    m.set_gate(True)
+    h1, b1 = m.collide_spheres(pts, radius)
+    m.set_gate(False)
+    h0, b0 = m.collide_spheres(pts, radius)
+    assert np.array_equal(h1, h0) and np.array_equal(b1, b0)
+    assert 0.05 < h0.mean() < 0.95
+    m.update_boxes(np.array([[2.425, 2.425, 2.425, 0.05, 1.0, 0.5]]), boxes[:3000])
+    h0u, b0u = m.collide_spheres(pts, radius)
+    m.set_gate(True)
+    h1u, b1u = m.collide_spheres(pts, radius)
+    assert np.array_equal(h1u, h0u) and np.array_equal(b1u, b0u)
+    assert not np.array_equal(h0u, h0)
+
+
 def test_edges_chunked_host_call_equals_device_call(bgr, oracle):
     """a large host-pointer batch is cut into chunks whose H2D copies overlap the sweep of the
     previous chunk: same hit / in_band bytes and same counters as the one-launch device call."""
