@@ -81,11 +81,16 @@ __global__ void popcount_kernel(const uint64_t* __restrict__ bits, int64_t n, un
 
 // ------------------------------------------------------------------ spheres (isStateValid)
 // Exact closed form: gap = dist(centre, leaf box) - r in double; hit = gap < 0.
+// One warp per sphere: the cells of the sphere's box (radius + margin, +1 cell) are read as whole
+// 4x4x4 brick words, one brick per lane (a 0.1 m sphere at 0.05 m cells touches <= 3x3x3 bricks:
+// 27 loads instead of 343 bit probes), masked to the box; each lane walks the set bits of its
+// word: leaf of the cell, exact point-to-box distance.  min over the warp.
 __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const float* __restrict__ c3,
                                                               int64_t n, double radius,
                                                               uint8_t* __restrict__ hit,
                                                               uint8_t* __restrict__ band, LevelGrid dil) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (i >= n) return;
     const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
     if (dil.bits) {
@@ -94,8 +99,10 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         const int gx = (int)floor((c[0] - m.origin[0]) * m.inv_res), gy = (int)floor((c[1] - m.origin[1]) * m.inv_res),
                   gz = (int)floor((c[2] - m.origin[2]) * m.inv_res);
         if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2] && !test_bit(dil, gx, gy, gz)) {
-            hit[i] = 0;
-            if (band) band[i] = 0;
+            if (lane == 0) {
+                hit[i] = 0;
+                if (band) band[i] = 0;
+            }
             return;
         }
     }
@@ -109,25 +116,50 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         empty |= lo[a] > hi[a];
     }
     double gmin = 1e300;
-    if (!empty)
-        for (int z = lo[2]; z <= hi[2] && gmin >= -kBandTol; ++z)      // gmin < -tol: a hit outside the band, decided
-            for (int y = lo[1]; y <= hi[1] && gmin >= -kBandTol; ++y)
-                for (int x = lo[0]; x <= hi[0]; ++x) {
-                    if (!test_bit(m.lv[0], x, y, z)) continue;
-                    int lx, ly, lz;
-                    const int L = find_leaf(m, x, y, z, lx, ly, lz);
-                    D3 bc;
-                    double e;
-                    leaf_box(m, L, lx, ly, lz, bc, e);
-                    const double tx = fmax(0.0, fabs(c[0] - bc.x) - e), ty = fmax(0.0, fabs(c[1] - bc.y) - e),
-                                 tz = fmax(0.0, fabs(c[2] - bc.z) - e);
-                    double d2 = tx * tx;
-                    d2 += ty * ty;
-                    d2 += tz * tz;
-                    gmin = fmin(gmin, sqrt(d2) - radius);
-                }
-    hit[i] = gmin < 0.0 ? 1 : 0;
-    if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
+    if (!empty) {
+        const int bl[3] = {lo[0] >> 2, lo[1] >> 2, lo[2] >> 2};
+        const int nbr[3] = {(hi[0] >> 2) - bl[0] + 1, (hi[1] >> 2) - bl[1] + 1, (hi[2] >> 2) - bl[2] + 1};
+        const int total = nbr[0] * nbr[1] * nbr[2];
+        for (int t = lane; t < total; t += 32) {
+            const int bx = bl[0] + t % nbr[0], by = bl[1] + (t / nbr[0]) % nbr[1], bz = bl[2] + t / (nbr[0] * nbr[1]);
+            unsigned long long W = __ldg(m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0] + bx);
+            if (W == 0ull) continue;
+            // cells of this brick inside the box, per axis
+            const int bb[3] = {bx, by, bz};
+            unsigned long long mask = ~0ull;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const int v0 = max(lo[a] - 4 * bb[a], 0), v1 = min(hi[a] - 4 * bb[a], 3);
+                unsigned long long ma = 0ull;
+                for (int v = v0; v <= v1; ++v)
+                    ma |= a == 0 ? (0x1111111111111111ull << v) : (a == 1 ? (0x000F000F000F000Full << (4 * v)) : (0xFFFFull << (16 * v)));
+                mask &= ma;
+            }
+            W &= mask;
+            while (W) {
+                const int bit = __ffsll((long long)W) - 1;
+                W &= W - 1ull;
+                const int x = 4 * bx + (bit & 3), y = 4 * by + ((bit >> 2) & 3), z = 4 * bz + (bit >> 4);
+                int lx, ly, lz;
+                const int L = find_leaf(m, x, y, z, lx, ly, lz);
+                D3 bc;
+                double e;
+                leaf_box(m, L, lx, ly, lz, bc, e);
+                const double tx = fmax(0.0, fabs(c[0] - bc.x) - e), ty = fmax(0.0, fabs(c[1] - bc.y) - e),
+                             tz = fmax(0.0, fabs(c[2] - bc.z) - e);
+                double d2 = tx * tx;
+                d2 += ty * ty;
+                d2 += tz * tz;
+                gmin = fmin(gmin, sqrt(d2) - radius);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) gmin = fmin(gmin, __shfl_xor_sync(kFull, gmin, o));
+    if (lane == 0) {
+        hit[i] = gmin < 0.0 ? 1 : 0;
+        if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
+    }
 }
 
 // ------------------------------------------------------------------ edges (isLineValid)
@@ -1333,7 +1365,7 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
         BGR_CHECK(ensure_dilated(h, gate_d, &bits));
         dil.bits = const_cast<uint64_t*>(bits);
     }
-    collide_spheres_kernel<<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
+    collide_spheres_kernel<<<(unsigned)div_up(n, 4), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }

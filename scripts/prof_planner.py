@@ -17,7 +17,7 @@ for w in range(3):
     ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
 ms = np.asarray(ms, dtype=np.float32)
 table = synth.points(9, 200_000, n_map * 0.05)
-P = B.PlannerParams((0.2, 0.2, 0.2), (12.6, 12.6, 12.6), mode=B.PLAN_MODE_MS, k=16, batch=4096,
+P = B.PlannerParams((0.2, 0.2, 0.2), (12.6, 12.6, 12.6), mode=B.PLAN_MODE_MS, k=16, batch=int(os.environ.get("BATCH", "4096")),
                     flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | B.PLAN_NO_GOAL, seed=5489)
 pl = B.Planner(P, omap, table, ms)
 target = int(os.environ.get("GROW", "150000"))
