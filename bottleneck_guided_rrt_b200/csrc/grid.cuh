@@ -567,12 +567,15 @@ struct GridNearestArgs {
     int32_t* idx;
     float* dist;
     int64_t index_base;
+    const long long* nq_dev;   // optional device-side query count (see NearestArgs)
+    int64_t nq_base;
 };
 
 __global__ void __launch_bounds__(kGridWarps * 32) grid_nearest_kernel(GridNearestArgs a) {
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
     if (qi >= a.nq) return;
+    if (a.nq_dev && qi >= a.nq_base + (int64_t)__ldg(a.nq_dev)) return;
     const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
     const GridGeom& gm = a.gm;
     const double kInfD = __longlong_as_double(0x7ff0000000000000LL);
@@ -696,7 +699,8 @@ __global__ void __launch_bounds__(kGridWarps * 32) grid_nearest_kernel(GridNeare
 }
 
 inline int grid_nearest(GridIndex& G, const float* x, const float* y, const float* z, int64_t n, const float* d_q,
-                        int64_t nq, int32_t* d_idx, float* d_dist, int64_t index_base, cudaStream_t st) {
+                        int64_t nq, int32_t* d_idx, float* d_dist, int64_t index_base, cudaStream_t st,
+                        const long long* nq_dev = nullptr, int64_t nq_base = 0) {
     GridNearestArgs a;
     a.gm = G.geom;
     a.pts = G.pts.p;
@@ -704,6 +708,7 @@ inline int grid_nearest(GridIndex& G, const float* x, const float* y, const floa
     a.n_indexed = G.n_indexed;
     a.x = x; a.y = y; a.z = z; a.n = n;
     a.q = d_q; a.nq = nq; a.idx = d_idx; a.dist = d_dist; a.index_base = index_base;
+    a.nq_dev = nq_dev; a.nq_base = nq_base;
     grid_nearest_kernel<<<(unsigned)div_up(nq, kGridWarps), kGridWarps * 32, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
     return BGR_OK;

@@ -8,4 +8,7 @@ int nns_reserve(bgr_nns* h, int64_t n);                       // capacity only, 
 void nns_soa(bgr_nns* h, float** x, float** y, float** z, float4** f4);   // current arrays (valid until the next reserve)
 void nns_set_size(bgr_nns* h, int64_t n);                     // after a device-side append
 cudaStream_t nns_stream(bgr_nns* h);
+// Nearest over a query array whose valid length (count_base + *d_count <= nq_cap) is known only on the device
+int nns_nearest_counted(bgr_nns* h, const float* d_q, int64_t nq_cap, int64_t nq_hint, const long long* d_count,
+                        int64_t count_base, int32_t* d_idx, float* d_dist);
 }  // namespace bgr

@@ -23,7 +23,13 @@ struct NearestArgs {
     int32_t* idx;    // [chunks][Q]
     float* dist;     // [chunks][Q]
     int64_t index_base;
+    const long long* nq_dev;   // optional: only the first nq_base + *nq_dev queries are valid (<= nq)
+    int64_t nq_base;
 };
+
+__device__ __forceinline__ int64_t valid_queries(const long long* nq_dev, int64_t nq_base, int64_t nq) {
+    return nq_dev ? min(nq, nq_base + (int64_t)__ldg(nq_dev)) : nq;
+}
 
 __device__ __forceinline__ double nextup_sq(float f) {
     const float nu = __uint_as_float(__float_as_uint(f) + 1u);  // f >= 0, finite or inf
@@ -34,6 +40,8 @@ __device__ __forceinline__ double nextup_sq(float f) {
 template <int R>
 __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    // query count known only on the device (planner: distinct sample points of the batch)
+    if ((int64_t)blockIdx.x * kConsumerWarps * R >= valid_queries(a.nq_dev, a.nq_base, a.nq)) return;
     float* tiles = reinterpret_cast<float*>(smem_raw);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + kStages * 3 * kTile);
     uint64_t* empty_bar = full_bar + kStages;

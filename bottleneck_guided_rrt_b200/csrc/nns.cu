@@ -401,7 +401,11 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
     return BGR_OK;
 }
 
-int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, float* d_dist) {
+// nq = capacity of the query / result arrays; with d_count only the first count_base + *d_count
+// queries are valid (the rest of the rows is left undefined) and nq_hint (host guess of that
+// number, e.g. the previous batch's) sizes the scan.
+int nearest_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, float* d_dist,
+                            const long long* d_count, int64_t count_base, int64_t nq_hint) {
     BGR_ARG(h != nullptr && nq >= 0, "bad nearest arguments");
     BGR_ARG(h->n >= 1, "Nearest on an empty tree");
     if (nq == 0) return BGR_OK;
@@ -411,16 +415,18 @@ int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx
         int method;
         BGR_CHECK(pick_method(h, nq, true, &method));
         if (method == BGR_METHOD_GRID || method == BGR_METHOD_GRID_GENERAL) {
-            return grid_nearest(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, d_idx, d_dist, h->index_base, h->stream);
+            return grid_nearest(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, d_idx, d_dist, h->index_base, h->stream,
+                                d_count, count_base);
         }
     }
     int R, chunks;
     int64_t per;
-    plan_scan(nq, h->n, &R, &chunks, &per);
+    plan_scan(d_count ? std::max<int64_t>(1, std::min(nq, nq_hint)) : nq, h->n, &R, &chunks, &per);
     if (R > 4) R = 4;   // double-precision state: keep registers in check
     NearestArgs a;
     a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = h->n;
     a.q = d_q; a.nq = nq; a.chunk_nodes = per; a.index_base = h->index_base;
+    a.nq_dev = d_count; a.nq_base = count_base;
     BGR_CHECK(h->part_idx.reserve((int64_t)chunks * nq, h->stream, false));
     BGR_CHECK(h->part_d2.reserve((int64_t)chunks * nq, h->stream, false));
     a.idx = h->part_idx.p; a.dist = h->part_d2.p;
@@ -434,6 +440,11 @@ int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
+
+int bgr_nns_nearest_dev(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, float* d_dist) {
+    return nearest_dev_impl(h, d_q, nq, d_idx, d_dist, nullptr, 0, nq);
+}
+
 
 int bgr_nns_nearest(bgr_nns* h, const float* q, int64_t nq, int32_t* idx, float* dist) {
     BGR_ARG(h != nullptr && nq >= 0 && (nq == 0 || (q && idx)), "bad nearest arguments");
@@ -479,3 +490,10 @@ int bgr_knn_merge_dev(const int32_t* d_idx_in, const float* d_d2_in, int g, int6
 }
 
 }  // extern "C"
+
+namespace bgr {
+int nns_nearest_counted(bgr_nns* h, const float* d_q, int64_t nq_cap, int64_t nq_hint, const long long* d_count,
+                        int64_t count_base, int32_t* d_idx, float* d_dist) {
+    return nearest_dev_impl(h, d_q, nq_cap, d_idx, d_dist, d_count, count_base, nq_hint);
+}
+}  // namespace bgr

@@ -46,7 +46,13 @@ struct PlanDev {                 // device view shared by the kernels
     int32_t *parent, *new_index;
     float* cost;
     unsigned long long* rkey;    // per node rewire proposal key
-    long long* counters;         // [0] accepted [1] goal candidate (-1) [2..] stats deltas
+    long long* counters;         // [0] accepted [1] goal candidate (-1) [2..] stats deltas [10] distinct table samples
+    // Nearest runs on the DISTINCT sample points of the batch: slots 0..n_fixed-1 = goal (+ the 3
+    // milestones in MS mode), then the table samples, compacted; qslot[c] = candidate c's slot
+    float* uq;
+    int32_t* qslot;
+    const int32_t* u_near;
+    int n_fixed;
 };
 
 // ------------------------------------------------------------------ MT19937 on the device
@@ -119,30 +125,58 @@ __device__ __forceinline__ float norm_ref(float ax, float ay, float az, float bx
 // ------------------------------------------------------------------ per-candidate kernels
 __global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 | RS:1155-1178
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= d.B) return;
-    const uint32_t* w = d.words + (size_t)c * d.W;
-    const float rand_chance = __double2float_rn(std_uniform(w[0], w[1], 0.0, 1.0));
-    long long ri = (long long)(float)(int)std_uniform(w[2], w[3], 0.0, (double)d.nt);   // float random_indice = int(x(gen))
-    if (ri > d.nt - 1) ri = d.nt - 1;
-    const float* src;
-    if (d.p.mode == BGR_PLAN_MODE_MS) {
-        int mi = (int)std_uniform(w[4], w[5], 0.0, 3.0);
-        if (mi > 2) mi = 2;
-        if ((double)rand_chance > 0.8) src = d.table + 3 * ri;
-        else if ((double)rand_chance < 0.8 && (double)rand_chance > 0.5) src = d.p.goal;
-        else src = d.milestones + 3 * mi;
-    } else {
-        src = rand_chance > d.p.goal_chance ? d.table + 3 * ri : d.p.goal;
+    const int lane = threadIdx.x & 31;
+    const bool live = c < d.B;
+    const float* src = d.p.goal;
+    int slot = 0;                                               // goal
+    bool from_table = false;
+    if (live) {
+        const uint32_t* w = d.words + (size_t)c * d.W;
+        const float rand_chance = __double2float_rn(std_uniform(w[0], w[1], 0.0, 1.0));
+        long long ri = (long long)(float)(int)std_uniform(w[2], w[3], 0.0, (double)d.nt);   // float random_indice = int(x(gen))
+        if (ri > d.nt - 1) ri = d.nt - 1;
+        if (d.p.mode == BGR_PLAN_MODE_MS) {
+            int mi = (int)std_uniform(w[4], w[5], 0.0, 3.0);
+            if (mi > 2) mi = 2;
+            if ((double)rand_chance > 0.8) { src = d.table + 3 * ri; from_table = true; }
+            else if ((double)rand_chance < 0.8 && (double)rand_chance > 0.5) src = d.p.goal;
+            else { src = d.milestones + 3 * mi; slot = 1 + mi; }
+        } else {
+            if (rand_chance > d.p.goal_chance) { src = d.table + 3 * ri; from_table = true; }
+        }
     }
+    // table samples take the next free slots (one atomic per warp); goal / milestone samples of the
+    // whole batch share their fixed slot: one Nearest query instead of thousands of identical ones
+    const unsigned tm = __ballot_sync(kFull, from_table);
+    if (tm) {
+        int base = 0;
+        if (lane == __ffs(tm) - 1) base = (int)atomicAdd((unsigned long long*)&d.counters[10], (unsigned long long)__popc(tm));
+        base = __shfl_sync(kFull, base, __ffs(tm) - 1);
+        if (from_table) slot = d.n_fixed + base + __popc(tm & ((1u << lane) - 1u));
+    }
+    if (!live) return;
     d.prand[3 * c] = src[0];
     d.prand[3 * c + 1] = src[1];
     d.prand[3 * c + 2] = src[2];
+    d.qslot[c] = slot;
+    if (from_table) {
+        d.uq[3 * slot] = src[0];
+        d.uq[3 * slot + 1] = src[1];
+        d.uq[3 * slot + 2] = src[2];
+    }
+    if (c < d.n_fixed) {                                        // the fixed slots (B >= 1: thread 0 writes all of them)
+        for (int f = c; f < d.n_fixed; f += d.B) {
+            const float* fs = f == 0 ? d.p.goal : d.milestones + 3 * (f - 1);
+            d.uq[3 * f] = fs[0]; d.uq[3 * f + 1] = fs[1]; d.uq[3 * f + 2] = fs[2];
+        }
+    }
 }
 
 __global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= d.B) return;
-    const int32_t ni = d.near[c];
+    const int32_t ni = d.u_near[d.qslot[c]];
+    d.near[c] = ni;
     const float nx = d.x[ni], ny = d.y[ni], nz = d.z[ni];
     const float rx = d.prand[3 * c], ry = d.prand[3 * c + 1], rz = d.prand[3 * c + 2];
     float ox, oy, oz;
@@ -390,7 +424,9 @@ struct bgr_planner {
     DevBuf<uint32_t> mt_state, words;
     DevBuf<float> table, milestones, prand, pnew, near_dist, knn_d2, e1, e2, costs, cost, psis, psi;
     DevBuf<uint8_t> found, hit, band, ehit, eband, ok;
-    DevBuf<int32_t> par, near, knn_idx, parent, new_index;
+    DevBuf<int32_t> par, near, knn_idx, parent, new_index, qslot, u_near;
+    DevBuf<float> uq, u_dist;
+    int64_t unique_hint = 0;   // distinct sample points of the previous batch (sizes the next Nearest scan)
     DevBuf<unsigned long long> rkey;
     int64_t rkey_init = 0;       // entries of rkey already set to ~0
     DevBuf<long long> counters;
@@ -497,6 +533,11 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_CHECK(pl->band.reserve(B, st, false));
     BGR_CHECK(pl->ok.reserve(B, st, false));
     BGR_CHECK(pl->near.reserve(B, st, false));
+    const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    BGR_CHECK(pl->qslot.reserve(B, st, false));
+    BGR_CHECK(pl->u_near.reserve(B + n_fixed, st, false));
+    BGR_CHECK(pl->u_dist.reserve(B + n_fixed, st, false));
+    BGR_CHECK(pl->uq.reserve(3 * (int64_t)(B + n_fixed), st, false));
     BGR_CHECK(pl->parent.reserve(B, st, false));
     BGR_CHECK(pl->new_index.reserve(B, st, false));
     BGR_CHECK(pl->cost.reserve(B, st, false));
@@ -533,6 +574,7 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     d.e1 = pl->e1.p; d.e2 = pl->e2.p; d.ehit = pl->ehit.p; d.eband = pl->eband.p;
     d.costs = pl->costs.p; d.psis = pl->psis.p; d.psi = pl->psi.p; d.ok = pl->ok.p; d.parent = pl->parent.p; d.new_index = pl->new_index.p;
     d.cost = pl->cost.p; d.rkey = pl->rkey.p; d.counters = pl->counters.p;
+    d.uq = pl->uq.p; d.qslot = pl->qslot.p; d.u_near = pl->u_near.p; d.n_fixed = n_fixed;
 
     const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);
     BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
@@ -540,7 +582,8 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_LAUNCH_CHECK();
     plan_sample_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
-    BGR_CHECK(bgr_nns_nearest_dev(pl->nns, pl->prand.p, B, pl->near.p, pl->near_dist.p));
+    BGR_CHECK(nns_nearest_counted(pl->nns, pl->uq.p, B + n_fixed, pl->unique_hint > 0 ? pl->unique_hint + pl->unique_hint / 4 + 8 : B + n_fixed,
+                                  pl->counters.p + 10, n_fixed, pl->u_near.p, pl->u_dist.p));
     plan_steer_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
     BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
@@ -571,6 +614,7 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_CUDA(cudaMemcpyAsync(hc, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
     BGR_CUDA(cudaStreamSynchronize(st));
     const int acc = (int)hc[0];
+    pl->unique_hint = hc[10] + n_fixed;
     const bool goal = hc[1] >= 0;
     nns_set_size(pl->nns, N + acc + (goal ? 1 : 0));
     pl->stats[0] += 1;
