@@ -100,6 +100,7 @@ def lib():
     L.bgr_planner_create.argtypes = [vp, vp, vp, i64, vp, i32, vp]
     L.bgr_planner_set_stream.argtypes = [vp, vp]
     L.bgr_planner_step.argtypes = [vp, vp, vp]
+    L.bgr_planner_run_many.argtypes = [vp, i32, i64, i64, vp]
     L.bgr_planner_run.argtypes = [vp, i64, i64, vp]
     L.bgr_planner_size.restype = i64
     L.bgr_planner_size.argtypes = [vp]
@@ -568,6 +569,16 @@ class Planner:
         g = C.c_int(0)
         _check(lib().bgr_planner_run(self._h, max_nodes, max_batches, C.byref(g)))
         return bool(g.value)
+
+    @staticmethod
+    def run_many(planners, max_nodes, max_batches=1 << 40):
+        """bgr_planner_run_many: independent queries stepped round-robin, one stream + one map
+        handle per planner.  Returns the list of goal flags."""
+        n = len(planners)
+        arr = (C.c_void_p * n)(*[p._h for p in planners])
+        flags = (C.c_int * n)()
+        _check(lib().bgr_planner_run_many(arr, n, max_nodes, max_batches, flags))
+        return [bool(f) for f in flags]
 
     def tree(self):
         n = len(self)

@@ -426,6 +426,7 @@ struct bgr_planner {
     DevBuf<uint8_t> found, hit, band, ehit, eband, ok;
     DevBuf<int32_t> par, near, knn_idx, parent, new_index, qslot, u_near;
     DevBuf<float> uq, u_dist;
+    int64_t pending_n = 0;     // tree size at the launch of the step in flight
     int64_t unique_hint = 0;   // distinct sample points of the previous batch (sizes the next Nearest scan)
     DevBuf<unsigned long long> rkey;
     int64_t rkey_init = 0;       // entries of rkey already set to ~0
@@ -508,11 +509,10 @@ int bgr_planner_nns(bgr_planner* pl, bgr_nns** out) {
     return BGR_OK;
 }
 
-int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
-    BGR_ARG(pl != nullptr, "null planner");
-    if (n_accepted) *n_accepted = 0;
-    if (goal_reached) *goal_reached = pl->goal_reached;
-    if (pl->goal_reached) return BGR_OK;
+// One step = step_launch (everything enqueued on the planner's stream, counters copied back
+// asynchronously) + step_finish (wait for the stream, host bookkeeping).  bgr_planner_run_many
+// launches the steps of several independent planners before it waits for any of them.
+static int step_launch(bgr_planner* pl) {
     const bgr_planner_params& P = pl->p;
     const int B = P.batch, K = P.k, K1 = K + 1;
     const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
@@ -612,7 +612,17 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     }
     long long* hc = (long long*)pl->host_counters.p;
     BGR_CUDA(cudaMemcpyAsync(hc, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
-    BGR_CUDA(cudaStreamSynchronize(st));
+    pl->pending_n = N;
+    return BGR_OK;
+}
+
+static int step_finish(bgr_planner* pl, int* n_accepted, int* goal_reached) {
+    const bgr_planner_params& P = pl->p;
+    const int B = P.batch;
+    const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    const int64_t N = pl->pending_n;
+    long long* hc = (long long*)pl->host_counters.p;
+    BGR_CUDA(cudaStreamSynchronize(pl->stream));
     const int acc = (int)hc[0];
     pl->unique_hint = hc[10] + n_fixed;
     const bool goal = hc[1] >= 0;
@@ -630,6 +640,41 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     }
     if (n_accepted) *n_accepted = acc;
     if (goal_reached) *goal_reached = pl->goal_reached;
+    return BGR_OK;
+}
+
+int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
+    BGR_ARG(pl != nullptr, "null planner");
+    if (n_accepted) *n_accepted = 0;
+    if (goal_reached) *goal_reached = pl->goal_reached;
+    if (pl->goal_reached) return BGR_OK;
+    BGR_CHECK(step_launch(pl));
+    return step_finish(pl, n_accepted, goal_reached);
+}
+
+// Independent planning queries (north_star: "independent start/goal planning queries per GPU"):
+// every round launches one step of each unfinished planner on its own stream, then collects
+// them, so the small per-step kernels of different queries overlap on the device.  The planners
+// must not share a stream or a map handle (the map owns per-call scratch memory).
+int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t max_batches, int* goal_reached) {
+    BGR_ARG(pls != nullptr && n >= 0, "bad arguments");
+    for (int i = 0; i < n; ++i) {
+        BGR_ARG(pls[i] != nullptr, "null planner %d", i);
+        for (int j = 0; j < i; ++j)
+            BGR_ARG(pls[i] != pls[j] && pls[i]->map != pls[j]->map && pls[i]->stream != pls[j]->stream,
+                    "planners %d and %d share a handle, a map or a stream", j, i);
+    }
+    std::vector<int> active;
+    for (int64_t b = 0; b < max_batches; ++b) {
+        active.clear();
+        for (int i = 0; i < n; ++i)
+            if (!pls[i]->goal_reached && bgr_nns_size(pls[i]->nns) < max_nodes) active.push_back(i);
+        if (active.empty()) break;
+        for (int i : active) BGR_CHECK(step_launch(pls[i]));
+        for (int i : active) BGR_CHECK(step_finish(pls[i], nullptr, nullptr));
+    }
+    if (goal_reached)
+        for (int i = 0; i < n; ++i) goal_reached[i] = pls[i]->goal_reached;
     return BGR_OK;
 }
 

@@ -291,6 +291,12 @@ int bgr_planner_set_stream(bgr_planner* pl, void* cuda_stream);
 int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached);
 /* steps until the goal is reached, the tree has >= max_nodes nodes or max_batches were run */
 int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached);
+/* independent planning queries (one planner per start/goal pair; the reference runs one process
+ * per query): every round launches one step of each unfinished planner on its own stream before
+ * waiting for any of them, so the steps overlap on the device.  Each planner's tree is exactly
+ * the one bgr_planner_run would grow.  The planners must not share a stream or a map handle.
+ * goal_reached: n flags (may be NULL). */
+int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t max_batches, int* goal_reached);
 int64_t bgr_planner_size(const bgr_planner* pl);
 /* tree download: xyz as 3 x N column-major (x0,y0,z0,...), parent[0] = -1 */
 int bgr_planner_get_tree(bgr_planner* pl, float* xyz_3xN, int32_t* parent);

@@ -103,3 +103,37 @@ def test_planner_argument_errors(bgr, world):
         bgr.Planner(bgr.PlannerParams((0, 0, 0), (1, 1, 1), mode=bgr.PLAN_MODE_MS), m, table, None)
     with pytest.raises(bgr.BgrError):
         bgr.Planner(bgr.PlannerParams((0, 0, 0), (1, 1, 1), flags=64), m, table, ms)
+
+
+def test_run_many_equals_run(bgr, oracle):
+    """bgr_planner_run_many (independent queries stepped round-robin on their own streams / map
+    handles) grows exactly the trees bgr_planner_run grows one query at a time."""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(64, 1, occupancy=0.02)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 2)
+    table = synth.points(9, 50000, 3.2)
+    ms = np.array([[0.8, 1.6, 1.6], [1.6, 1.6, 1.6], [2.4, 1.6, 1.6]], dtype=np.float32)
+    goals = [(3.0, 3.0, 3.0), (2.9, 0.3, 2.8), (0.3, 2.9, 0.4), (3.0, 0.2, 0.2)]
+
+    def make(i, stream=None):
+        m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64), stream=stream)
+        m.set_boxes(boxes)
+        P = bgr.PlannerParams((0.2, 0.2, 0.2), goals[i], mode=bgr.PLAN_MODE_MS, k=8, batch=64,
+                              flags=bgr.PLAN_EDGE_CHECK | bgr.PLAN_REWIRE, seed=100 + i)
+        return bgr.Planner(P, m, table, ms, stream=stream)
+
+    streams = [torch.cuda.Stream() for _ in goals]
+    many = [make(i, s.cuda_stream) for i, s in enumerate(streams)]
+    flags = bgr.Planner.run_many(many, 3000, 400)
+    torch.cuda.synchronize()
+    for i in range(len(goals)):
+        one = make(i)
+        g = one.run(3000, 400)
+        assert g == flags[i] and len(one) == len(many[i])
+        ax, ap = one.tree()
+        bx, bp = many[i].tree()
+        assert np.array_equal(ax.view(np.uint32), bx.view(np.uint32)) and np.array_equal(ap, bp)
+        assert one.stats() == many[i].stats()
+    with pytest.raises(RuntimeError):
+        bgr.Planner.run_many([many[0], many[0]], 10, 1)
