@@ -10,8 +10,11 @@
 //   parents    : int32 array (the reference keeps them as float in V[i][3])
 //   MT19937    : 624-word state in HBM, advanced by a one-CTA kernel (3-phase parallel twist)
 // One 48-byte counter block is read back per step (accepted count, goal flag, statistics).
+#include <atomic>
 #include <cmath>
 #include <cstring>
+#include <string>
+#include <thread>
 #include <vector>
 #include "internal.cuh"
 
@@ -653,9 +656,9 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
 }
 
 // Independent planning queries (north_star: "independent start/goal planning queries per GPU"):
-// every round launches one step of each unfinished planner on its own stream, then collects
-// them, so the small per-step kernels of different queries overlap on the device.  The planners
-// must not share a stream or a map handle (the map owns per-call scratch memory).
+// the queries run concurrently, each on its own stream, so their small per-step kernels overlap
+// on the device.  The planners must not share a stream or a map handle (the map owns per-call
+// scratch memory).
 int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t max_batches, int* goal_reached) {
     BGR_ARG(pls != nullptr && n >= 0, "bad arguments");
     for (int i = 0; i < n; ++i) {
@@ -664,15 +667,41 @@ int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t ma
             BGR_ARG(pls[i] != pls[j] && pls[i]->map != pls[j]->map && pls[i]->stream != pls[j]->stream,
                     "planners %d and %d share a handle, a map or a stream", j, i);
     }
-    std::vector<int> active;
-    for (int64_t b = 0; b < max_batches; ++b) {
-        active.clear();
-        for (int i = 0; i < n; ++i)
-            if (!pls[i]->goal_reached && bgr_nns_size(pls[i]->nns) < max_nodes) active.push_back(i);
-        if (active.empty()) break;
-        for (int i : active) BGR_CHECK(step_launch(pls[i]));
-        for (int i : active) BGR_CHECK(step_finish(pls[i], nullptr, nullptr));
+    // one host thread per query in flight (a step is ~30 driver calls: a single thread cannot feed
+    // several streams fast enough); each thread runs whole queries, taken from a shared counter
+    int dev = 0;
+    BGR_CUDA(cudaGetDevice(&dev));
+    const int nthreads = std::max(1, std::min(n, std::min(16, (int)std::thread::hardware_concurrency())));
+    std::atomic<int> next{0};
+    std::vector<int> rcs((size_t)n, BGR_OK);
+    std::vector<std::string> errs((size_t)n);
+    auto worker = [&]() {
+        if (cudaSetDevice(dev) != cudaSuccess) return;
+        for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+            bgr_planner* pl = pls[i];
+            for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes; ++b) {
+                int rc = step_launch(pl);
+                if (rc == BGR_OK) rc = step_finish(pl, nullptr, nullptr);
+                if (rc != BGR_OK) {
+                    rcs[(size_t)i] = rc;
+                    errs[(size_t)i] = get_error();
+                    break;
+                }
+            }
+        }
+    };
+    if (nthreads == 1) {
+        worker();
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(worker);
+        for (auto& t : th) t.join();
     }
+    for (int i = 0; i < n; ++i)
+        if (rcs[(size_t)i] != BGR_OK) {
+            set_error("planner %d: %s", i, errs[(size_t)i].c_str());
+            return rcs[(size_t)i];
+        }
     if (goal_reached)
         for (int i = 0; i < n; ++i) goal_reached[i] = pls[i]->goal_reached;
     return BGR_OK;

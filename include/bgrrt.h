@@ -292,8 +292,8 @@ int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached);
 /* steps until the goal is reached, the tree has >= max_nodes nodes or max_batches were run */
 int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached);
 /* independent planning queries (one planner per start/goal pair; the reference runs one process
- * per query): every round launches one step of each unfinished planner on its own stream before
- * waiting for any of them, so the steps overlap on the device.  Each planner's tree is exactly
+ * per query): the queries run concurrently (one host thread and one stream per query in flight,
+ * up to 16), so their small per-step kernels overlap on the device.  Each planner's tree is exactly
  * the one bgr_planner_run would grow.  The planners must not share a stream or a map handle.
  * goal_reached: n flags (may be NULL). */
 int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t max_batches, int* goal_reached);
