@@ -1104,7 +1104,7 @@ struct bgr_map {
     int last_gate_d = 0;
     bool gate_on = true;
     int pipe_chunks = 0;               // > 1: the sweep of chunk c waits for pipe.ev_in[c] (host-pointer call)
-    int64_t pipe_per = 0;
+    int64_t pipe_begin[CopyPipe::kMaxChunks + 1] = {0};   // chunk c = edges [pipe_begin[c], pipe_begin[c+1])
     CopyPipe pipe;                     // side streams of the host-pointer collide_edges
     uint64_t last_stats[4] = {0, 0, 0, 0};
     cudaEvent_t tev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // kernel boundaries of the last collide_edges (timing on)
@@ -1430,11 +1430,10 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         // one sweep launch per chunk of a chunked host call (each waits for its H2D copy), one
         // narrow / finalize pass over the whole batch
         const int nch = h->pipe_chunks > 1 ? h->pipe_chunks : 1;
-        const int64_t per = nch > 1 ? h->pipe_per : n;
         for (int c = 0; c < nch; ++c) {
-            a.e_begin = (int64_t)c * per;
-            a.n = std::min<int64_t>(n, a.e_begin + per);
-            if (a.n <= a.e_begin) break;
+            a.e_begin = nch > 1 ? h->pipe_begin[c] : 0;
+            a.n = nch > 1 ? h->pipe_begin[c + 1] : n;
+            if (a.n <= a.e_begin) continue;
             if (nch > 1) BGR_CUDA(cudaStreamWaitEvent(h->stream, h->pipe.ev_in[c], 0));
             edges_sweep_kernel<<<(unsigned)div_up(a.n - a.e_begin, kSweepEdges), kSweepThreads, 0, h->stream>>>(a);
             BGR_LAUNCH_CHECK();
@@ -1489,16 +1488,20 @@ int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t 
     // the staging buffers may still be read by earlier work on the map's stream
     BGR_CUDA(cudaEventRecord(P.ev_start, h->stream));
     BGR_CUDA(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
-    const int64_t per = round_up(div_up(n, chunks), 256);
+    // equal chunks (measured: tapering them towards the end, or more than 4, is slower — the first
+    // sweep then starts later / the launches get too small)
+    h->pipe_begin[0] = 0;
+    for (int c = 0; c < chunks; ++c)
+        h->pipe_begin[c + 1] = c + 1 == chunks ? n : std::min<int64_t>(n, round_up(n * (int64_t)(c + 1) / chunks, 256));
     for (int c = 0; c < chunks; ++c) {
-        const int64_t s0 = (int64_t)c * per, m = std::min<int64_t>(per, n - s0);
-        if (m <= 0) break;
-        BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p + 3 * s0, p1 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
-        BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p + 3 * s0, p2 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+        const int64_t s0 = h->pipe_begin[c], m = h->pipe_begin[c + 1] - s0;
+        if (m > 0) {
+            BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p + 3 * s0, p1 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+            BGR_CUDA(cudaMemcpyAsync(h->p2_dev.p + 3 * s0, p2 + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+        }
         BGR_CUDA(cudaEventRecord(P.ev_in[c], P.s_in));
     }
     h->pipe_chunks = chunks;
-    h->pipe_per = per;
     const int rc = bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
                                              band ? h->band_dev.p : nullptr);
     h->pipe_chunks = 0;
