@@ -1023,39 +1023,74 @@ __global__ void __launch_bounds__(128) edges_narrow_kernel(Edge2Args a) {
     const MapView& m = a.m;
     const unsigned count = min(a.qctl[0], a.queue_cap);
     unsigned long long n_mpr = 0, n_cap = 0;
-    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const NarrowRec rec = a.queue[i];
-        const unsigned cur = __ldcg(a.gflags + rec.edge);
-        if (cur & (F_DEEP | F_OVERFLOW)) continue;
-        if ((cur & F_HIT) && (!a.want_band || (cur & F_DEFL))) continue;   // already decided
-        const int L = (int)(rec.a >> 12), lx = (int)(rec.a & 4095), ly = (int)(rec.b >> 12), lz = (int)(rec.b & 4095);
-        D3 bc;
-        double e;
-        leaf_box(m, L, lx, ly, lz, bc, e);
-        const int64_t eg = rec.edge;
-        const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
-        const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
-        ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
-        int capped = 0;
-        unsigned f = 0;
-        const bool h = mpr_shape_box(o, bc, e, kBandTol, &capped) != 0;
-        ++n_mpr;
-        if (h) f |= F_HIT;
-        if (a.want_band) {
-            ShapeObj o2 = o;
-            if (h) {
-                o2.radius = fmax(0.0, o2.radius - kBandFlag);
-                if (o.type == kShapeCyl) o2.height = fmax(0.0, o2.height - kBandFlag);
-                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_DEFL;
-            } else {
-                o2.radius += kBandFlag;
-                if (o.type == kShapeCyl) o2.height += kBandFlag;
-                if (mpr_shape_box(o2, bc, e, kBandTol, &capped)) f |= F_INFL;
+    if (a.want_band) {
+        // With the band test a pair needs the exact test of the shape AND of the shape deflated
+        // (after a hit) or inflated (after a miss) by kBandFlag.  The narrow phase is a latency
+        // chain (one MPR run after the other per thread, few pairs), so a pair takes 4 lanes: lane 0
+        // runs the shape, lane 1 the deflated, lane 2 the inflated one, all at once.
+        const int lane = threadIdx.x & 31, sub = lane & 3, grp = lane & ~3;
+        const unsigned stride = gridDim.x * blockDim.x / 4;
+        for (unsigned base = (blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) / 4; base < count; base += stride) {
+            const unsigned i = base + (unsigned)(lane >> 2);
+            bool active = i < count;
+            NarrowRec rec = {0, 0, 0, 0};
+            if (active) rec = a.queue[i];
+            unsigned cur = 0;
+            if (active && sub == 0) cur = __ldcg(a.gflags + rec.edge);
+            cur = __shfl_sync(kFull, cur, grp);            // one read per pair: the 4 lanes must agree
+            if (cur & (F_DEEP | F_OVERFLOW)) active = false;
+            if ((cur & F_HIT) && (cur & F_DEFL)) active = false;      // already decided
+            int hitv = 0, capped = 0;
+            if (active && sub < 3) {
+                const int L = (int)(rec.a >> 12), lx = (int)(rec.a & 4095), ly = (int)(rec.b >> 12), lz = (int)(rec.b & 4095);
+                D3 bc;
+                double e;
+                leaf_box(m, L, lx, ly, lz, bc, e);
+                const int64_t eg = rec.edge;
+                const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
+                const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
+                ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+                if (sub == 1) {
+                    o.radius = fmax(0.0, o.radius - kBandFlag);
+                    if (o.type == kShapeCyl) o.height = fmax(0.0, o.height - kBandFlag);
+                } else if (sub == 2) {
+                    o.radius += kBandFlag;
+                    if (o.type == kShapeCyl) o.height += kBandFlag;
+                }
+                hitv = mpr_shape_box(o, bc, e, kBandTol, &capped) != 0;
             }
-            ++n_mpr;
+            const int h0 = __shfl_sync(kFull, hitv, grp), h1 = __shfl_sync(kFull, hitv, grp + 1), h2 = __shfl_sync(kFull, hitv, grp + 2);
+            const int c0 = __shfl_sync(kFull, capped, grp), c1 = __shfl_sync(kFull, capped, grp + 1), c2 = __shfl_sync(kFull, capped, grp + 2);
+            if (active && sub == 0) {
+                unsigned f = 0;
+                if (h0) f |= F_HIT;
+                if (h0 && h1) f |= F_DEFL;
+                if (!h0 && h2) f |= F_INFL;
+                n_mpr += 2;                                 // the two runs the result depends on
+                if (c0 || (h0 ? c1 : c2)) { f |= F_CAP; ++n_cap; }
+                if (f) atomicOr(a.gflags + rec.edge, f);
+            }
         }
-        if (capped) { f |= F_CAP; ++n_cap; }
-        if (f) atomicOr(a.gflags + rec.edge, f);
+    } else {
+        for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+            const NarrowRec rec = a.queue[i];
+            const unsigned cur = __ldcg(a.gflags + rec.edge);
+            if (cur & (F_DEEP | F_OVERFLOW | F_HIT)) continue;   // decided
+            const int L = (int)(rec.a >> 12), lx = (int)(rec.a & 4095), ly = (int)(rec.b >> 12), lz = (int)(rec.b & 4095);
+            D3 bc;
+            double e;
+            leaf_box(m, L, lx, ly, lz, bc, e);
+            const int64_t eg = rec.edge;
+            const float p1[3] = {a.p1[3 * eg], a.p1[3 * eg + 1], a.p1[3 * eg + 2]};
+            const float p2[3] = {a.p2[3 * eg], a.p2[3 * eg + 1], a.p2[3 * eg + 2]};
+            ShapeObj o = make_edge_obj(p1, p2, a.radius, a.shape);
+            int capped = 0;
+            unsigned f = 0;
+            if (mpr_shape_box(o, bc, e, kBandTol, &capped)) f |= F_HIT;
+            ++n_mpr;
+            if (capped) { f |= F_CAP; ++n_cap; }
+            if (f) atomicOr(a.gflags + rec.edge, f);
+        }
     }
     if (a.stats) {
         for (int o = 16; o > 0; o >>= 1) {
@@ -1441,7 +1476,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.e_begin = 0;
         a.n = n;
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
-        const int nblk = (int)std::min<int64_t>(4LL * num_sms(), std::max<int64_t>(1, div_up(cap, 128)));
+        const int nblk = (int)std::min<int64_t>((ma.want_band ? 16LL : 4LL) * num_sms(), std::max<int64_t>(1, div_up(cap, 32)));
         edges_narrow_kernel<<<nblk, 128, 0, h->stream>>>(a);
         BGR_LAUNCH_CHECK();
         ma.only_overflow = 1;   // no-op unless the queue overflowed
