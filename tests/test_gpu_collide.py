@@ -298,6 +298,41 @@ def test_edges_chunked_host_call_equals_device_call(bgr, oracle):
     assert np.array_equal(h0, h2) and np.array_equal(b0, b2)
 
 
+def test_edges_full_size_properties(bgr, oracle):
+    """BASELINE config 3 at full size (1,000,000 cylinder edges vs the 512^3 map, ~6.5 M leaf
+    boxes): gate on == gate off, chunked host call == device call, reversal symmetry outside the
+    band, and the oracle on a 200-edge subsample."""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(512, 4, n_walls=8, wall_thick=4, door_cells=5)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (512, 512, 512))
+    m.set_boxes(boxes)
+    assert m.occupied_cells() == int(occ.sum())
+    p1, p2 = synth.edges(4, 1_000_000, occ)
+    d1, d2 = torch.from_numpy(p1).cuda(), torch.from_numpy(p2).cuda()
+    h, b = m.collide_edges(d1, d2)
+    torch.cuda.synchronize()
+    h, b = h.cpu().numpy(), b.cpu().numpy()
+    st, g = m.last_stats(), m.gate_stats()
+    assert st["iter_cap"] == 0 and 0 < g["rect_items"] < st["work_items"] // 4
+    assert 0.3 < h.mean() < 0.7 and b.sum() < 1000
+    m.set_gate(False)
+    h0, b0 = m.collide_edges(d1, d2)
+    torch.cuda.synchronize()
+    assert np.array_equal(h, h0.cpu().numpy()) and np.array_equal(b, b0.cpu().numpy())
+    m.set_gate(True)
+    hh, bh = m.collide_edges(p1, p2)                       # host pointers: 4 chunks
+    assert np.array_equal(h, hh) and np.array_equal(b, bh)
+    hr, br = m.collide_edges(d2, d1)
+    torch.cuda.synchronize()
+    hr, br = hr.cpu().numpy(), br.cpu().numpy()
+    assert not ((hr != h) & (b == 0) & (br == 0)).any()
+    sub = np.arange(0, 1_000_000, 5000)
+    oh, _ = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
+    assert not ((oh != h[sub]) & (b[sub] == 0)).any()
+
+
 def test_octomap_ingestion_and_refresh(bgr, oracle):
     """serialised Octomap (full message data, MS:279) -> toBoxes rows -> bitmap; then a map refresh
     that rasterises only the changed leaves (bgr_map_refresh_boxes)."""
