@@ -390,12 +390,107 @@ int orc_collide_spheres(const double* boxes, int64_t nb, const float* centers, i
     return 0;
 }
 
+// mode 2 = "library-best" CPU baseline: what a maintainer gets from an FCL
+// broadphase instead of the reference's loop over every leaf — the boxes are bucketed once into a
+// coarse uniform grid (8 finest cells per bucket side, CSR lists, cached per box array); an edge
+// visits the buckets its axis-aligned bounding box overlaps, culls by bounding sphere and runs the
+// same MPR on what is left.  Conservative (a colliding box overlaps the AABB), so the booleans equal
+// modes 0 / 1 (tests/test_oracle.py).
+namespace {
+struct EdgeBuckets {
+    const double* boxes = nullptr;
+    int64_t nb = -1;
+    double cell = 0, org[3] = {0, 0, 0};
+    int g[3] = {0, 0, 0};
+    double max_half = 0;                 // largest box half size (buckets hold box CENTRES)
+    std::vector<int64_t> start;
+    std::vector<int32_t> items;
+};
+EdgeBuckets g_buckets;
+
+void build_buckets(const double* boxes, int64_t nb) {
+    EdgeBuckets& B = g_buckets;
+    if (B.boxes == boxes && B.nb == nb) return;
+    B.boxes = boxes; B.nb = nb;
+    double mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY}, smin = INFINITY;
+    B.max_half = 0;
+    for (int64_t b = 0; b < nb; ++b) {
+        for (int a = 0; a < 3; ++a) { mn[a] = std::min(mn[a], boxes[6 * b + a]); mx[a] = std::max(mx[a], boxes[6 * b + a]); }
+        smin = std::min(smin, boxes[6 * b + 3]);
+        B.max_half = std::max(B.max_half, 0.5 * boxes[6 * b + 3]);
+    }
+    if (nb == 0) { B.g[0] = B.g[1] = B.g[2] = 0; B.start.assign(1, 0); B.items.clear(); return; }
+    B.cell = 8.0 * smin;
+    int64_t cells = 1;
+    for (int a = 0; a < 3; ++a) {
+        B.org[a] = mn[a];
+        B.g[a] = (int)std::floor((mx[a] - mn[a]) / B.cell) + 1;
+        cells *= B.g[a];
+    }
+    auto cell_of = [&](const double* c) {
+        int64_t id = 0;
+        for (int a = 2; a >= 0; --a) {
+            int v = (int)std::floor((c[a] - B.org[a]) / B.cell);
+            v = std::min(std::max(v, 0), B.g[a] - 1);
+            id = id * B.g[a] + v;
+        }
+        return id;
+    };
+    B.start.assign((size_t)cells + 1, 0);
+    for (int64_t b = 0; b < nb; ++b) B.start[(size_t)cell_of(boxes + 6 * b) + 1]++;
+    for (int64_t c = 0; c < cells; ++c) B.start[(size_t)c + 1] += B.start[(size_t)c];
+    B.items.resize((size_t)nb);
+    std::vector<int64_t> cur(B.start.begin(), B.start.end() - 1);
+    for (int64_t b = 0; b < nb; ++b) B.items[(size_t)cur[(size_t)cell_of(boxes + 6 * b)]++] = (int32_t)b;
+}
+}  // namespace
+
 int orc_collide_edges(const double* boxes, int64_t nb, const float* p1, const float* p2,
                       int64_t m, double radius, int shape, int mode, double band_tol,
                       uint8_t* hit, uint8_t* band, int threads) {
 #ifdef _OPENMP
     if (threads > 0) omp_set_num_threads(threads);
 #endif
+    if (mode == 2) {
+        build_buckets(boxes, nb);
+        const EdgeBuckets& B = g_buckets;
+#pragma omp parallel for schedule(dynamic, 16)
+        for (int64_t i = 0; i < m; ++i) {
+            const Obj e = make_edge(p1 + 3 * i, p2 + 3 * i, radius, shape);
+            const Frame f = frame_of(e);
+            const double reach = std::sqrt(e.height * e.height + radius * radius) + radius;
+            bool flag = false;
+            int lo[3], hi[3];
+            bool empty = nb == 0;
+            for (int a = 0; a < 3 && !empty; ++a) {
+                // AABB of the (capsule hull of the) shape, grown by the largest box half size
+                const double ext = f.h * std::fabs(f.u[a]) + radius + B.max_half + 1e-3;
+                lo[a] = std::max(0, (int)std::floor((f.c[a] - ext - B.org[a]) / B.cell));
+                hi[a] = std::min(B.g[a] - 1, (int)std::floor((f.c[a] + ext - B.org[a]) / B.cell));
+                empty = lo[a] > hi[a];
+            }
+            for (int z = empty ? 1 : lo[2]; !empty && z <= hi[2] && !flag; ++z)
+                for (int y = lo[1]; y <= hi[1] && !flag; ++y) {
+                    const int64_t row = ((int64_t)z * B.g[1] + y) * B.g[0];
+                    for (int64_t k = B.start[(size_t)(row + lo[0])]; k < B.start[(size_t)(row + hi[0] + 1)]; ++k) {
+                        const double* bx = boxes + 6 * (int64_t)B.items[(size_t)k];
+                        const double R = reach + bx[3] * 0.8660254037844387 + 1e-3;
+                        const double dx = bx[0] - e.pos.v[0], dy = bx[1] - e.pos.v[1], dz = bx[2] - e.pos.v[2];
+                        if (dx * dx + dy * dy + dz * dz > R * R) continue;
+                        // tighter cull: distance of the box centre to the axis segment
+                        const double al = dx * f.u[0] + dy * f.u[1] + dz * f.u[2];
+                        const double t = std::max(-f.h, std::min(f.h, al));
+                        const double ex = dx - t * f.u[0], ey = dy - t * f.u[1], ez = dz - t * f.u[2];
+                        const double R2 = radius + bx[3] * 0.8660254037844387 + 1e-3;
+                        if (ex * ex + ey * ey + ez * ez > R2 * R2) continue;
+                        if (mpr(e, make_box(bx, bx[3]), 1e-6, nullptr)) { flag = true; break; }
+                    }
+                }
+            hit[i] = flag ? 1 : 0;
+            if (band) band[i] = 0;
+        }
+        return 0;
+    }
 #pragma omp parallel for schedule(dynamic, 4)
     for (int64_t i = 0; i < m; ++i) {
         const Obj e = make_edge(p1 + 3 * i, p2 + 3 * i, radius, shape);
