@@ -301,7 +301,7 @@ def test_edges_chunked_host_call_equals_device_call(bgr, oracle):
 def test_edges_full_size_properties(bgr, oracle):
     """BASELINE config 3 at full size (1,000,000 cylinder edges vs the 512^3 map, ~6.5 M leaf
     boxes): gate on == gate off, chunked host call == device call, reversal symmetry outside the
-    band, and the oracle on a 200-edge subsample."""
+    band, and the oracle's booleans for all 1,000,000 edges."""
     import torch
     from bottleneck_guided_rrt_b200 import synth
     occ = synth.make_map(512, 4, n_walls=8, wall_thick=4, door_cells=5)
@@ -328,9 +328,15 @@ def test_edges_full_size_properties(bgr, oracle):
     torch.cuda.synchronize()
     hr, br = hr.cpu().numpy(), br.cpu().numpy()
     assert not ((hr != h) & (b == 0) & (br == 0)).any()
-    sub = np.arange(0, 1_000_000, 5000)
-    oh, _ = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
-    assert not ((oh != h[sub]) & (b[sub] == 0)).any()
+    # the oracle on EVERY edge (its bucketed broadphase in front of the same MPR: mode 2, equal to the
+    # reference-literal loop by tests/test_oracle.py) and the literal loop itself on a subsample
+    oh, _ = oracle.collide_edges(boxes, p1, p2, 0.03, 0, mode=2, want_band=False)
+    bad = (oh != h) & (b == 0)
+    assert not bad.any(), np.nonzero(bad)[0][:10]
+    assert (oh != h).sum() <= b.sum()
+    sub = np.arange(0, 1_000_000, 10000)
+    ol, _ = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
+    assert np.array_equal(ol, oh[sub])
 
 
 def test_octomap_ingestion_and_refresh(bgr, oracle):
