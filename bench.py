@@ -323,6 +323,23 @@ def run_ours(args):
                              "work_items_per_s": stats["work_items"] / (sweep_ms * 1e-3)},
             }
 
+            # sphere state checks (isStateValid MS:310-351) on the same map: the edges' first endpoints
+            d_shit = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+            d_sband = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+
+            def sphere_step():
+                omap.collide_spheres(d_p1, 0.1, hit=d_shit, band=d_sband)
+
+            sphere_ms = max_over_ranks(timed_steps(torch, stream, sphere_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
+            sbytes = 14.0 * N_EDGES + map_bytes
+            out["state_checks"] = {
+                "value": world * N_EDGES / (sphere_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_ms,
+                "config": {"workload": "1,000,000 spheres/GPU (r=0.1) vs the configs[2] map", "hit_fraction": float(d_shit.float().mean().item()),
+                           "in_band": int(d_sband.sum().item())},
+                "roofline": {"bound": "hbm", "kernel": "collide_spheres_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
+                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": sbytes / (sphere_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                             "algorithmic_bytes": sbytes, "peak_src": pk["src"], "traffic": None}}
+
         # ---------------------------------------------------------------- batched planner (configs[0], configs[3])
         if not args.skip_planner:
             out["planner"] = planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier)

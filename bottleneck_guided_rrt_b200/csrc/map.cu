@@ -124,29 +124,25 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
             const int bx = bl[0] + t % nbr[0], by = bl[1] + (t / nbr[0]) % nbr[1], bz = bl[2] + t / (nbr[0] * nbr[1]);
             unsigned long long W = __ldg(m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0] + bx);
             if (W == 0ull) continue;
-            // cells of this brick inside the box, per axis
-            const int bb[3] = {bx, by, bz};
-            unsigned long long mask = ~0ull;
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                const int v0 = max(lo[a] - 4 * bb[a], 0), v1 = min(hi[a] - 4 * bb[a], 3);
-                unsigned long long ma = 0ull;
-                for (int v = v0; v <= v1; ++v)
-                    ma |= a == 0 ? (0x1111111111111111ull << v) : (a == 1 ? (0x000F000F000F000Full << (4 * v)) : (0xFFFFull << (16 * v)));
-                mask &= ma;
-            }
-            W &= mask;
+            // cells of this brick inside the box, per axis (x: nibble pattern, y: 4-bit groups, z: 16-bit groups)
+            const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
+            const int y0 = max(lo[1] - 4 * by, 0), y1 = min(hi[1] - 4 * by, 3);
+            const int z0 = max(lo[2] - 4 * bz, 0), z1 = min(hi[2] - 4 * bz, 3);
+            const unsigned long long mx = (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull;
+            const unsigned long long my = (unsigned long long)(((1u << (4 * y1 + 4)) - (1u << (4 * y0))) & 0xFFFFu) * 0x0001000100010001ull;
+            const unsigned long long mz = (z1 == 3 ? ~0ull : ((1ull << (16 * z1 + 16)) - 1ull)) & ~((1ull << (16 * z0)) - 1ull);
+            W &= mx & my & mz;
+            // The leaves are unions of their finest cells (level 0 holds every cell of a pruned leaf), so
+            // the distance to the nearest leaf is the distance to the nearest occupied CELL: no leaf lookup.
+            const double half = 0.5 * m.res;
             while (W) {
                 const int bit = __ffsll((long long)W) - 1;
                 W &= W - 1ull;
                 const int x = 4 * bx + (bit & 3), y = 4 * by + ((bit >> 2) & 3), z = 4 * bz + (bit >> 4);
-                int lx, ly, lz;
-                const int L = find_leaf(m, x, y, z, lx, ly, lz);
-                D3 bc;
-                double e;
-                leaf_box(m, L, lx, ly, lz, bc, e);
-                const double tx = fmax(0.0, fabs(c[0] - bc.x) - e), ty = fmax(0.0, fabs(c[1] - bc.y) - e),
-                             tz = fmax(0.0, fabs(c[2] - bc.z) - e);
+                const double ccx = m.origin[0] + ((double)x + 0.5) * m.res, ccy = m.origin[1] + ((double)y + 0.5) * m.res,
+                             ccz = m.origin[2] + ((double)z + 0.5) * m.res;
+                const double tx = fmax(0.0, fabs(c[0] - ccx) - half), ty = fmax(0.0, fabs(c[1] - ccy) - half),
+                             tz = fmax(0.0, fabs(c[2] - ccz) - half);
                 double d2 = tx * tx;
                 d2 += ty * ty;
                 d2 += tz * tz;

@@ -339,6 +339,34 @@ def test_edges_full_size_properties(bgr, oracle):
     assert np.array_equal(ol, oh[sub])
 
 
+def test_spheres_full_size_properties(bgr, oracle):
+    """1,000,000 state checks (r = 0.1) against the 512^3 map: gate on == gate off, chunk /
+    permutation independence, and the oracle's MPR loop on a subsample."""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(512, 4, n_walls=8, wall_thick=4, door_cells=5)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (512, 512, 512))
+    m.set_boxes(boxes)
+    pts = synth.points(21, 1_000_000, 25.6)
+    dp = torch.from_numpy(pts).cuda()
+    h, b = m.collide_spheres(dp, 0.1)
+    torch.cuda.synchronize()
+    h, b = h.cpu().numpy(), b.cpu().numpy()
+    assert 0.3 < h.mean() < 0.99
+    m.set_gate(False)
+    h0, b0 = m.collide_spheres(dp, 0.1)
+    torch.cuda.synchronize()
+    assert np.array_equal(h, h0.cpu().numpy()) and np.array_equal(b, b0.cpu().numpy())
+    m.set_gate(True)
+    perm = np.random.default_rng(3).permutation(len(pts))[:200000]
+    hp, bp = m.collide_spheres(pts[perm], 0.1)
+    assert np.array_equal(hp, h[perm]) and np.array_equal(bp, b[perm])
+    sub = np.arange(0, 1_000_000, 8000)
+    oh, _ = oracle.collide_spheres(boxes, pts[sub], 0.1, mode=1, want_band=False)
+    assert not ((oh != h[sub]) & (b[sub] == 0)).any()
+
+
 def test_octomap_ingestion_and_refresh(bgr, oracle):
     """serialised Octomap (full message data, MS:279) -> toBoxes rows -> bitmap; then a map refresh
     that rasterises only the changed leaves (bgr_map_refresh_boxes)."""
