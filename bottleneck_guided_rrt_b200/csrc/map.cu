@@ -81,6 +81,12 @@ __global__ void popcount_kernel(const uint64_t* __restrict__ bits, int64_t n, un
 
 // ------------------------------------------------------------------ spheres (isStateValid)
 // Exact closed form: gap = dist(centre, leaf box) - r in double; hit = gap < 0.
+__device__ __forceinline__ int nth_set_bit64(unsigned long long v, int r) {   // r-th (0-based) set bit
+    const unsigned lo32 = (unsigned)v, hi32 = (unsigned)(v >> 32);
+    const int clo = __popc(lo32);
+    return r < clo ? (int)__fns(lo32, 0, r + 1) : 32 + (int)__fns(hi32, 0, r - clo + 1);
+}
+
 // One warp per sphere: the cells of the sphere's box (radius + margin, +1 cell) are read as whole
 // 4x4x4 brick words, one brick per lane (a 0.1 m sphere at 0.05 m cells touches <= 3x3x3 bricks:
 // 27 loads instead of 343 bit probes), masked to the box; each lane walks the set bits of its
@@ -115,43 +121,70 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         hi[a] = min(m.dims[a] - 1, (int)floor((c[a] + r - m.origin[a]) * m.inv_res) + 1);
         empty |= lo[a] > hi[a];
     }
-    double gmin = 1e300;
+    double d2min = 1e300;
     if (!empty) {
         const int bl[3] = {lo[0] >> 2, lo[1] >> 2, lo[2] >> 2};
         const int nbr[3] = {(hi[0] >> 2) - bl[0] + 1, (hi[1] >> 2) - bl[1] + 1, (hi[2] >> 2) - bl[2] + 1};
         const int total = nbr[0] * nbr[1] * nbr[2];
-        for (int t = lane; t < total; t += 32) {
-            const int bx = bl[0] + t % nbr[0], by = bl[1] + (t / nbr[0]) % nbr[1], bz = bl[2] + t / (nbr[0] * nbr[1]);
-            unsigned long long W = __ldg(m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0] + bx);
-            if (W == 0ull) continue;
-            // cells of this brick inside the box, per axis (x: nibble pattern, y: 4-bit groups, z: 16-bit groups)
-            const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
-            const int y0 = max(lo[1] - 4 * by, 0), y1 = min(hi[1] - 4 * by, 3);
-            const int z0 = max(lo[2] - 4 * bz, 0), z1 = min(hi[2] - 4 * bz, 3);
-            const unsigned long long mx = (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull;
-            const unsigned long long my = (unsigned long long)(((1u << (4 * y1 + 4)) - (1u << (4 * y0))) & 0xFFFFu) * 0x0001000100010001ull;
-            const unsigned long long mz = (z1 == 3 ? ~0ull : ((1ull << (16 * z1 + 16)) - 1ull)) & ~((1ull << (16 * z0)) - 1ull);
-            W &= mx & my & mz;
-            // The leaves are unions of their finest cells (level 0 holds every cell of a pruned leaf), so
-            // the distance to the nearest leaf is the distance to the nearest occupied CELL: no leaf lookup.
-            const double half = 0.5 * m.res;
-            while (W) {
-                const int bit = __ffsll((long long)W) - 1;
-                W &= W - 1ull;
-                const int x = 4 * bx + (bit & 3), y = 4 * by + ((bit >> 2) & 3), z = 4 * bz + (bit >> 4);
-                const double ccx = m.origin[0] + ((double)x + 0.5) * m.res, ccy = m.origin[1] + ((double)y + 0.5) * m.res,
-                             ccz = m.origin[2] + ((double)z + 0.5) * m.res;
-                const double tx = fmax(0.0, fabs(c[0] - ccx) - half), ty = fmax(0.0, fabs(c[1] - ccy) - half),
-                             tz = fmax(0.0, fabs(c[2] - ccz) - half);
-                double d2 = tx * tx;
-                d2 += ty * ty;
-                d2 += tz * tz;
-                gmin = fmin(gmin, sqrt(d2) - radius);
+        const double half = 0.5 * m.res;
+        for (int t0 = 0; t0 < total; t0 += 32) {
+            // ---- one brick per lane: its word masked to the box
+            const int t = t0 + lane;
+            unsigned long long W = 0ull;
+            int bxyz = 0;
+            if (t < total) {
+                const int bx = bl[0] + t % nbr[0], by = bl[1] + (t / nbr[0]) % nbr[1], bz = bl[2] + t / (nbr[0] * nbr[1]);
+                W = __ldg(m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0] + bx);
+                // cells of this brick inside the box, per axis (x: nibble pattern, y: 4-bit groups, z: 16-bit groups)
+                const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
+                const int y0 = max(lo[1] - 4 * by, 0), y1 = min(hi[1] - 4 * by, 3);
+                const int z0 = max(lo[2] - 4 * bz, 0), z1 = min(hi[2] - 4 * bz, 3);
+                const unsigned long long mx = (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull;
+                const unsigned long long my = (unsigned long long)(((1u << (4 * y1 + 4)) - (1u << (4 * y0))) & 0xFFFFu) * 0x0001000100010001ull;
+                const unsigned long long mz = (z1 == 3 ? ~0ull : ((1ull << (16 * z1 + 16)) - 1ull)) & ~((1ull << (16 * z0)) - 1ull);
+                W &= mx & my & mz;
+                bxyz = bx | (by << 10) | (bz << 20);
+            }
+            // ---- the set bits of the 32 words, one per lane (dense: the words are mostly empty or sparse)
+            const int cnt = __popcll(W);
+            int incl = cnt;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(kFull, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int T = __shfl_sync(kFull, incl, 31);
+            for (int j0 = 0; j0 < T; j0 += 32) {
+                const int j = j0 + lane;
+                int src = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int v = __shfl_sync(kFull, incl, src + step - 1);
+                    if (v <= j) src += step;
+                }
+                src = min(src, 31);
+                const int s_incl = __shfl_sync(kFull, incl, src), s_cnt = __shfl_sync(kFull, cnt, src);
+                const unsigned long long s_W = __shfl_sync(kFull, W, src);
+                const int s_b = __shfl_sync(kFull, bxyz, src);
+                if (j < T) {
+                    // The leaves are unions of their finest cells (level 0 holds every cell of a pruned leaf), so
+                    // the distance to the nearest leaf is the distance to the nearest occupied CELL: no leaf lookup.
+                    const int bit = nth_set_bit64(s_W, j - (s_incl - s_cnt));
+                    const int x = 4 * (s_b & 1023) + (bit & 3), y = 4 * ((s_b >> 10) & 1023) + ((bit >> 2) & 3), z = 4 * (s_b >> 20) + (bit >> 4);
+                    const double ccx = m.origin[0] + ((double)x + 0.5) * m.res, ccy = m.origin[1] + ((double)y + 0.5) * m.res,
+                                 ccz = m.origin[2] + ((double)z + 0.5) * m.res;
+                    const double tx = fmax(0.0, fabs(c[0] - ccx) - half), ty = fmax(0.0, fabs(c[1] - ccy) - half),
+                                 tz = fmax(0.0, fabs(c[2] - ccz) - half);
+                    double d2 = tx * tx;
+                    d2 += ty * ty;
+                    d2 += tz * tz;
+                    d2min = fmin(d2min, d2);
+                }
             }
         }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) gmin = fmin(gmin, __shfl_xor_sync(kFull, gmin, o));
+    for (int o = 16; o > 0; o >>= 1) d2min = fmin(d2min, __shfl_xor_sync(kFull, d2min, o));
+    const double gmin = d2min < 1e299 ? sqrt(d2min) - radius : 1e300;   // sqrt is monotone: min of the distances
     if (lane == 0) {
         hit[i] = gmin < 0.0 ? 1 : 0;
         if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
@@ -666,12 +699,6 @@ __device__ __forceinline__ void cta_prefix(int val, int* prefix, int* warp_sums)
     prefix[tid + 1] = off + inc;
     if (tid == 0) prefix[0] = 0;
     __syncthreads();
-}
-
-__device__ __forceinline__ int nth_set_bit64(unsigned long long v, int r) {   // r-th (0-based) set bit
-    const unsigned lo32 = (unsigned)v, hi32 = (unsigned)(v >> 32);
-    const int clo = __popc(lo32);
-    return r < clo ? (int)__fns(lo32, 0, r + 1) : 32 + (int)__fns(hi32, 0, r - clo + 1);
 }
 
 constexpr int kGateSlabs = 128;   // slabs per edge the gate tracks (longer edges run every slab)
