@@ -34,6 +34,7 @@ from .capi import (  # noqa: F401
     PLAN_REWIRE,
     PLAN_QUIRKS,
     PLAN_NO_GOAL,
+    PLAN_DEDUP,
     PLAN_MODE_RS,
     PLAN_MODE_MS,
 )

@@ -113,7 +113,7 @@ def lib():
     return L
 
 
-PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL = 1, 2, 4, 8
+PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP = 1, 2, 4, 8, 16
 PLAN_MODE_RS, PLAN_MODE_MS = 0, 1
 
 

@@ -162,6 +162,7 @@ __global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 |
     d.prand[3 * c + 1] = src[1];
     d.prand[3 * c + 2] = src[2];
     d.qslot[c] = slot;
+    if (!from_table) atomicMax((unsigned long long*)&d.counters[11 + slot], (unsigned long long)(d.B - c));   // first candidate of the slot
     if (from_table) {
         d.uq[3 * slot] = src[0];
         d.uq[3 * slot + 1] = src[1];
@@ -173,6 +174,14 @@ __global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 |
             d.uq[3 * f] = fs[0]; d.uq[3 * f + 1] = fs[1]; d.uq[3 * f + 2] = fs[2];
         }
     }
+}
+
+// BGR_PLAN_DEDUP: copies of a goal / milestone candidate are rejected like a failed state check
+__global__ void plan_dedup_kernel(PlanDev d) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d.B) return;
+    const int slot = d.qslot[c];
+    if (slot < d.n_fixed && (long long)(d.B - c) != d.counters[11 + slot]) d.hit[c] = 1;
 }
 
 __global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
@@ -463,7 +472,7 @@ int bgr_planner_create(const bgr_planner_params* p, bgr_map* map, const float* t
     BGR_ARG(p->batch >= 1 && p->batch <= 65536, "batch must be in 1..65536");
     BGR_ARG(p->mode == BGR_PLAN_MODE_RS || p->mode == BGR_PLAN_MODE_MS, "unknown sampler mode %d", p->mode);
     BGR_ARG(p->mode != BGR_PLAN_MODE_MS || (milestones != nullptr && nm >= 3), "mode MS needs >= 3 milestone points");
-    BGR_ARG((p->flags & ~15u) == 0, "unknown planner flags %u", p->flags);
+    BGR_ARG((p->flags & ~31u) == 0, "unknown planner flags %u", p->flags);
     BGR_ARG(p->eta > 0.f && p->state_radius >= 0 && p->edge_radius >= 0, "bad eta / radii");
     bgr_planner* pl = new bgr_planner;
     pl->p = *p;
@@ -590,6 +599,10 @@ static int step_launch(bgr_planner* pl) {
     plan_steer_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
     BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
+    if (P.flags & BGR_PLAN_DEDUP) {
+        plan_dedup_kernel<<<gb, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+    }
     if (have_knn)
         // candidates the state check rejected never read their neighbour rows: skip their search
         BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->hit.p, pl->knn_idx.p, pl->knn_d2.p));

@@ -260,6 +260,9 @@ int bgr_map_find_labels(bgr_map* map, const double* path_3xP, int64_t p, double 
 #define BGR_PLAN_REWIRE 2u      /* beyond reference: real rewiring (MS:883/923 only print) */
 #define BGR_PLAN_QUIRKS 4u      /* MS:1236-1238: rows of the `found` branch keep the Nearest index as parent */
 #define BGR_PLAN_NO_GOAL 8u     /* never stop / append the goal node: grow the tree to max_nodes */
+#define BGR_PLAN_DEDUP 16u      /* beyond reference (batch > 1): the goal / milestone samples of one batch are the same
+                                 * point and, against one snapshot, the same candidate; keep the first of each and
+                                 * reject the copies (counted in rejected_state) instead of appending coincident nodes */
 #define BGR_PLAN_MODE_RS 0      /* rrt_star.cpp sampler: rand_chance > goal_chance ? table : goal */
 #define BGR_PLAN_MODE_MS 1      /* rrt_star_milestones.cpp sampler: >0.8 table, (0.5,0.8) goal, else milestone[int z] */
 

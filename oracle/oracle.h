@@ -95,6 +95,7 @@ void orc_edge_frame(const float p1[3], const float p2[3], double out[8]);
 #define ORC_PLAN_REWIRE     2u   /* beyond reference: real rewiring (the reference only prints) */
 #define ORC_PLAN_QUIRKS     4u   /* MS:1236-1238: `found` rows keep the Nearest index as stored parent */
 #define ORC_PLAN_NO_GOAL    8u   /* do not stop / append the goal node (grow to max_nodes) */
+#define ORC_PLAN_DEDUP      16u  /* beyond reference: one candidate per distinct goal / milestone sample of a batch */
 typedef struct orc_plan_params {   /* same layout as bgr_planner_params (include/bgrrt.h) */
     float start[3], goal[3];
     float eta;            /* MS:100  0.15 */

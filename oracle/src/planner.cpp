@@ -103,9 +103,11 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
     if (pl->goal_reached) return 0;
     const int B = P.batch, K = P.k;
     const int64_t N = (int64_t)pl->par.size(), T = (int64_t)pl->table.size() / 3, nb = (int64_t)pl->boxes.size() / 6;
-    const bool edge_check = P.flags & 1u, rewire = P.flags & 2u, quirks = P.flags & 4u, no_goal = P.flags & 8u;
+    const bool edge_check = P.flags & 1u, rewire = P.flags & 2u, quirks = P.flags & 4u, no_goal = P.flags & 8u, dedup = P.flags & 16u;
     std::vector<float> prand(3 * B), pnew(3 * B);
     std::vector<uint8_t> found(B);
+    std::vector<int> slot(B, -1);            // -1 table sample, 0 goal, 1 + i milestone i
+    int first_of[4] = {-1, -1, -1, -1};
     // ---- sampler: draw order y, x, (z) — MS:1182-1184 / RS:1155-1156
     for (int c = 0; c < B; ++c) {
         const float rand_chance = (float)orc_mt_std_uniform(pl->mt, 0.0, 1.0);
@@ -115,11 +117,13 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
         if (P.mode == 1) {
             const int mi = (int)orc_mt_std_uniform(pl->mt, 0.0, 3.0);
             if ((double)rand_chance > 0.8) src = pl->table.data() + 3 * ri;
-            else if ((double)rand_chance < 0.8 && (double)rand_chance > 0.5) src = P.goal;
-            else src = pl->milestones.data() + 3 * (mi > 2 ? 2 : mi);
+            else if ((double)rand_chance < 0.8 && (double)rand_chance > 0.5) { src = P.goal; slot[c] = 0; }
+            else { src = pl->milestones.data() + 3 * (mi > 2 ? 2 : mi); slot[c] = 1 + (mi > 2 ? 2 : mi); }
         } else {
-            src = rand_chance > P.goal_chance ? pl->table.data() + 3 * ri : P.goal;
+            if (rand_chance > P.goal_chance) src = pl->table.data() + 3 * ri;
+            else { src = P.goal; slot[c] = 0; }
         }
+        if (slot[c] >= 0 && first_of[slot[c]] < 0) first_of[slot[c]] = c;
         std::memcpy(&prand[3 * c], src, 3 * sizeof(float));
     }
     // ---- Nearest + steer (against the snapshot)
@@ -131,6 +135,11 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
     std::vector<uint8_t> hit(B), band(B);
     orc_collide_spheres(pl->boxes.data(), nb, pnew.data(), B, P.state_radius, 1, 1e-6, hit.data(), band.data(), 0);
     for (int c = 0; c < B; ++c) pl->stats[6] += band[c];
+    // ORC_PLAN_DEDUP: the goal / milestone samples of one batch are the same point and, against one
+    // snapshot, the same candidate: only the first of each is kept, the copies are rejected here
+    if (dedup)
+        for (int c = 0; c < B; ++c)
+            if (slot[c] >= 0 && first_of[slot[c]] != c) hit[c] = 1;
     // ---- kNN + choose parent
     std::vector<int32_t> knn_idx((size_t)B * K, -1), parent(B);
     std::vector<float> knn_d2((size_t)B * K), cost(B), psi(B);

@@ -21,16 +21,20 @@ cand = synth.points(77, 4000, n_map * 0.05)
 hit, _ = omap.collide_spheres(cand, 0.1)
 free = cand[hit == 0]
 print("free candidates", len(free))
+EXTRA = int(os.environ.get("EXTRA_FLAGS", "0"))
 for batch in (64, 256, 1024):
-    t0 = time.perf_counter(); ok = 0; nodes = 0
+    t0 = time.perf_counter(); ok = 0; nodes = 0; plen = 0.0
     NQ = 8
     for qi in range(NQ):
         s, g = free[2 * qi], free[2 * qi + 1]
         P = B.PlannerParams(tuple(s), tuple(g), mode=B.PLAN_MODE_MS, k=16, batch=batch,
-                            flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, seed=100 + qi)
+                            flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | EXTRA, seed=100 + qi)
         pl = B.Planner(P, omap, table, ms)
         reached = pl.run(60000)
         ok += int(reached); nodes += len(pl)
+        if reached:
+            pts = pl.tree()[0][pl.path()].astype(np.float64)
+            plen += float(np.linalg.norm(np.diff(pts, axis=0), axis=1).sum())
     torch.cuda.synchronize()
     el = time.perf_counter() - t0
-    print("batch %d: %d/%d reached, %.1f nodes avg, %.3f s per query" % (batch, ok, NQ, nodes / NQ, el / NQ))
+    print("flags+%d batch %d: %d/%d reached, %.1f nodes avg, %.3f s per query, mean path length %.3f m" % (EXTRA, batch, ok, NQ, nodes / NQ, el / NQ, plen / max(ok, 1)))

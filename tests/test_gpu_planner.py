@@ -76,6 +76,22 @@ def test_batched_edge_checks_and_rewiring(bgr, oracle, world, flags):
         assert gs["rejected_edge"] >= 0
 
 
+@pytest.mark.parametrize("mode,flags", [(0, 16), (1, 16), (1, 16 | 3), (1, 16 | 3 | 8)])
+def test_batched_dedup_of_goal_and_milestone_samples(bgr, oracle, world, mode, flags):
+    # BGR_PLAN_DEDUP: one candidate per distinct goal / milestone sample of a batch, oracle in lockstep
+    gp, gs = _compare(bgr, oracle, world, 2500, 30, mode=mode, k=10, batch=256, flags=flags, seed=3)
+    x, _ = gp.tree()
+    # no two nodes appended in the same batch coincide: distinct coordinates >= nodes - (goal node copies)
+    uniq = np.unique(x.view(np.uint32).reshape(-1, 3), axis=0).shape[0]
+    plain = bgr.Planner(bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=mode, k=10, batch=256,
+                                          flags=flags & ~16, seed=3), world[0], world[2], world[3])
+    plain.run(2500, 30)
+    px, _ = plain.tree()
+    puniq = np.unique(px.view(np.uint32).reshape(-1, 3), axis=0).shape[0]
+    assert uniq / len(x) > puniq / len(px), (uniq, len(x), puniq, len(px))
+    assert gs["rejected_state"] > plain.stats()["rejected_state"]
+
+
 def test_goal_reached_and_path(bgr, oracle, world):
     """run to the goal: goal node appended with the reaching node as parent (MS:1346-1347);
     BuildPlan walks parents back to the root (MS:156-171)."""

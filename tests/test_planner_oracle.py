@@ -90,3 +90,41 @@ def test_batched_rewiring_stays_a_tree(oracle, bgr):
         cur = np.where(alive, par[np.maximum(cur, 0)], cur)
     assert not (cur > 0).any(), "a parent chain does not reach the root: rewiring closed a cycle"
     assert depth.max() < len(par)
+
+
+def test_dedup_keeps_one_candidate_per_fixed_sample(oracle, bgr):
+    """ORC_PLAN_DEDUP (beyond reference): the goal / milestone samples of one batch are the same
+    point against the same snapshot; with the flag each batch appends at most one node per fixed
+    sample, so nodes of one batch no longer coincide, and the table-sample nodes are the ones the
+    plain run would have appended in its first batch."""
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(64, 1, occupancy=0.0)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    table = synth.points(9, 20000, 3.2)
+    ms = np.array([[1.0, 0.5, 1.5], [2.0, 1.0, 2.0], [2.5, 2.0, 1.0]], np.float32)   # not collinear with start -> goal
+
+    def grow(flags, batches):
+        P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_MS, k=8, batch=256,
+                              flags=flags | bgr.PLAN_NO_GOAL, seed=17)
+        op = oracle.Planner(P, boxes, table, ms)
+        sizes = [len(op)]
+        for _ in range(batches):
+            op.step()
+            sizes.append(len(op))
+        return op, sizes
+
+    op, sizes = grow(bgr.PLAN_DEDUP, 12)
+    xyz, _ = op.tree()
+    def copies(x, sz):
+        return sum((b - a) - np.unique(x[a:b].view(np.uint32).reshape(-1, 3), axis=0).shape[0]
+                   for a, b in zip(sz[:-1], sz[1:]))
+
+    plain, psizes = grow(0, 12)
+    pxyz, _ = plain.tree()
+    # what is left are table entries drawn twice in one batch (256 draws of 20 000: rare)
+    assert copies(xyz, sizes) <= 3 and copies(pxyz, psizes) > 300
+    # same draws: the first batch differs only by the dropped copies
+    first = set(map(tuple, xyz[sizes[0]:sizes[1]].view(np.uint32).reshape(-1, 3).tolist()))
+    pfirst = set(map(tuple, pxyz[psizes[0]:psizes[1]].view(np.uint32).reshape(-1, 3).tolist()))
+    assert first == pfirst and sizes[1] < psizes[1]
+    assert op.stats()["rejected_state"] > plain.stats()["rejected_state"]
