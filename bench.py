@@ -495,6 +495,17 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def host_cpu_model():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("model name"):
+                    return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
 def cpu_knn_baseline(pts, q, budget_s):
     """the oracle's libnabo-1.0.7 kd-tree restatement (kind "port"), OpenMP over queries on all
     host cores; index prebuilt (as for the GPU arm); repeated until ~budget_s of wall time."""
@@ -511,7 +522,7 @@ def cpu_knn_baseline(pts, q, budget_s):
         el = time.perf_counter() - t0
         if el > budget_s or reps >= 50:
             break
-    return {"value": reps * len(q) / el, "unit": "queries/s", "cores": cores, "kind": "port",
+    return {"value": reps * len(q) / el, "unit": "queries/s", "cores": cores, "kind": "port", "cpu_model": host_cpu_model(),
             "sample": "%d x %d queries, k=%d, on the prebuilt kd-tree of %d nodes (build %.2f s not counted); "
                       "libnabo restatement oracle/src/nabo_kdtree.cpp" % (reps, len(q), K_NN, len(pts), build_s)}
 
@@ -567,7 +578,7 @@ def run_reference(args):
         tree.knn(q, K_NN, threads=cores)
     el = time.perf_counter() - t0
     value = args.steps * N_QUERIES / el
-    cb = {"value": value, "unit": "queries/s", "cores": cores, "kind": "port",
+    cb = {"value": value, "unit": "queries/s", "cores": cores, "kind": "port", "cpu_model": host_cpu_model(),
           "sample": "%d steps x %d queries, k=%d, prebuilt libnabo-restatement kd-tree over %d nodes" % (args.steps, N_QUERIES, K_NN, N_NODES)}
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3, "higher_is_better": True,
