@@ -99,26 +99,35 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
     const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (i >= n) return;
     const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
-    if (dil.bits) {
-        // gate: level 0 dilated by ceil((radius + 1e-4) / res) cells.  The centre's cell clear in it =>
-        // no leaf within radius + 1e-4 of the centre: free, and not a tolerance-band contact.
+    {
         const int gx = (int)floor((c[0] - m.origin[0]) * m.inv_res), gy = (int)floor((c[1] - m.origin[1]) * m.inv_res),
                   gz = (int)floor((c[2] - m.origin[2]) * m.inv_res);
-        if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2] && !test_bit(dil, gx, gy, gz)) {
-            if (lane == 0) {
-                hit[i] = 0;
-                if (band) band[i] = 0;
+        if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2]) {
+            // gate: level 0 dilated by ceil((radius + 1e-4) / res) cells.  The centre's cell clear in it =>
+            // no leaf within radius + 1e-4 of the centre: free, and not a tolerance-band contact.
+            // The centre's own cell occupied => distance 0, gap = -radius: decided without the box walk.
+            const bool clear = dil.bits && !test_bit(dil, gx, gy, gz);
+            if (clear || test_bit(m.lv[0], gx, gy, gz)) {
+                if (lane == 0) {
+                    hit[i] = (!clear && radius > 0.0) ? 1 : 0;
+                    if (band) band[i] = (!clear && radius <= kBandTol) ? 1 : 0;
+                }
+                return;
             }
-            return;
         }
     }
+    // a cell closer than radius - tolerance decides the query (hit, not in the band): stop looking
+    const double thr2 = radius > kBandTol ? (radius - kBandTol) * (radius - kBandTol) * (1.0 - 1e-12) : -1.0;
+    bool decided = false;
     int lo[3], hi[3];
     bool empty = false;
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
         const double r = radius + kSweepMargin;
-        lo[a] = max(0, (int)floor((c[a] - r - m.origin[a]) * m.inv_res) - 1);
-        hi[a] = min(m.dims[a] - 1, (int)floor((c[a] + r - m.origin[a]) * m.inv_res) + 1);
+        // cells outside [c - r, c + r] are farther than radius + 1e-4: they decide neither hit nor band
+        // (the 1e-4 m margin is ~1e9 times the rounding of the cell computation)
+        lo[a] = max(0, (int)floor((c[a] - r - m.origin[a]) * m.inv_res));
+        hi[a] = min(m.dims[a] - 1, (int)floor((c[a] + r - m.origin[a]) * m.inv_res));
         empty |= lo[a] > hi[a];
     }
     double d2min = 1e300;
@@ -127,7 +136,7 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         const int nbr[3] = {(hi[0] >> 2) - bl[0] + 1, (hi[1] >> 2) - bl[1] + 1, (hi[2] >> 2) - bl[2] + 1};
         const int total = nbr[0] * nbr[1] * nbr[2];
         const double half = 0.5 * m.res;
-        for (int t0 = 0; t0 < total; t0 += 32) {
+        for (int t0 = 0; t0 < total && !decided; t0 += 32) {
             // ---- one brick per lane: its word masked to the box
             const int t = t0 + lane;
             unsigned long long W = 0ull;
@@ -179,8 +188,16 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
                     d2 += tz * tz;
                     d2min = fmin(d2min, d2);
                 }
+                if (__any_sync(kFull, d2min < thr2)) { decided = true; break; }
             }
         }
+    }
+    if (decided) {
+        if (lane == 0) {
+            hit[i] = 1;
+            if (band) band[i] = 0;
+        }
+        return;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) d2min = fmin(d2min, __shfl_xor_sync(kFull, d2min, o));
