@@ -82,40 +82,62 @@ __global__ void popcount_kernel(const uint64_t* __restrict__ bits, int64_t n, un
 // ------------------------------------------------------------------ spheres (isStateValid)
 // Exact closed form: gap = dist(centre, leaf box) - r in double; hit = gap < 0.
 __device__ __forceinline__ int nth_set_bit64(unsigned long long v, int r) {   // r-th (0-based) set bit
-    const unsigned lo32 = (unsigned)v, hi32 = (unsigned)(v >> 32);
-    const int clo = __popc(lo32);
-    return r < clo ? (int)__fns(lo32, 0, r + 1) : 32 + (int)__fns(hi32, 0, r - clo + 1);
+    // popcount bisection (the __fns intrinsic is a long software loop)
+    unsigned w = (unsigned)v;
+    int base = 0, c = __popc(w);
+    if (r >= c) { r -= c; w = (unsigned)(v >> 32); base = 32; }
+    c = __popc(w & 0xFFFFu); if (r >= c) { r -= c; w >>= 16; base += 16; }
+    c = __popc(w & 0xFFu);   if (r >= c) { r -= c; w >>= 8;  base += 8; }
+    c = __popc(w & 0xFu);    if (r >= c) { r -= c; w >>= 4;  base += 4; }
+    c = __popc(w & 0x3u);    if (r >= c) { r -= c; w >>= 2;  base += 2; }
+    return base + ((r >= (int)(w & 1u)) ? 1 : 0);
 }
 
-// One warp per sphere: the cells of the sphere's box (radius + margin, +1 cell) are read as whole
-// 4x4x4 brick words, one brick per lane (a 0.1 m sphere at 0.05 m cells touches <= 3x3x3 bricks:
-// 27 loads instead of 343 bit probes), masked to the box; each lane walks the set bits of its
-// word: leaf of the cell, exact point-to-box distance.  min over the warp.
+// The cells of the sphere's box (radius + margin) are read as whole 4x4x4 brick words, one brick per
+// lane (a 0.1 m sphere at 0.05 m cells touches <= 3x3x3 bricks: 27 loads instead of 125+ bit probes),
+// masked to the box; the set bits are spread over the lanes: exact point-to-cell distance, min over
+// the warp.  G = spheres per warp: with G = 32 (large batches) each lane first runs the gate of its
+// own sphere and the warp then walks only the undecided ones, one after the other; G = 1 (small
+// batches, e.g. a planner step) keeps one warp per sphere so the walks run side by side.
+template <int G>
 __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const float* __restrict__ c3,
                                                               int64_t n, double radius,
                                                               uint8_t* __restrict__ hit,
                                                               uint8_t* __restrict__ band, LevelGrid dil) {
     const int lane = threadIdx.x & 31;
-    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (i >= n) return;
-    const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
-    {
-        const int gx = (int)floor((c[0] - m.origin[0]) * m.inv_res), gy = (int)floor((c[1] - m.origin[1]) * m.inv_res),
-                  gz = (int)floor((c[2] - m.origin[2]) * m.inv_res);
+    const int64_t first = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * G;
+    if (first >= n) return;
+    const int64_t my = first + (G == 1 ? 0 : lane);
+    double mc[3] = {0.0, 0.0, 0.0};
+    bool need = false;
+    if (my < n) {
+        mc[0] = (double)c3[3 * my]; mc[1] = (double)c3[3 * my + 1]; mc[2] = (double)c3[3 * my + 2];
+        need = true;
+        const int gx = (int)floor((mc[0] - m.origin[0]) * m.inv_res), gy = (int)floor((mc[1] - m.origin[1]) * m.inv_res),
+                  gz = (int)floor((mc[2] - m.origin[2]) * m.inv_res);
         if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2]) {
             // gate: level 0 dilated by ceil((radius + 1e-4) / res) cells.  The centre's cell clear in it =>
             // no leaf within radius + 1e-4 of the centre: free, and not a tolerance-band contact.
             // The centre's own cell occupied => distance 0, gap = -radius: decided without the box walk.
-            const bool clear = dil.bits && !test_bit(dil, gx, gy, gz);
-            if (clear || test_bit(m.lv[0], gx, gy, gz)) {
-                if (lane == 0) {
-                    hit[i] = (!clear && radius > 0.0) ? 1 : 0;
-                    if (band) band[i] = (!clear && radius <= kBandTol) ? 1 : 0;
+            const int64_t w = ((int64_t)(gz >> 2) * m.lv[0].nb[1] + (gy >> 2)) * m.lv[0].nb[0] + (gx >> 2);   // same geometry in both maps
+            const int b = ((gz & 3) << 4) | ((gy & 3) << 2) | (gx & 3);
+            const bool clear = dil.bits && !((__ldg(dil.bits + w) >> b) & 1ull);
+            if (clear || ((__ldg(m.lv[0].bits + w) >> b) & 1ull)) {
+                if (G != 1 || lane == 0) {
+                    hit[my] = (!clear && radius > 0.0) ? 1 : 0;
+                    if (band) band[my] = (!clear && radius <= kBandTol) ? 1 : 0;
                 }
-                return;
+                need = false;
             }
         }
     }
+    unsigned pending = __ballot_sync(kFull, need);
+    if (G == 1) pending &= 1u;
+    while (pending) {
+    const int src = __ffs(pending) - 1;
+    pending &= pending - 1u;
+    const int64_t i = first + src;
+    const double c[3] = {__shfl_sync(kFull, mc[0], src), __shfl_sync(kFull, mc[1], src), __shfl_sync(kFull, mc[2], src)};
     // a cell closer than radius - tolerance decides the query (hit, not in the band): stop looking
     const double thr2 = radius > kBandTol ? (radius - kBandTol) * (radius - kBandTol) * (1.0 - 1e-12) : -1.0;
     bool decided = false;
@@ -135,6 +157,8 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         const int bl[3] = {lo[0] >> 2, lo[1] >> 2, lo[2] >> 2};
         const int nbr[3] = {(hi[0] >> 2) - bl[0] + 1, (hi[1] >> 2) - bl[1] + 1, (hi[2] >> 2) - bl[2] + 1};
         const int total = nbr[0] * nbr[1] * nbr[2];
+        const int n01 = nbr[0] * nbr[1];
+        const float inv0 = 1.f / (float)nbr[0], inv01 = 1.f / (float)n01;   // exact quotients below 2^20 bricks
         const double half = 0.5 * m.res;
         for (int t0 = 0; t0 < total && !decided; t0 += 32) {
             // ---- one brick per lane: its word masked to the box
@@ -142,7 +166,16 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
             unsigned long long W = 0ull;
             int bxyz = 0;
             if (t < total) {
-                const int bx = bl[0] + t % nbr[0], by = bl[1] + (t / nbr[0]) % nbr[1], bz = bl[2] + t / (nbr[0] * nbr[1]);
+                int oz, oy, ox;
+                if (total < (1 << 20)) {
+                    oz = (int)(((float)t + 0.5f) * inv01);
+                    const int rem = t - oz * n01;
+                    oy = (int)(((float)rem + 0.5f) * inv0);
+                    ox = rem - oy * nbr[0];
+                } else {
+                    oz = t / n01; oy = (t / nbr[0]) % nbr[1]; ox = t % nbr[0];
+                }
+                const int bx = bl[0] + ox, by = bl[1] + oy, bz = bl[2] + oz;
                 W = __ldg(m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0] + bx);
                 // cells of this brick inside the box, per axis (x: nibble pattern, y: 4-bit groups, z: 16-bit groups)
                 const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
@@ -197,7 +230,7 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
             hit[i] = 1;
             if (band) band[i] = 0;
         }
-        return;
+        continue;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) d2min = fmin(d2min, __shfl_xor_sync(kFull, d2min, o));
@@ -206,6 +239,7 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         hit[i] = gmin < 0.0 ? 1 : 0;
         if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
     }
+    }   // while (pending)
 }
 
 // ------------------------------------------------------------------ edges (isLineValid)
@@ -1440,7 +1474,12 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
         BGR_CHECK(ensure_dilated(h, gate_d, &bits));
         dil.bits = const_cast<uint64_t*>(bits);
     }
-    collide_spheres_kernel<<<(unsigned)div_up(n, 4), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
+    // large batches: 32 spheres per warp (lane-per-sphere gate, then the warp walks the undecided ones);
+    // small ones: a warp per sphere so the walks overlap
+    if (n >= (int64_t)num_sms() * 2048)
+        collide_spheres_kernel<32><<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
+    else
+        collide_spheres_kernel<1><<<(unsigned)div_up(n, 4), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
     BGR_LAUNCH_CHECK();
     return BGR_OK;
 }
