@@ -41,6 +41,7 @@ struct GridIndex {
     DevBuf<int32_t> block_sums;
     DevBuf<float> partial;        // bbox partials
     DevBuf<double> sumsq;         // build scratch
+    DevBuf<int32_t> heavy;        // queries handed to grid_knn_heavy_kernel and its scratch (layout: kHeavyInts)
     double crowd = 0.0;           // sum(cell count^2) / n: the occupancy of the cell an average NODE sits in
                                   // (~kPtsPerCell+1 for a uniform cloud, thousands for a piled-up tree)
 };
@@ -274,7 +275,7 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
 
 inline void grid_release(GridIndex& G) {
     G.pts.release(); G.cell_start.release(); G.cell_id.release(); G.cursor.release();
-    G.block_sums.release(); G.partial.release(); G.sumsq.release();
+    G.block_sums.release(); G.partial.release(); G.sumsq.release(); G.heavy.release();
     G.n_indexed = 0;
 }
 
@@ -301,6 +302,9 @@ struct GridKnnArgs {
     int fast;            // enable the one-pass ring-1 path
     const uint8_t* skip; // optional per-query flag: non-zero = leave this query's rows untouched
     float fast_target;   // expected survivors the a-priori threshold aims at (k + ~2.5 sqrt k)
+    int32_t* heavy;      // optional: [0] count, [1..heavy_cap] query numbers (see grid_knn_heavy_kernel)
+    int heavy_cap;
+    int64_t heavy_min;   // ring-1 block + tail at least this long => heavy
 };
 
 __device__ __forceinline__ uint32_t radius_sentinel_g(float mr) {
@@ -323,7 +327,11 @@ constexpr int kGridWarps = 8;
 // repeated; after kFastTries the caller falls back to the general ring search.
 constexpr int kFastTries = 3;
 
-__global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArgs a) {
+// PILED = the index is crowded (see grid_knn): pile queries are set aside for grid_knn_heavy_kernel
+// and the long scans (unsorted tail, rows longer than a warp) keep 3 x 32 nodes in flight; the lean
+// instantiation serves uniform clouds, where neither occurs and the extra registers would spill.
+template <bool PILED>
+__global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kernel(GridKnnArgs a) {
     __shared__ unsigned long long cand[kGridWarps][kFastCap];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
@@ -378,6 +386,16 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
 #pragma unroll
         for (int o = 8; o > 0; o >>= 1) n27 += __shfl_xor_sync(kFull, n27, o);   // lanes 0..15 hold rows
         n27 = __shfl_sync(kFull, n27, 0);
+        if (PILED && a.heavy && (int64_t)n27 + (a.n - a.n_indexed) >= a.heavy_min) {
+            // a piled-up block (thousands of coincident nodes): one warp would walk it alone, several times
+            int slot = 0;
+            if (lane == 0) slot = atomicAdd(a.heavy, 1);
+            slot = __shfl_sync(kFull, slot, 0);
+            if (slot < a.heavy_cap) {
+                if (lane == 0) a.heavy[1 + slot] = (int32_t)qi;
+                return;
+            }
+        }
         const float b2 = face2(1);
         // largest usable threshold: strictly below the unscanned region, within the radius limit
         const float tmax = fminf(lim, b2 == __uint_as_float(kInfBits) ? lim : __uint_as_float(max(__float_as_uint(b2), 1u) - 1u));
@@ -400,10 +418,27 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
                     }
                     c += __popc(m);
                 };
-                for (int64_t base = a.n_indexed; base < a.n; base += 32) {          // unsorted tail
-                    const int64_t j = base + lane;
-                    const bool valid = j < a.n;
-                    consider(valid ? a.x[j] : 0.f, valid ? a.y[j] : 0.f, valid ? a.z[j] : 0.f, (uint32_t)j, valid);
+                if (PILED) {
+                    for (int64_t base = a.n_indexed; base < a.n; base += 96) {          // unsorted tail, 3 x 32 nodes in flight
+                        float tx[3], ty[3], tz[3];
+    #pragma unroll
+                        for (int u = 0; u < 3; ++u) {
+                            const int64_t j = base + 32 * u + lane;
+                            const bool valid = j < a.n;
+                            tx[u] = valid ? a.x[j] : 0.f; ty[u] = valid ? a.y[j] : 0.f; tz[u] = valid ? a.z[j] : 0.f;
+                        }
+    #pragma unroll
+                        for (int u = 0; u < 3; ++u) {
+                            const int64_t j = base + 32 * u + lane;
+                            if (base + 32 * u < a.n) consider(tx[u], ty[u], tz[u], (uint32_t)j, j < a.n);
+                        }
+                    }
+                } else {
+                    for (int64_t base = a.n_indexed; base < a.n; base += 32) {          // unsorted tail
+                        const int64_t j = base + lane;
+                        const bool valid = j < a.n;
+                        consider(valid ? a.x[j] : 0.f, valid ? a.y[j] : 0.f, valid ? a.z[j] : 0.f, (uint32_t)j, valid);
+                    }
                 }
                 // rows in groups of three: the three leading LDG.128 are in flight together
 #pragma unroll 1
@@ -420,12 +455,28 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
                         if (s0[i] < e0[i]) consider(p[i].x, p[i].y, p[i].z, (uint32_t)__float_as_int(p[i].w), s0[i] + lane < e0[i]);
-                        for (int b = s0[i] + 32; b < e0[i]; b += 32) {      // rows longer than a warp (rare)
-                            const int j = b + lane;
-                            const bool valid = j < e0[i];
-                            float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (valid) q4 = __ldg(a.pts + j);
-                            consider(q4.x, q4.y, q4.z, (uint32_t)__float_as_int(q4.w), valid);
+                        if (PILED) {
+                            for (int b = s0[i] + 32; b < e0[i]; b += 96) {      // rows longer than a warp: 3 x 32 nodes in flight
+                                float4 q4[3];
+#pragma unroll
+                                for (int u = 0; u < 3; ++u) {
+                                    const int j = b + 32 * u + lane;
+                                    q4[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                                    if (j < e0[i]) q4[u] = __ldg(a.pts + j);
+                                }
+#pragma unroll
+                                for (int u = 0; u < 3; ++u)
+                                    if (b + 32 * u < e0[i])
+                                        consider(q4[u].x, q4[u].y, q4[u].z, (uint32_t)__float_as_int(q4[u].w), b + 32 * u + lane < e0[i]);
+                            }
+                        } else {
+                            for (int b = s0[i] + 32; b < e0[i]; b += 32) {      // rows longer than a warp (rare)
+                                const int j = b + lane;
+                                const bool valid = j < e0[i];
+                                float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (valid) q4 = __ldg(a.pts + j);
+                                consider(q4.x, q4.y, q4.z, (uint32_t)__float_as_int(q4.w), valid);
+                            }
                         }
                     }
                 }
@@ -475,11 +526,28 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
     };
 
     // ---- unsorted tail [n_indexed, n)
-    for (int64_t base = a.n_indexed; base < a.n; base += 32) {
-        const int64_t j = base + lane;
-        const bool valid = j < a.n;
-        const float px = valid ? a.x[j] : 0.f, py = valid ? a.y[j] : 0.f, pz = valid ? a.z[j] : 0.f;
-        offer(px, py, pz, (uint32_t)j, valid);
+    if (PILED) {
+        for (int64_t base = a.n_indexed; base < a.n; base += 96) {
+            float tx[3], ty[3], tz[3];
+    #pragma unroll
+            for (int u = 0; u < 3; ++u) {
+                const int64_t j = base + 32 * u + lane;
+                const bool valid = j < a.n;
+                tx[u] = valid ? a.x[j] : 0.f; ty[u] = valid ? a.y[j] : 0.f; tz[u] = valid ? a.z[j] : 0.f;
+            }
+    #pragma unroll
+            for (int u = 0; u < 3; ++u) {
+                const int64_t j = base + 32 * u + lane;
+                if (base + 32 * u < a.n) offer(tx[u], ty[u], tz[u], (uint32_t)j, j < a.n);
+            }
+        }
+    } else {
+        for (int64_t base = a.n_indexed; base < a.n; base += 32) {
+            const int64_t j = base + lane;
+            const bool valid = j < a.n;
+            const float px = valid ? a.x[j] : 0.f, py = valid ? a.y[j] : 0.f, pz = valid ? a.z[j] : 0.f;
+            offer(px, py, pz, (uint32_t)j, valid);
+        }
     }
     touched += (unsigned long long)(a.n - a.n_indexed);
 
@@ -522,12 +590,27 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
                     nonempty &= nonempty - 1;
                     const int rs = __shfl_sync(kFull, s, src), re = __shfl_sync(kFull, e, src);
                     touched += (unsigned long long)(re - rs);
-                    for (int b = rs; b < re; b += 32) {
-                        const int j = b + lane;
-                        const bool valid = j < re;
-                        float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (valid) p = __ldg(a.pts + j);
-                        offer(p.x, p.y, p.z, (uint32_t)__float_as_int(p.w), valid);
+                    if (PILED) {
+                        for (int b = rs; b < re; b += 96) {
+                            float4 p[3];
+    #pragma unroll
+                            for (int u = 0; u < 3; ++u) {
+                                const int j = b + 32 * u + lane;
+                                p[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                                if (j < re) p[u] = __ldg(a.pts + j);
+                            }
+    #pragma unroll
+                            for (int u = 0; u < 3; ++u)
+                                if (b + 32 * u < re) offer(p[u].x, p[u].y, p[u].z, (uint32_t)__float_as_int(p[u].w), b + 32 * u + lane < re);
+                        }
+                    } else {
+                        for (int b = rs; b < re; b += 32) {
+                            const int j = b + lane;
+                            const bool valid = j < re;
+                            float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (valid) p = __ldg(a.pts + j);
+                            offer(p.x, p.y, p.z, (uint32_t)__float_as_int(p.w), valid);
+                        }
                     }
                 }
             }
@@ -545,6 +628,102 @@ __global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArg
         a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
     }
     if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+}
+
+// Queries the main kernel set aside because their ring-1 block is piled up (a planner tree holds
+// thousands of coincident copies of a reached milestone; no grid separates them, and one warp
+// walking the pile alone, several times, was 0.19 ms of a 0.52 ms planner step).  Each such query
+// is scanned over the whole raw store by kHeavySlices CTAs on different SMs: CTA (b, s) takes the
+// 128-node tiles s, s + S, s + 2S, ... in a scrambled order (growth-ordered store: an in-order scan
+// tightens its bound on almost every tile), its 4 warp lists are merged through shared memory, and
+// the CTA that finishes last merges the S partial lists and writes the row.  Same arithmetic, same
+// admission rules and the same (d2, index) order as the ring search => the same rows.
+constexpr int kHeavyCap = 256;
+constexpr int kHeavySlices = 32;
+constexpr int kHeavyWarps = 4;
+// layout of GridIndex::heavy (int32): [0] count | [1, 1+cap) queries | [1+cap, 1+2cap) finished slices |
+// then cap * S * 32 * 2 words of partial lists
+constexpr int kHeavyInts = 1 + 2 * kHeavyCap + kHeavyCap * kHeavySlices * 64;
+
+__global__ void __launch_bounds__(kHeavyWarps * 32) grid_knn_heavy_kernel(GridKnnArgs a) {
+    __shared__ uint32_t sd[kHeavyWarps][32], si[kHeavyWarps][32];
+    const int b = blockIdx.x, sl = blockIdx.y;
+    const int cnt = min(a.heavy[0], a.heavy_cap);
+    if (b >= cnt) return;
+    const int64_t qi = a.heavy[1 + b];
+    int* done = a.heavy + 1 + a.heavy_cap;
+    uint32_t* part = reinterpret_cast<uint32_t*>(a.heavy + 1 + 2 * a.heavy_cap);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
+    const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
+    const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
+    WarpList L;
+    L.init(sent);
+    uint32_t tau_d = sent, tau_i = 0u;
+    float tau_f = __uint_as_float(sent);
+    constexpr int kTileN = kHeavyWarps * 32;
+    const int64_t ntiles = (a.n + kTileN - 1) / kTileN;
+    const int M = ntiles > sl ? (int)((ntiles - sl + kHeavySlices - 1) / kHeavySlices) : 0;
+    int stride = 1;
+    if (M >= 3) {
+        for (stride = max(1, (int)(0.6180339887f * (float)M));; ++stride) {
+            int u = stride, v = M;
+            while (v) { const int w = u % v; u = v; v = w; }
+            if (u == 1) break;
+        }
+    }
+    for (int m = 0; m < M; ++m) {
+        const int mm = (int)(((long long)m * stride) % M);
+        const int64_t j = ((int64_t)sl + (int64_t)kHeavySlices * mm) * kTileN + threadIdx.x;
+        const bool valid = j < a.n;
+        const float px = valid ? a.x[j] : 0.f, py = valid ? a.y[j] : 0.f, pz = valid ? a.z[j] : 0.f;
+        const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
+        const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        const bool pass = valid && (d <= tau_f) && (self || d > FLT_EPSILON);
+        if (__any_sync(kFull, pass)) {
+            warp_offer(L, pass, __float_as_uint(d), (uint32_t)j, tau_d, tau_i, a.k, lane);
+            tau_f = __uint_as_float(tau_d);
+        }
+    }
+    sd[warp][lane] = L.d;
+    si[warp][lane] = L.i;
+    __syncthreads();
+    if (warp != 0) return;
+    for (int w = 1; w < kHeavyWarps; ++w) {
+        const uint32_t cd = sd[w][lane], ci = si[w][lane];
+        const bool pass = lane < a.k && cd != sent;
+        if (__any_sync(kFull, pass)) warp_offer(L, pass, cd, ci, tau_d, tau_i, a.k, lane);
+    }
+    uint32_t* mine = part + (((size_t)b * kHeavySlices + sl) * 32 + lane) * 2;
+    __stcg(mine, L.d);
+    __stcg(mine + 1, L.i);
+    __threadfence();
+    __syncwarp();
+    int prev = 0;
+    if (lane == 0) prev = atomicAdd(done + b, 1);
+    prev = __shfl_sync(kFull, prev, 0);
+    if (prev != kHeavySlices - 1) return;
+    __threadfence();
+    for (int s0 = 0; s0 < kHeavySlices; s0 += 8) {          // 8 partial lists in flight
+        uint32_t cd[8], ci[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const uint32_t* other = part + (((size_t)b * kHeavySlices + s0 + u) * 32 + lane) * 2;
+            cd[u] = __ldcg(other);
+            ci[u] = __ldcg(other + 1);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const bool pass = s0 + u != sl && lane < a.k && cd[u] != sent;
+            if (__any_sync(kFull, pass)) warp_offer(L, pass, cd[u], ci[u], tau_d, tau_i, a.k, lane);
+        }
+    }
+    if (lane < a.k) {
+        const bool empty = (L.d == sent);
+        a.idx[qi * a.k + lane] = empty ? -1 : (int32_t)((int64_t)L.i + a.index_base);
+        a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
+    }
+    if (a.counter && lane == 0) atomicAdd(a.counter, (unsigned long long)a.n);
 }
 
 // ---------------------------------------------------------------- grid Nearest (MS:138-154)
@@ -730,8 +909,22 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     a.fast = fast;
     a.skip = d_skip;
     a.fast_target = (float)k + 2.5f * sqrtf((float)k) + 1.f;
-    grid_knn_kernel<<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
+    // piled-up index (crowd: occupancy of the cell an average node sits in; ~9 for a uniform cloud):
+    // queries whose ring-1 block is a pile go to the CTA-per-query scan
+    a.heavy = nullptr; a.heavy_cap = 0; a.heavy_min = 0;
+    if (fast && G.n_indexed > 0 && G.crowd > 64.0) {
+        BGR_CHECK(G.heavy.reserve(kHeavyInts, st, false));
+        BGR_CUDA(cudaMemsetAsync(G.heavy.p, 0, (1 + 2 * kHeavyCap) * sizeof(int32_t), st));
+        a.heavy = G.heavy.p; a.heavy_cap = kHeavyCap;
+        a.heavy_min = std::max<int64_t>(2048, n / 128);
+    }
+    if (a.heavy) grid_knn_kernel<true><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
+    else grid_knn_kernel<false><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
+    if (a.heavy) {
+        grid_knn_heavy_kernel<<<dim3(kHeavyCap, kHeavySlices), kHeavyWarps * 32, 0, st>>>(a);
+        BGR_LAUNCH_CHECK();
+    }
     return BGR_OK;
 }
 

@@ -184,6 +184,29 @@ __global__ void plan_dedup_kernel(PlanDev d) {
     if (slot < d.n_fixed && (long long)(d.B - c) != d.counters[11 + slot]) d.hit[c] = 1;
 }
 
+// The goal / milestone candidates of a batch that share a sample slot share the nearest node, the
+// steered point and therefore the neighbour rows: the search runs for the first of them only
+// (kskip marks the others) and plan_knn_spread_kernel copies its rows to the copies.
+__global__ void plan_knn_rep_kernel(PlanDev d, uint8_t* __restrict__ kskip) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= d.B) return;
+    const int slot = d.qslot[c];
+    kskip[c] = (d.hit[c] || (slot < d.n_fixed && (long long)(d.B - c) != d.counters[11 + slot])) ? 1 : 0;
+}
+
+__global__ void plan_knn_spread_kernel(PlanDev d, float* __restrict__ knn_d2) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)d.B * d.K) return;
+    const int c = (int)(t / d.K), j = (int)(t - (int64_t)c * d.K);
+    if (d.hit[c]) return;
+    const int slot = d.qslot[c];
+    if (slot >= d.n_fixed) return;
+    const int first = d.B - (int)d.counters[11 + slot];
+    if (first == c) return;
+    d.knn_idx[(size_t)c * d.K + j] = d.knn_idx[(size_t)first * d.K + j];
+    knn_d2[(size_t)c * d.K + j] = knn_d2[(size_t)first * d.K + j];
+}
+
 __global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= d.B) return;
@@ -433,9 +456,12 @@ struct bgr_planner {
     int nm = 0;
     int goal_reached = 0;
     int64_t stats[8] = {0, 0, 0, 0, 0, 0, 0, -1};
-    DevBuf<uint32_t> mt_state, words;
+    DevBuf<uint32_t> mt_state, words, words2;   // sample-stream words: this step's and the next one's (filled ahead)
+    int words_cur = 0;
+    bool words_ahead = false;                   // the current buffer was filled at the end of the previous step
+    cudaEvent_t ev_step = nullptr;              // recorded after the counters copy of the step in flight
     DevBuf<float> table, milestones, prand, pnew, near_dist, knn_d2, e1, e2, costs, cost, psis, psi;
-    DevBuf<uint8_t> found, hit, band, ehit, eband, ok;
+    DevBuf<uint8_t> found, hit, kskip, band, ehit, eband, ok;
     DevBuf<int32_t> par, near, knn_idx, parent, new_index, qslot, u_near;
     DevBuf<float> uq, u_dist;
     int64_t pending_n = 0;     // tree size at the launch of the step in flight
@@ -452,10 +478,11 @@ int bgr_planner_destroy(bgr_planner* pl) {
     if (!pl) return BGR_OK;
     cudaStreamSynchronize(pl->stream);
     if (pl->nns) bgr_nns_destroy(pl->nns);
-    pl->mt_state.release(); pl->words.release(); pl->table.release(); pl->milestones.release();
+    if (pl->ev_step) cudaEventDestroy(pl->ev_step);
+    pl->mt_state.release(); pl->words.release(); pl->words2.release(); pl->table.release(); pl->milestones.release();
     pl->prand.release(); pl->pnew.release(); pl->near_dist.release(); pl->knn_d2.release();
     pl->e1.release(); pl->e2.release(); pl->costs.release(); pl->cost.release(); pl->psis.release(); pl->psi.release();
-    pl->found.release(); pl->hit.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
+    pl->found.release(); pl->hit.release(); pl->kskip.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
     pl->ok.release(); pl->par.release(); pl->near.release(); pl->knn_idx.release(); pl->parent.release();
     pl->new_index.release(); pl->rkey.release(); pl->counters.release(); pl->host_counters.release();
     delete pl;
@@ -537,11 +564,13 @@ static int step_launch(bgr_planner* pl) {
     BGR_CHECK(nns_reserve(pl->nns, N + B + 1));
     BGR_CHECK(pl->par.reserve(N + B + 1, st, true, N));
     BGR_CHECK(pl->words.reserve((int64_t)B * W, st, false));
+    BGR_CHECK(pl->words2.reserve((int64_t)B * W, st, false));
     BGR_CHECK(pl->prand.reserve(3 * (int64_t)B, st, false));
     BGR_CHECK(pl->pnew.reserve(3 * (int64_t)B, st, false));
     BGR_CHECK(pl->near_dist.reserve(B, st, false));
     BGR_CHECK(pl->found.reserve(B, st, false));
     BGR_CHECK(pl->hit.reserve(B, st, false));
+    BGR_CHECK(pl->kskip.reserve(B, st, false));
     BGR_CHECK(pl->band.reserve(B, st, false));
     BGR_CHECK(pl->ok.reserve(B, st, false));
     BGR_CHECK(pl->near.reserve(B, st, false));
@@ -580,7 +609,9 @@ static int step_launch(bgr_planner* pl) {
     d.x = x; d.y = y; d.z = z;
     d.par = pl->par.p;
     d.n = N; d.B = B; d.K = K; d.W = W; d.have_knn = have_knn;
-    d.words = pl->words.p; d.table = pl->table.p; d.nt = pl->nt; d.milestones = pl->milestones.p;
+    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
+    uint32_t* words_next = pl->words_cur ? pl->words.p : pl->words2.p;
+    d.words = words_now; d.table = pl->table.p; d.nt = pl->nt; d.milestones = pl->milestones.p;
     d.prand = pl->prand.p; d.pnew = pl->pnew.p; d.found = pl->found.p; d.near = pl->near.p;
     d.hit = pl->hit.p; d.band = pl->band.p; d.knn_idx = pl->knn_idx.p;
     d.e1 = pl->e1.p; d.e2 = pl->e2.p; d.ehit = pl->ehit.p; d.eband = pl->eband.p;
@@ -590,8 +621,10 @@ static int step_launch(bgr_planner* pl) {
 
     const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);
     BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
-    mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, pl->words.p, B * W);
-    BGR_LAUNCH_CHECK();
+    if (!pl->words_ahead) {
+        mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, words_now, B * W);
+        BGR_LAUNCH_CHECK();
+    }
     plan_sample_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
     BGR_CHECK(nns_nearest_counted(pl->nns, pl->uq.p, B + n_fixed, pl->unique_hint > 0 ? pl->unique_hint + pl->unique_hint / 4 + 8 : B + n_fixed,
@@ -603,9 +636,15 @@ static int step_launch(bgr_planner* pl) {
         plan_dedup_kernel<<<gb, 256, 0, st>>>(d);
         BGR_LAUNCH_CHECK();
     }
-    if (have_knn)
-        // candidates the state check rejected never read their neighbour rows: skip their search
-        BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->hit.p, pl->knn_idx.p, pl->knn_d2.p));
+    if (have_knn) {
+        // candidates the state check rejected never read their neighbour rows, and the copies of a goal /
+        // milestone candidate have the rows of the first one: skip their searches
+        plan_knn_rep_kernel<<<gb, 256, 0, st>>>(d, pl->kskip.p);
+        BGR_LAUNCH_CHECK();
+        BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->kskip.p, pl->knn_idx.p, pl->knn_d2.p));
+        plan_knn_spread_kernel<<<gbk, 256, 0, st>>>(d, pl->knn_d2.p);
+        BGR_LAUNCH_CHECK();
+    }
     if (edge_check) {
         plan_edges_kernel<<<gbk1, 256, 0, st>>>(d);
         BGR_LAUNCH_CHECK();
@@ -628,6 +667,14 @@ static int step_launch(bgr_planner* pl) {
     }
     long long* hc = (long long*)pl->host_counters.p;
     BGR_CUDA(cudaMemcpyAsync(hc, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    if (!pl->ev_step) BGR_CUDA(cudaEventCreateWithFlags(&pl->ev_step, cudaEventDisableTiming));
+    BGR_CUDA(cudaEventRecord(pl->ev_step, st));
+    // the sample stream does not depend on the tree: the next step's words (a single-CTA, serial MT19937
+    // regeneration) are produced behind the counters copy, while the host turns the step around
+    mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, words_next, B * W);
+    BGR_LAUNCH_CHECK();
+    pl->words_ahead = true;
+    pl->words_cur ^= 1;
     pl->pending_n = N;
     return BGR_OK;
 }
@@ -638,7 +685,7 @@ static int step_finish(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
     const int64_t N = pl->pending_n;
     long long* hc = (long long*)pl->host_counters.p;
-    BGR_CUDA(cudaStreamSynchronize(pl->stream));
+    BGR_CUDA(cudaEventSynchronize(pl->ev_step));   // the counters are home; the next step's words may still be in flight
     const int acc = (int)hc[0];
     pl->unique_hint = hc[10] + n_fixed;
     const bool goal = hc[1] >= 0;

@@ -97,6 +97,36 @@ def test_knn_clustered_and_outside_queries(bgr, oracle):
         _check(bgr, oracle, pts, q, 16, method)
 
 
+@pytest.mark.parametrize("flags", [0, 1, 2, 3])
+def test_knn_piled_up_nodes(bgr, oracle, flags):
+    """a planner tree holds thousands of coincident copies of a reached milestone: the queries whose
+    ring-1 block is such a pile go through grid_knn_heavy_kernel (one CTA per query over the raw
+    store).  Rows must equal the oracle's, with and without self matches (every copy is a self
+    match of a query at the pile), sorted or not, for queries at, next to and far from the piles,
+    and when more queries are heavy than the heavy list holds (the rest take the ring search)."""
+    rng = np.random.default_rng(11)
+    base = rng.uniform(0, 12.8, (60000, 3)).astype(np.float32)
+    piles = np.array([[3.0, 3.0, 3.0], [9.5, 2.25, 7.0], [6.4, 6.4, 6.4]], np.float32)
+    pts = np.concatenate([base, np.repeat(piles[:1], 30000, 0), np.repeat(piles[1:2], 9000, 0),
+                          np.repeat(piles[2:], 5000, 0)])
+    pts = pts[rng.permutation(len(pts))]
+    near = (piles[rng.integers(0, 3, 400)] + rng.normal(0, 0.05, (400, 3))).astype(np.float32)
+    q = np.concatenate([piles, np.repeat(piles, 4, 0), near, rng.uniform(0, 12.8, (300, 3)).astype(np.float32)])
+    for method in (2, 3):
+        _check(bgr, oracle, pts, q, 16, method, flags=flags)
+    # appended tail on top of the piled index, k = 32, a radius limit
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(2)
+    nns.knn(q[:8], 4)
+    extra = np.concatenate([np.repeat(piles[:1], 500, 0), rng.uniform(0, 12.8, (700, 3)).astype(np.float32)])
+    nns.append(extra)
+    allp = np.concatenate([pts, extra])
+    idx, d2, _ = nns.knn(q, 32, 0.0, flags, 0.3)
+    oi, od = oracle.knn_brute(allp, q, 32, flags, 0.3)
+    assert np.array_equal(d2.view(np.uint32), od.view(np.uint32)) and np.array_equal(idx, oi)
+    nns.close()
+
+
 def test_knn_errors_like_libnabo(bgr, oracle):
     pts = oracle.points(2, 10, 1.0)
     nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
