@@ -124,6 +124,13 @@ def test_knn_piled_up_nodes(bgr, oracle, flags):
     idx, d2, _ = nns.knn(q, 32, 0.0, flags, 0.3)
     oi, od = oracle.knn_brute(allp, q, 32, flags, 0.3)
     assert np.array_equal(d2.view(np.uint32), od.view(np.uint32)) and np.array_equal(idx, oi)
+    if flags == 0:
+        # Nearest over the piles: the copies take the coincident-node shortcut (equal Norm: last index wins)
+        for method in (1, 2):
+            nns.set_method(method)
+            ni, nd = nns.nearest(q)
+            ri, rd = oracle.nearest(allp, q)
+            assert np.array_equal(ni, ri) and np.array_equal(nd.view(np.uint32), rd.view(np.uint32))
     nns.close()
 
 
