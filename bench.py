@@ -432,8 +432,13 @@ def planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier)
         zz, yy = np.nonzero(occ3[:, :, x0] == 0)
         ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
     ms = np.asarray(ms, dtype=np.float32)
-    res["config3_bottleneck_256_batch4096"] = grow(256, 5, 3, 5, B.PLAN_MODE_MS, 16, 4096,
-                                                   B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, 200_000, ms, (12.6, 12.6, 12.6))
+    # wall clock of ~860 host-driven steps: sensitive to whatever else the host is doing, so the growth is
+    # repeated (same seed, same tree) and every run is listed; the headline is the fastest
+    runs3 = [grow(256, 5, 3, 5, B.PLAN_MODE_MS, 16, 4096, B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, 200_000, ms, (12.6, 12.6, 12.6))
+             for _ in range(3)]
+    best3 = min(runs3, key=lambda r: r["seconds"])
+    best3["seconds_all_runs"] = [r["seconds"] for r in runs3]
+    res["config3_bottleneck_256_batch4096"] = best3
     # configs[4](i): independent start/goal planning queries on a 256^3 map, each run to the goal
     # (bounded sample: 8 queries per GPU instead of 512; cap 60,000 nodes per query).  The queries
     # are stepped round-robin by bgr_planner_run_many, each on its own stream and map handle, so
