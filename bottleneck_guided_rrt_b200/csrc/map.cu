@@ -148,8 +148,9 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         const double r = radius + kSweepMargin;
         // cells outside [c - r, c + r] are farther than radius + 1e-4: they decide neither hit nor band
         // (the 1e-4 m margin is ~1e9 times the rounding of the cell computation)
-        lo[a] = max(0, (int)floor((c[a] - r - m.origin[a]) * m.inv_res));
-        hi[a] = min(m.dims[a] - 1, (int)floor((c[a] + r - m.origin[a]) * m.inv_res));
+        const double g = (c[a] - m.origin[a]) * m.inv_res, rc = r * m.inv_res;
+        lo[a] = max(0, (int)floor(g - rc));
+        hi[a] = min(m.dims[a] - 1, (int)floor(g + rc));
         empty |= lo[a] > hi[a];
     }
     double d2min = 1e300;
@@ -158,7 +159,7 @@ __global__ void __launch_bounds__(128) collide_spheres_kernel(MapView m, const f
         const int nbr[3] = {(hi[0] >> 2) - bl[0] + 1, (hi[1] >> 2) - bl[1] + 1, (hi[2] >> 2) - bl[2] + 1};
         const int total = nbr[0] * nbr[1] * nbr[2];
         const int n01 = nbr[0] * nbr[1];
-        const float inv0 = 1.f / (float)nbr[0], inv01 = 1.f / (float)n01;   // exact quotients below 2^20 bricks
+        const float inv0 = __frcp_rn((float)nbr[0]), inv01 = __frcp_rn((float)n01);   // exact quotients below 2^20 bricks
         const double half = 0.5 * m.res;
         for (int t0 = 0; t0 < total && !decided; t0 += 32) {
             // ---- one brick per lane: its word masked to the box
