@@ -331,11 +331,23 @@ def run_ours(args):
                 omap.collide_spheres(d_p1, 0.1, hit=d_shit, band=d_sband)
 
             sphere_ms = max_over_ranks(timed_steps(torch, stream, sphere_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
+            # the same call with HOST buffers (pinned), copies inside the timed region
+            shh, sbh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()
+            shn, sbn = shh.numpy(), sbh.numpy()
+
+            def sphere_e2e_step():
+                omap.collide_spheres(p1n, 0.1, hit=shn, band=sbn)
+
+            sphere_e2e_ms = max_over_ranks(timed_steps(torch, stream, sphere_e2e_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
+            assert np.array_equal(shn, d_shit.cpu().numpy()) and np.array_equal(sbn, d_sband.cpu().numpy()), \
+                "sphere checks: host-buffer and device-resident results differ"
             sbytes = 14.0 * N_EDGES + map_bytes
             out["state_checks"] = {
                 "value": world * N_EDGES / (sphere_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_ms,
                 "config": {"workload": "1,000,000 spheres/GPU (r=0.1) vs the configs[2] map", "hit_fraction": float(d_shit.float().mean().item()),
                            "in_band": int(d_sband.sum().item())},
+                "e2e": {"value": world * N_EDGES / (sphere_e2e_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_e2e_ms,
+                        "h2d_bytes_per_step": int(12 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
                 "roofline": {"bound": "hbm", "kernel": "collide_spheres_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
                              "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": sbytes / (sphere_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                              "algorithmic_bytes": sbytes, "peak_src": pk["src"], "traffic": None}}

@@ -1477,7 +1477,7 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
     }
     // large batches: 32 spheres per warp (lane-per-sphere gate, then the warp walks the undecided ones);
     // small ones: a warp per sphere so the walks overlap
-    if (n >= (int64_t)num_sms() * 2048)
+    if (n >= (int64_t)num_sms() * 1024)
         collide_spheres_kernel<32><<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
     else
         collide_spheres_kernel<1><<<(unsigned)div_up(n, 4), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
@@ -1491,12 +1491,45 @@ int bgr_map_collide_spheres(bgr_map* h, const float* c, int64_t n, double radius
     BGR_CHECK(h->p1_dev.reserve(3 * n, h->stream, false));
     BGR_CHECK(h->hit_dev.reserve(n, h->stream, false));
     BGR_CHECK(h->band_dev.reserve(n, h->stream, false));
-    BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, c, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    BGR_CHECK(bgr_map_collide_spheres_dev(h, h->p1_dev.p, n, radius, h->hit_dev.p, band ? h->band_dev.p : nullptr));
-    BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
-    if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    // large batches: cut into chunks so the upload of chunk c+1 and the download of chunk c-1 overlap the
+    // kernel of chunk c (results are per sphere: chunking cannot change them)
+    const int chunks = pipe_disabled() ? 1 : (int)std::min<int64_t>(4, n / 131072);
+    if (chunks <= 1) {
+        BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p, c, (size_t)3 * n * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+        BGR_CHECK(bgr_map_collide_spheres_dev(h, h->p1_dev.p, n, radius, h->hit_dev.p, band ? h->band_dev.p : nullptr));
+        BGR_CUDA(cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+        if (band) BGR_CUDA(cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaStreamSynchronize(h->stream));
+        return BGR_OK;
+    }
+    BGR_CHECK(h->pipe.init());
+    CopyPipe& P = h->pipe;
+    BGR_CUDA(cudaEventRecord(P.ev_start, h->stream));
+    BGR_CUDA(cudaStreamWaitEvent(P.s_in, P.ev_start, 0));
+    BGR_CUDA(cudaStreamWaitEvent(P.s_out, P.ev_start, 0));
+    const int64_t per = round_up(div_up(n, chunks), 128);
+    for (int k = 0; k < chunks; ++k) {
+        const int64_t s0 = (int64_t)k * per, m = std::min<int64_t>(per, n - s0);
+        if (m <= 0) break;
+        BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p + 3 * s0, c + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
+        BGR_CUDA(cudaEventRecord(P.ev_in[k], P.s_in));
+    }
+    int rc = BGR_OK;
+    for (int k = 0; k < chunks && rc == BGR_OK; ++k) {
+        const int64_t s0 = (int64_t)k * per, m = std::min<int64_t>(per, n - s0);
+        if (m <= 0) break;
+        cudaStreamWaitEvent(h->stream, P.ev_in[k], 0);
+        rc = bgr_map_collide_spheres_dev(h, h->p1_dev.p + 3 * s0, m, radius, h->hit_dev.p + s0, band ? h->band_dev.p + s0 : nullptr);
+        if (rc != BGR_OK) break;
+        cudaEventRecord(P.ev_out[k], h->stream);
+        cudaStreamWaitEvent(P.s_out, P.ev_out[k], 0);
+        cudaMemcpyAsync(hit + s0, h->hit_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out);
+        if (band) cudaMemcpyAsync(band + s0, h->band_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out);
+    }
+    cudaStreamSynchronize(P.s_in);
+    cudaStreamSynchronize(P.s_out);
     BGR_CUDA(cudaStreamSynchronize(h->stream));
-    return BGR_OK;
+    return rc;
 }
 
 // fast path needs the swept hull of one slab to fit a kRectMax x kRectMax cell rectangle:

@@ -359,9 +359,11 @@ def test_spheres_full_size_properties(bgr, oracle):
     torch.cuda.synchronize()
     assert np.array_equal(h, h0.cpu().numpy()) and np.array_equal(b, b0.cpu().numpy())
     m.set_gate(True)
-    perm = np.random.default_rng(3).permutation(len(pts))[:200000]
+    perm = np.random.default_rng(3).permutation(len(pts))[:100000]       # small batch: a warp per sphere
     hp, bp = m.collide_spheres(pts[perm], 0.1)
     assert np.array_equal(hp, h[perm]) and np.array_equal(bp, b[perm])
+    hh, bh = m.collide_spheres(pts, 0.1)                                 # host buffers: chunked, copies overlapped
+    assert np.array_equal(hh, h) and np.array_equal(bh, b)
     sub = np.arange(0, 1_000_000, 8000)
     oh, _ = oracle.collide_spheres(boxes, pts[sub], 0.1, mode=1, want_band=False)
     assert not ((oh != h[sub]) & (b[sub] == 0)).any()
