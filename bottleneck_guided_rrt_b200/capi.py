@@ -63,6 +63,7 @@ def lib():
     L.bgr_nns_knn_dev.argtypes = [vp, vp, i64, i32, f32, u32, f32, vp, vp, vp, vp]
     L.bgr_nns_nearest.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
+    L.bgr_nns_debug_stats.argtypes = [vp, vp]
     L.bgr_nns_destroy.argtypes = [vp]
     L.bgr_knn_merge_dev.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
     L.bgr_knn_merge_strided_dev.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, vp]
@@ -260,6 +261,10 @@ class NNSearchF:
                                  _ptr(indices), _ptr(dists2), C.byref(touched)))
         return indices, dists2, touched.value
 
+    def debug_stats(self):
+        """which code paths this handle has run (bgr_nns_debug_stats): test / measurement aid"""
+        return _nns_debug(self._h)
+
     def nearest(self, query, idx=None, dist=None):
         """Batched reference Nearest(): returns (index (Q,) int32, Norm (Q,) float32)."""
         if _is_dev(query):
@@ -277,6 +282,16 @@ class NNSearchF:
         dist = np.empty(nq, dtype=np.float32) if dist is None else dist
         _check(lib().bgr_nns_nearest(self._h, _ptr(q), nq, _ptr(idx), _ptr(dist)))
         return idx, dist
+
+
+_NNS_DEBUG_KEYS = ("index_builds", "grid_knn_launches", "grid_knn_piled_launches", "heavy_queries_last_launch",
+                   "grid_nearest_launches", "scan_nearest_launches", "brute_knn_launches", "nodes_indexed")
+
+
+def _nns_debug(handle):
+    s = np.zeros(8, dtype=np.uint64)
+    _check(lib().bgr_nns_debug_stats(handle, _ptr(s)))
+    return dict(zip(_NNS_DEBUG_KEYS, (int(v) for v in s)))
 
 
 def knn_merge_dev(idx_slabs, d2_slabs, idx_out, d2_out, stream=0):
@@ -593,6 +608,12 @@ class Planner:
         out = np.empty(n.value, dtype=np.int32)
         _check(lib().bgr_planner_get_path(self._h, _ptr(out), C.byref(n)))
         return out
+
+    def nns_debug_stats(self):
+        """code paths the planner's own node store has run (bgr_planner_nns + bgr_nns_debug_stats)"""
+        h = C.c_void_p()
+        _check(lib().bgr_planner_nns(self._h, C.byref(h)))
+        return _nns_debug(h)
 
     def stats(self):
         s = np.zeros(8, dtype=np.int64)

@@ -53,6 +53,18 @@ inline int64_t div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 int num_sms();  // of the current device (cached)
 
+// a handle's memory and kernels live on the device that was current at its creation: calls made with
+// another device current are refused (BGR_ERR_STATE) instead of failing inside a launch
+inline int check_device(int handle_device) {
+    int cur = -1;
+    BGR_CUDA(cudaGetDevice(&cur));
+    if (cur != handle_device) {
+        set_error("handle belongs to CUDA device %d but device %d is current (cudaSetDevice first)", handle_device, cur);
+        return BGR_ERR_STATE;
+    }
+    return BGR_OK;
+}
+
 // Filter image of a node for the brute-force kNN scan (knn_brute.cuh): {-2x,-2y,-2z,|p|^2''},
 // |p|^2'' = f32 sum of squares shrunk by 16 ulp and rounded down — it absorbs the rounding of
 // this sum and of the 3-FMA filter chain so the filter can never reject a true neighbour.

@@ -44,6 +44,9 @@ struct GridIndex {
     DevBuf<int32_t> heavy;        // queries handed to grid_knn_heavy_kernel and its scratch (layout: kHeavyInts)
     double crowd = 0.0;           // sum(cell count^2) / n: the occupancy of the cell an average NODE sits in
                                   // (~kPtsPerCell+1 for a uniform cloud, thousands for a piled-up tree)
+    // which code paths ran (bgr_nns_debug_stats): index builds, grid_knn_kernel<false> / <true> launches,
+    // grid_nearest_kernel launches
+    uint64_t n_builds = 0, n_lean = 0, n_piled = 0, n_grid_nearest = 0;
 };
 
 __device__ __forceinline__ int cell_coord(float v, float mn, float inv_cs, int g) {
@@ -270,6 +273,7 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
     G.crowd = ss / (double)n;
     G.geom = gm;
     G.n_indexed = n;
+    G.n_builds++;
     return BGR_OK;
 }
 
@@ -890,6 +894,7 @@ inline int grid_nearest(GridIndex& G, const float* x, const float* y, const floa
     a.nq_dev = nq_dev; a.nq_base = nq_base;
     grid_nearest_kernel<<<(unsigned)div_up(nq, kGridWarps), kGridWarps * 32, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
+    G.n_grid_nearest++;
     return BGR_OK;
 }
 
@@ -921,6 +926,7 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     if (a.heavy) grid_knn_kernel<true><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     else grid_knn_kernel<false><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
+    if (a.heavy) G.n_piled++; else G.n_lean++;
     if (a.heavy) {
         grid_knn_heavy_kernel<<<dim3(kHeavyCap, kHeavySlices), kHeavyWarps * 32, 0, st>>>(a);
         BGR_LAUNCH_CHECK();

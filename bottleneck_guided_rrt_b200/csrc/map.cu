@@ -1193,7 +1193,10 @@ __global__ void edges_finalize_kernel(const unsigned* __restrict__ gflags, int64
 
 // ====================================================================== host side
 struct bgr_map {
+    int device = 0;                    // device current at creation: every call must run with it current
     cudaStream_t stream = nullptr;
+    void* aux = nullptr;               // scratch of the path post-processing entry points (path.cu), owned by the map
+    void (*aux_free)(void*) = nullptr;
     double res = 0;
     double origin[3] = {0, 0, 0};
     int dims[3] = {0, 0, 0};
@@ -1239,6 +1242,11 @@ struct bgr_map {
 namespace bgr {
 MapView map_view(const bgr_map* h) { return h->view(); }
 cudaStream_t map_stream(const bgr_map* h) { return h->stream; }
+int map_device(const bgr_map* h) { return h->device; }
+void** map_aux(bgr_map* h, void (*free_fn)(void*)) {
+    h->aux_free = free_fn;
+    return &h->aux;
+}
 }  // namespace bgr
 
 namespace {
@@ -1297,6 +1305,7 @@ void keys_of(const std::vector<LeafRec>& recs, std::vector<uint64_t>& keys) {
 int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
     h->dil_cells[0] = h->dil_cells[1] = 0;
     if (recs.empty()) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
     BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
     BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
     raster_kernel<<<(unsigned)div_up((int64_t)recs.size(), 256), 256, 0, h->stream>>>(h->view(), h->recs.p, (int64_t)recs.size(), set);
@@ -1343,7 +1352,10 @@ int bgr_map_create(double res, const double origin[3], const int dims[3], bgr_ma
     *out = nullptr;
     BGR_ARG(res > 0 && origin && dims, "bad map geometry");
     for (int a = 0; a < 3; ++a) BGR_ARG(dims[a] >= 1 && dims[a] <= 4096, "dims[%d]=%d out of range [1,4096]", a, dims[a]);
+    int dev = 0;
+    BGR_CUDA(cudaGetDevice(&dev));
     bgr_map* h = new bgr_map;
+    h->device = dev;
     h->res = res;
     for (int a = 0; a < 3; ++a) { h->origin[a] = origin[a]; h->dims[a] = dims[a]; }
     for (int L = 0; L <= kMaxLevel; ++L) {
@@ -1378,14 +1390,20 @@ int bgr_map_set_boxes(bgr_map* h, const double* boxes, int64_t nb) {
     std::vector<LeafRec> recs;
     int64_t counts[kMaxLevel + 1] = {0};
     BGR_CHECK(boxes_to_recs(h, boxes, nb, recs, counts));
+    std::vector<uint64_t> keys;
+    keys_of(recs, keys);                // de-duplicated: refresh_boxes counts leaves per unique key too
     for (int L = 0; L <= kMaxLevel; ++L) {
         BGR_CUDA(cudaMemsetAsync(h->bits[L].p, 0, (size_t)h->words[L] * 8, h->stream));
-        h->level_count[L] = counts[L];
+        h->level_count[L] = 0;
     }
+    for (uint64_t k : keys) h->level_count[(int)(k >> 48)] += 1;
     refresh_mask(h);
-    keys_of(recs, h->leaf_keys);
+    // the leaf list is trusted by refresh_boxes only once the bitmap really holds it
+    h->keys_valid = false;
+    BGR_CHECK(raster(h, recs, 1));
+    h->leaf_keys.swap(keys);
     h->keys_valid = true;
-    return raster(h, recs, 1);
+    return BGR_OK;
 }
 
 // Map refresh (the octomap server republishes the whole tree; abb_sense.cpp:447-452 resets it
@@ -1410,12 +1428,17 @@ int bgr_map_refresh_boxes(bgr_map* h, const double* boxes, int64_t nb, int64_t* 
     std::vector<LeafRec> add_r(add_k.size()), rem_r(rem_k.size());
     for (size_t i = 0; i < add_k.size(); ++i) add_r[i] = key_leaf(add_k[i]);
     for (size_t i = 0; i < rem_k.size(); ++i) rem_r[i] = key_leaf(rem_k[i]);
-    for (const LeafRec& r : rem_r) h->level_count[r.level] = std::max<int64_t>(0, h->level_count[r.level] - 1);
+    // a failure between the two rasters leaves the bitmap between the two lists: the stored list is
+    // invalid until both succeed, and the next refresh then falls back to a full set_boxes
+    h->keys_valid = false;
     for (const LeafRec& r : add_r) h->level_count[r.level] += 1;
+    refresh_mask(h);                    // a superset of the levels in use while the rasters run
     BGR_CHECK(raster(h, rem_r, 0));     // removals first: a leaf split into children clears, then its children set
     BGR_CHECK(raster(h, add_r, 1));
+    for (const LeafRec& r : rem_r) h->level_count[r.level] = std::max<int64_t>(0, h->level_count[r.level] - 1);
     refresh_mask(h);
     h->leaf_keys.swap(keys);
+    h->keys_valid = true;
     if (n_added) *n_added = (int64_t)add_k.size();
     if (n_removed) *n_removed = (int64_t)rem_k.size();
     return BGR_OK;
@@ -1466,6 +1489,7 @@ int bgr_map_download_bitmap(bgr_map* h, uint64_t* out, int64_t* n_words) {
 int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double radius, uint8_t* d_hit, uint8_t* d_band) {
     BGR_ARG(h != nullptr && n >= 0 && radius >= 0, "bad collide_spheres arguments");
     if (n == 0) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
     LevelGrid dil;
     dil.bits = nullptr;
     for (int a = 0; a < 3; ++a) dil.nb[a] = h->nb[0][a];
@@ -1514,21 +1538,26 @@ int bgr_map_collide_spheres(bgr_map* h, const float* c, int64_t n, double radius
         BGR_CUDA(cudaMemcpyAsync(h->p1_dev.p + 3 * s0, c + 3 * s0, (size_t)3 * m * sizeof(float), cudaMemcpyHostToDevice, P.s_in));
         BGR_CUDA(cudaEventRecord(P.ev_in[k], P.s_in));
     }
-    int rc = BGR_OK;
-    for (int k = 0; k < chunks && rc == BGR_OK; ++k) {
+    // every CUDA return is checked; on a failure the three streams are still drained before returning,
+    // so no copy into the caller's buffers is left in flight
+    auto chunk = [&](int k) -> int {
         const int64_t s0 = (int64_t)k * per, m = std::min<int64_t>(per, n - s0);
-        if (m <= 0) break;
-        cudaStreamWaitEvent(h->stream, P.ev_in[k], 0);
-        rc = bgr_map_collide_spheres_dev(h, h->p1_dev.p + 3 * s0, m, radius, h->hit_dev.p + s0, band ? h->band_dev.p + s0 : nullptr);
-        if (rc != BGR_OK) break;
-        cudaEventRecord(P.ev_out[k], h->stream);
-        cudaStreamWaitEvent(P.s_out, P.ev_out[k], 0);
-        cudaMemcpyAsync(hit + s0, h->hit_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out);
-        if (band) cudaMemcpyAsync(band + s0, h->band_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out);
+        if (m <= 0) return BGR_OK;
+        BGR_CUDA(cudaStreamWaitEvent(h->stream, P.ev_in[k], 0));
+        BGR_CHECK(bgr_map_collide_spheres_dev(h, h->p1_dev.p + 3 * s0, m, radius, h->hit_dev.p + s0, band ? h->band_dev.p + s0 : nullptr));
+        BGR_CUDA(cudaEventRecord(P.ev_out[k], h->stream));
+        BGR_CUDA(cudaStreamWaitEvent(P.s_out, P.ev_out[k], 0));
+        BGR_CUDA(cudaMemcpyAsync(hit + s0, h->hit_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out));
+        if (band) BGR_CUDA(cudaMemcpyAsync(band + s0, h->band_dev.p + s0, (size_t)m, cudaMemcpyDeviceToHost, P.s_out));
+        return BGR_OK;
+    };
+    int rc = BGR_OK;
+    for (int k = 0; k < chunks && rc == BGR_OK; ++k) rc = chunk(k);
+    const cudaError_t e1 = cudaStreamSynchronize(P.s_in), e2 = cudaStreamSynchronize(P.s_out), e3 = cudaStreamSynchronize(h->stream);
+    if (rc == BGR_OK && (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess)) {
+        set_error("collide_spheres: stream synchronisation failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
+        rc = BGR_ERR_CUDA;
     }
-    cudaStreamSynchronize(P.s_in);
-    cudaStreamSynchronize(P.s_out);
-    BGR_CUDA(cudaStreamSynchronize(h->stream));
     return rc;
 }
 
@@ -1545,6 +1574,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
     BGR_ARG(radius + kSweepMargin < 64 * h->res, "radius too large for the sweep (>= 64 cells)");
     BGR_ARG(n < ((int64_t)1 << 31), "too many edges in one call");
     if (n == 0) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
     BGR_CHECK(h->stats.reserve(6, h->stream, false));
     BGR_CHECK(h->eflags.reserve(n, h->stream, false));
     BGR_CHECK(h->qctl.reserve(2, h->stream, false));
@@ -1653,12 +1683,16 @@ int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t 
     const int rc = bgr_map_collide_edges_dev(h, h->p1_dev.p, h->p2_dev.p, n, radius, shape, h->hit_dev.p,
                                              band ? h->band_dev.p : nullptr);
     h->pipe_chunks = 0;
+    cudaError_t ec = cudaSuccess;
     if (rc == BGR_OK) {
-        cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
-        if (band) cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+        ec = cudaMemcpyAsync(hit, h->hit_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+        if (ec == cudaSuccess && band) ec = cudaMemcpyAsync(band, h->band_dev.p, (size_t)n, cudaMemcpyDeviceToHost, h->stream);
     }
-    cudaStreamSynchronize(P.s_in);
-    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    const cudaError_t e1 = cudaStreamSynchronize(P.s_in), e2 = cudaStreamSynchronize(h->stream);
+    if (rc == BGR_OK && (ec != cudaSuccess || e1 != cudaSuccess || e2 != cudaSuccess)) {
+        set_error("collide_edges: copy / synchronisation failed: %s", cudaGetErrorString(ec != cudaSuccess ? ec : (e1 != cudaSuccess ? e1 : e2)));
+        return BGR_ERR_CUDA;
+    }
     return rc;
 }
 
@@ -1713,6 +1747,7 @@ int bgr_map_destroy(bgr_map* h) {
     h->stats.release(); h->eflags.release(); h->qctl.release(); h->queue.release();
     h->dil[0].release(); h->dil[1].release(); h->dil_tmp.release();
     h->pipe.release();
+    if (h->aux && h->aux_free) h->aux_free(h->aux);
     for (int i = 0; i < 5; ++i)
         if (h->tev[i]) cudaEventDestroy(h->tev[i]);
     delete h;

@@ -59,4 +59,7 @@ struct bgr_map;
 namespace bgr {
 MapView map_view(const bgr_map* h);      // map.cu
 cudaStream_t map_stream(const bgr_map* h);
+int map_device(const bgr_map* h);
+// slot for scratch memory another translation unit keeps per map (freed with free_fn by bgr_map_destroy)
+void** map_aux(bgr_map* h, void (*free_fn)(void*));
 }  // namespace bgr

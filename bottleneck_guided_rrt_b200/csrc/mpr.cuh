@@ -209,10 +209,21 @@ __device__ __forceinline__ ShapeObj make_edge_obj(const float p1[3], const float
         const float nrm = __fsqrt_rn(n2);
         const float vx = __fdiv_rn(dx, nrm), vy = __fdiv_rn(dy, nrm), vz = __fdiv_rn(dz, nrm);
         if (vz < -1.f + 1e-5f) {
+            // Eigen takes a JacobiSVD null-space axis here (perpendicular to both vectors, sign
+            // unspecified); the right-handed one, normalize(-vy, vx, 0), reproduces the edge direction
+            // (the shapes are symmetric about their axis).  Exactly antiparallel: (1,0,0).
             const float c2 = fmaxf(vz, -1.f);
             const float w2 = __fmul_rn(__fadd_rn(1.f, c2), 0.5f);
-            qx = __fsqrt_rn(__fsub_rn(1.f, w2));
-            qy = 0.f;
+            const float sv = __fsqrt_rn(__fsub_rn(1.f, w2));
+            const float an2 = __fadd_rn(__fmul_rn(vy, vy), __fmul_rn(vx, vx));
+            float ax = 1.f, ay = 0.f;
+            if (an2 > 0.f) {
+                const float inva = __fdiv_rn(1.f, __fsqrt_rn(an2));
+                ax = __fmul_rn(-vy, inva);
+                ay = __fmul_rn(vx, inva);
+            }
+            qx = __fmul_rn(ax, sv);
+            qy = __fmul_rn(ay, sv);
             qz = 0.f;
             qw = __fsqrt_rn(w2);
         } else {

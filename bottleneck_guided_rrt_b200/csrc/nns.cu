@@ -1,6 +1,7 @@
 // bgr_nns_* — libnabo-shaped nearest-neighbour object over an append-only SoA node store
 // in HBM.  Host side of the C ABI declared in include/bgrrt.h (reference surface:
 // MS:138-154 Nearest, MS:1277-1315 libnabo create/knn/delete).
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <vector>
@@ -29,6 +30,7 @@ struct bgr_nns {
     GridIndex grid;
     CopyPipe pipe;               // side streams of the host-pointer kNN (chunked D2H overlap)
     double tail_work = 0.0;      // pair evaluations spent on the unsorted tail since the last index build
+    uint64_t n_brute = 0, n_scan_nearest = 0;   // knn_brute_kernel / nearest_kernel launches (bgr_nns_debug_stats)
 };
 
 namespace {
@@ -65,6 +67,7 @@ int grow_store(bgr_nns* h, int64_t need) {
 
 int append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
     if (m == 0) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
     BGR_ARG(h->n + m < (int64_t)1 << 31, "node count exceeds int32 index range");
     BGR_CHECK(grow_store(h, h->n + m));
     deinterleave_kernel<<<(unsigned)div_up(m, 256), 256, 0, h->stream>>>(d_pts, m, h->x.p + h->n,
@@ -74,15 +77,17 @@ int append_dev(bgr_nns* h, const float* d_pts, int64_t m) {
     return BGR_OK;
 }
 
+constexpr int kMaxDevices = 64;   // power of two
 constexpr size_t kBruteSmem = (size_t)kStages * kTile * sizeof(float4) + 2 * kStages * sizeof(uint64_t);
 constexpr size_t kNearestSmem = (size_t)kStages * 3 * kTile * sizeof(float) + 2 * kStages * sizeof(uint64_t);
 
 template <int R>
 int launch_brute(bgr_nns* h, BruteArgs a, int chunks) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the opt-in above 48 KB is per device (and run_many's worker threads race here): one flag per device
+    static std::atomic<bool> attr_set[kMaxDevices];
+    if (!attr_set[h->device & (kMaxDevices - 1)].load(std::memory_order_acquire)) {
         BGR_CUDA(cudaFuncSetAttribute(knn_brute_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBruteSmem));
-        attr_set = true;
+        attr_set[h->device & (kMaxDevices - 1)].store(true, std::memory_order_release);
     }
     dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
     knn_brute_kernel<R><<<grid, kBruteThreads, kBruteSmem, h->stream>>>(a);
@@ -92,10 +97,10 @@ int launch_brute(bgr_nns* h, BruteArgs a, int chunks) {
 
 template <int R>
 int launch_nearest(bgr_nns* h, NearestArgs a, int chunks) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<bool> attr_set[kMaxDevices];
+    if (!attr_set[h->device & (kMaxDevices - 1)].load(std::memory_order_acquire)) {
         BGR_CUDA(cudaFuncSetAttribute(nearest_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kNearestSmem));
-        attr_set = true;
+        attr_set[h->device & (kMaxDevices - 1)].store(true, std::memory_order_release);
     }
     dim3 grid((unsigned)div_up(a.nq, (int64_t)kConsumerWarps * R), (unsigned)chunks);
     nearest_kernel<R><<<grid, kBruteThreads, kNearestSmem, h->stream>>>(a);
@@ -146,6 +151,7 @@ int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flag
         case 2: BGR_CHECK(launch_brute<2>(h, a, chunks)); break;
         default: BGR_CHECK(launch_brute<1>(h, a, chunks)); break;
     }
+    h->n_brute++;
     if (chunks > 1) {
         knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
                                                                          nq * k, nq, k, d_idx, d_d2);
@@ -314,6 +320,7 @@ static int knn_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int k, float e
                         float max_radius, const float* d_radii, int32_t* d_idx, float* d_d2,
                         uint64_t* touched, const uint8_t* d_skip) {
     BGR_CHECK(check_knn_args(h, nq, k, eps, flags, max_radius));
+    BGR_CHECK(check_device(h->device));
     if (touched) *touched = 0;
     if (nq == 0) return BGR_OK;
     int method;
@@ -409,6 +416,7 @@ int nearest_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, f
     BGR_ARG(h != nullptr && nq >= 0, "bad nearest arguments");
     BGR_ARG(h->n >= 1, "Nearest on an empty tree");
     if (nq == 0) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
     {
         // large trees: the grid index answers Nearest exactly (grid_nearest_kernel); the plain scan
         // below stays for small trees and for METHOD_BRUTE
@@ -438,6 +446,7 @@ int nearest_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, f
     nearest_reduce_kernel<<<(unsigned)div_up(nq, 256), 256, 0, h->stream>>>(h->part_idx.p, h->part_d2.p, chunks,
                                                                             nq, d_idx, d_dist);
     BGR_LAUNCH_CHECK();
+    h->n_scan_nearest++;
     return BGR_OK;
 }
 
@@ -459,6 +468,19 @@ int bgr_nns_nearest(bgr_nns* h, const float* q, int64_t nq, int32_t* idx, float*
     if (dist)
         BGR_CUDA(cudaMemcpyAsync(dist, h->d2_dev.p, (size_t)nq * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_nns_debug_stats(bgr_nns* h, uint64_t out[8]) {
+    BGR_ARG(h != nullptr && out != nullptr, "bad arguments");
+    out[0] = h->grid.n_builds; out[1] = h->grid.n_lean; out[2] = h->grid.n_piled; out[3] = 0;
+    out[4] = h->grid.n_grid_nearest; out[5] = h->n_scan_nearest; out[6] = h->n_brute; out[7] = (uint64_t)h->grid.n_indexed;
+    if (h->grid.n_piled && h->grid.heavy.p) {
+        int32_t cnt = 0;
+        BGR_CUDA(cudaMemcpyAsync(&cnt, h->grid.heavy.p, sizeof(cnt), cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaStreamSynchronize(h->stream));
+        out[3] = (uint64_t)std::max(0, cnt);
+    }
     return BGR_OK;
 }
 

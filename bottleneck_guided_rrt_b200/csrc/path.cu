@@ -102,7 +102,18 @@ struct Scratch {
     DevBuf<uint8_t> hit, band;
     DevBuf<double> pts, best;
 };
-thread_local Scratch g_scratch;   // handles are single-threaded (bgrrt.h); scratch follows the calling thread
+// the scratch belongs to the map handle (its stream and device), not to the process or the thread
+void free_scratch(void* p) {
+    Scratch* s = static_cast<Scratch*>(p);
+    s->path.release(); s->p1.release(); s->p2.release(); s->hit.release(); s->band.release();
+    s->pts.release(); s->best.release();
+    delete s;
+}
+Scratch& scratch_of(bgr_map* map) {
+    void** slot = map_aux(map, free_scratch);
+    if (!*slot) *slot = new Scratch;
+    return *static_cast<Scratch*>(*slot);
+}
 
 }  // namespace
 
@@ -117,8 +128,9 @@ int bgr_map_prune_path(bgr_map* map, const float* path_3xP, int64_t p, double ra
         return BGR_ERR_UNSUPPORTED;
     }
     BGR_ARG(*n_keep >= p, "keep buffer too small (%lld < %lld)", (long long)*n_keep, (long long)p);
+    BGR_CHECK(check_device(map_device(map)));
     cudaStream_t st = map_stream(map);
-    Scratch& s = g_scratch;
+    Scratch& s = scratch_of(map);
     const int64_t m = p * (p - 1) / 2;
     std::vector<uint8_t> hit((size_t)m), band((size_t)m);
     if (m > 0) {
@@ -206,8 +218,9 @@ int bgr_map_clearance(bgr_map* map, const double* pts_3xM, int64_t m, double rad
     BGR_ARG(map != nullptr && m >= 0 && (m == 0 || (pts_3xM && dist)) && radius >= 0, "bad clearance arguments");
     if (m == 0) return BGR_OK;
     BGR_ARG(m <= (1 << 20), "too many points in one call");
+    BGR_CHECK(check_device(map_device(map)));
     cudaStream_t st = map_stream(map);
-    Scratch& s = g_scratch;
+    Scratch& s = scratch_of(map);
     BGR_CHECK(s.pts.reserve(3 * m, st, false));
     BGR_CHECK(s.best.reserve(m, st, false));
     std::vector<double> init((size_t)m, 1000.0 + radius);            // MS:962 min_dist = 1000

@@ -306,9 +306,13 @@ __global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS
     if (d.have_knn) {
         int32_t pc = -5;
         for (int j = 0; j < d.K; ++j) {
+            // an unfilled slot (fewer than K admissible nodes: the self-match rule drops the copies that
+            // coincide with the candidate) has no cost: plan_cost_kernel left costs[] untouched for it
+            const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
+            if (ind < 0) continue;
             if (edge_check && d.ehit[(size_t)c * K1 + j]) continue;
             const float temp = d.costs[(size_t)c * K1 + j];
-            if (temp < lowest) { pc = d.knn_idx[(size_t)c * d.K + j]; lowest = temp; pslot = j; }
+            if (temp < lowest) { pc = ind; lowest = temp; pslot = j; }
         }
         if (pc > 0) {
             parent_index = pc;

@@ -17,8 +17,14 @@
  * Layout conventions (libnabo's): a point set is dim x N column-major float, i.e.
  * x0,y0,z0,x1,y1,z1,...; knn results are k x Q column-major (query c owns [c*k, c*k+k)).
  * "_dev" variants take DEVICE pointers and are asynchronous on the handle's stream;
- * the others take HOST pointers, copy through pinned staging and return synchronised.
- * Handles are not thread-safe (the reference caller is single-threaded).
+ * the others take HOST pointers, copy with cudaMemcpyAsync straight from / to the caller's
+ * buffers and return synchronised.  Large batches are cut into chunks whose copies overlap
+ * the kernels of their neighbours: that overlap needs page-locked caller buffers
+ * (cudaHostAlloc / cudaHostRegister); pageable buffers give the same results with the
+ * copies serialised by the driver.
+ * Handles are not thread-safe (the reference caller is single-threaded) and belong to the
+ * CUDA device that was current when they were created: calls made with another device
+ * current return BGR_ERR_STATE.
  */
 #ifndef BGRRT_H
 #define BGRRT_H
@@ -105,6 +111,12 @@ int bgr_nns_knn_skip_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, 
 int bgr_nns_nearest(bgr_nns* nns, const float* q_3xQ, int64_t nq, int32_t* idx, float* dist);
 int bgr_nns_nearest_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int32_t* d_idx,
                         float* d_dist);
+/* test / measurement aid — which code paths this handle has run so far: [0] grid index builds,
+ * [1] grid_knn_kernel launches (uniform clouds), [2] launches of its crowded-index instantiation,
+ * [3] queries the LAST crowded launch handed to grid_knn_heavy_kernel (may exceed its 256 slots: the
+ * rest ran the ring search), [4] grid_nearest_kernel launches, [5] nearest_kernel (plain scan)
+ * launches, [6] knn_brute_kernel launches, [7] nodes covered by the current index */
+int bgr_nns_debug_stats(bgr_nns* nns, uint64_t out[8]);
 int bgr_nns_destroy(bgr_nns* nns);
 
 /* Merge G per-shard top-k slabs (each k x Q, ascending, global indices) into one top-k by

@@ -59,6 +59,10 @@ int64_t   orc_nabo_knn(const orc_nabo*, const float* q, int64_t nq, int k, float
 int orc_nearest(const float* V_xyz, int64_t n, const float* q_xyz, int64_t nq,
                 int32_t* out_idx, float* out_dist, int threads);
 float orc_norm(const float* a, const float* b);                /* MS:130-134 */
+/* calls of orc_norm (process-wide) where float(pow(s,0.5)) != float(sqrt(s)): the reference's pow
+ * against the correctly rounded root the CUDA path uses; tests assert it stays 0 */
+long long orc_norm_pow_sqrt_mismatches(void);
+float orc_pow_root(double s);                                  /* float(pow(s, 0.5)), counted as above */
 
 /* steer: MS:1233-1253.  nearest, rnd: 3 floats; out: 3 floats; returns 1 if rnd kept. */
 int orc_steer(const float* nearest, const float* rnd, float eta, float* out);
@@ -115,6 +119,9 @@ typedef struct orc_planner orc_planner;
 orc_planner* orc_planner_create(const orc_plan_params* p, const double* boxes, int64_t nb,
                                 const float* table_xyz, int64_t nt, const float* milestones_xyz, int nm);
 void    orc_planner_destroy(orc_planner*);
+/* collision mode of the planner's state / edge checks: 1 = every leaf box (default), 2 = bucket-grid
+ * broadphase in front of the same MPR (same booleans; edge band flags not computed) */
+void    orc_planner_set_collision_mode(orc_planner*, int mode);
 int     orc_planner_step(orc_planner*, int* n_accepted, int* goal_reached);
 int     orc_planner_run(orc_planner*, int64_t max_nodes, int64_t max_batches);
 int64_t orc_planner_size(const orc_planner*);

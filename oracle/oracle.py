@@ -67,6 +67,8 @@ def lib():
         L.orc_planner_create.restype = vp
         L.orc_planner_create.argtypes = [vp, vp, i64, vp, i64, vp, i32]
         L.orc_planner_destroy.argtypes = [vp]
+        L.orc_planner_set_collision_mode.argtypes = [vp, i32]
+        L.orc_norm_pow_sqrt_mismatches.restype = C.c_longlong
         L.orc_planner_step.argtypes = [vp, vp, vp]
         L.orc_planner_run.argtypes = [vp, i64, i64]
         L.orc_planner_size.restype = i64
@@ -174,6 +176,12 @@ def nearest(V, q, threads=0):
 def norm(a, b):
     a, b = _f32(a), _f32(b)
     return float(lib().orc_norm(_p(a), _p(b)))
+
+
+def pow_sqrt_mismatches():
+    """calls of the oracle's Norm / steer / edge length in this process where float(pow(s, 0.5)) (the
+    reference's form) differed from float(sqrt(s)) (correctly rounded, what the CUDA path computes)"""
+    return int(lib().orc_norm_pow_sqrt_mismatches())
 
 
 def steer(nearest_pt, rnd, eta=0.15):
@@ -285,7 +293,7 @@ class Planner:
     """CPU restatement of the planner loop (oracle/src/planner.cpp).  `params` is any ctypes
     struct with the orc_plan_params layout (the product's PlannerParams has it)."""
 
-    def __init__(self, params, boxes, table, milestones=None):
+    def __init__(self, params, boxes, table, milestones=None, collision_mode=1):
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 6)
         t = _f32(table).reshape(-1, 3)
         m = _f32(milestones).reshape(-1, 3) if milestones is not None else np.zeros((0, 3), np.float32)
@@ -293,6 +301,7 @@ class Planner:
         self._h = lib().orc_planner_create(C.byref(params), _p(b), b.shape[0], _p(t), t.shape[0], _p(m), m.shape[0])
         if not self._h:
             raise ValueError("orc_planner_create failed")
+        lib().orc_planner_set_collision_mode(self._h, int(collision_mode))
 
     def __del__(self):
         if getattr(self, "_h", None):

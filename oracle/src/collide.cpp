@@ -222,23 +222,35 @@ Obj make_sphere(const double c[3], double r) {
 //   tf1.setQuatRotation(Quaternion3f(w,x,y,z)) widened to double  (MS:435)
 // Eigen: v1 = b/sqrt(b.squaredNorm()) (fixed-size-3 redux order x^2+(y^2+z^2)),
 // c = v1.z, axis = (0,0,1) x v1 = (-v1.y, v1.x, 0), s = sqrt((1+c)*2), vec = axis*(1/s),
-// w = s*0.5.  For c < -1+1e-5 Eigen falls back to a JacobiSVD null-space axis; here the
-// deterministic axis (1,0,0) rotated pi (documented divergence, sub-band effect only).
+// w = s*0.5.  For c < -1+1e-5 Eigen falls back to a JacobiSVD null-space axis (a unit vector
+// perpendicular to both; its SIGN is an implementation detail of the SVD, and the wrong sign
+// mirrors the edge about z by up to ~9e-3 rad): here the axis normalize(-vy, vx, 0), which
+// reproduces the edge direction.  The reference's result in this branch is therefore unpinned.
 // p1 == p2: Eigen yields NaN; defined here as identity rotation, lz = 0.
 void edge_frame_f32(const float p1[3], const float p2[3], float c[3], float q[4], float* lz) {
     c[0] = (p1[0] + p2[0]) / 2; c[1] = (p1[1] + p2[1]) / 2; c[2] = (p1[2] + p2[2]) / 2;
     const float dx = p2[0] - p1[0], dy = p2[1] - p1[1], dz = p2[2] - p1[2];
-    *lz = (float)std::pow((std::pow((double)dz, 2) + std::pow((double)dy, 2)) + std::pow((double)dx, 2), 0.5);
+    *lz = orc_pow_root((std::pow((double)dz, 2) + std::pow((double)dy, 2)) + std::pow((double)dx, 2));
     const float n2 = dx * dx + (dy * dy + dz * dz);
     if (!(n2 > 0.f)) { q[0] = q[1] = q[2] = 0.f; q[3] = 1.f; return; }
     const float nrm = std::sqrt(n2);
     const float vx = dx / nrm, vy = dy / nrm, vz = dz / nrm;
     const float cc = vz;
     if (cc < -1.f + 1e-5f) {
+        // rotation axis = the unit vector perpendicular to both, on the right-handed side, so that
+        // the rotated z axis IS the edge direction (the shapes are symmetric about their axis: only
+        // that direction matters); exactly antiparallel: (1,0,0)
         const float c2 = std::max(cc, -1.f);
         const float w2 = (1.f + c2) * 0.5f;
         const float sv = std::sqrt(1.f - w2);
-        q[0] = 1.f * sv; q[1] = 0.f; q[2] = 0.f; q[3] = std::sqrt(w2);
+        const float an2 = vy * vy + vx * vx;
+        float ax = 1.f, ay = 0.f;
+        if (an2 > 0.f) {
+            const float inva = 1.f / std::sqrt(an2);
+            ax = -vy * inva;
+            ay = vx * inva;
+        }
+        q[0] = ax * sv; q[1] = ay * sv; q[2] = 0.f; q[3] = std::sqrt(w2);
         return;
     }
     const float s = std::sqrt((1.f + cc) * 2.f);
@@ -359,37 +371,6 @@ double orc_sep_cyl_box(const float p1[3], const float p2[3], double r, double dr
     return gap_edge_box(f, box_c, box_size);
 }
 
-int orc_collide_spheres(const double* boxes, int64_t nb, const float* centers, int64_t m,
-                        double radius, int mode, double band_tol, uint8_t* hit, uint8_t* band,
-                        int threads) {
-#ifdef _OPENMP
-    if (threads > 0) omp_set_num_threads(threads);
-#endif
-#pragma omp parallel for schedule(dynamic, 8)
-    for (int64_t i = 0; i < m; ++i) {
-        // MS:319-322: Vec3f(point[0],point[1],point[2]) widens the floats; Sphere(0.1)
-        const double c[3] = {(double)centers[3 * i], (double)centers[3 * i + 1], (double)centers[3 * i + 2]};
-        const Obj s = make_sphere(c, radius);
-        bool flag = false;
-        for (int64_t b = 0; b < nb; ++b) {
-            const double* bx = boxes + 6 * b;
-            if (mode == 1) {
-                const double R = radius + bx[3] * 0.8660254037844387 + 1e-3;
-                const double dx = bx[0] - c[0], dy = bx[1] - c[1], dz = bx[2] - c[2];
-                if (dx * dx + dy * dy + dz * dz > R * R) continue;
-            }
-            if (mpr(s, make_box(bx, bx[3]), 1e-6, nullptr)) { flag = true; break; }   // MS:331-340
-        }
-        hit[i] = flag ? 1 : 0;
-        if (band) {
-            double g = INFINITY;
-            for (int64_t b = 0; b < nb; ++b) g = std::min(g, gap_sphere_box(c, radius, boxes + 6 * b, boxes[6 * b + 3]));
-            band[i] = std::fabs(g) <= band_tol ? 1 : 0;
-        }
-    }
-    return 0;
-}
-
 // mode 2 = "library-best" CPU baseline: what a maintainer gets from an FCL
 // broadphase instead of the reference's loop over every leaf — the boxes are bucketed once into a
 // coarse uniform grid (8 finest cells per bucket side, CSR lists, cached per box array); an edge
@@ -444,6 +425,69 @@ void build_buckets(const double* boxes, int64_t nb) {
     for (int64_t b = 0; b < nb; ++b) B.items[(size_t)cur[(size_t)cell_of(boxes + 6 * b)]++] = (int32_t)b;
 }
 }  // namespace
+
+int orc_collide_spheres(const double* boxes, int64_t nb, const float* centers, int64_t m,
+                        double radius, int mode, double band_tol, uint8_t* hit, uint8_t* band,
+                        int threads) {
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#endif
+    if (mode == 2) build_buckets(boxes, nb);
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int64_t i = 0; i < m; ++i) {
+        // MS:319-322: Vec3f(point[0],point[1],point[2]) widens the floats; Sphere(0.1)
+        const double c[3] = {(double)centers[3 * i], (double)centers[3 * i + 1], (double)centers[3 * i + 2]};
+        const Obj s = make_sphere(c, radius);
+        bool flag = false;
+        if (mode == 2) {
+            // bucket-grid broadphase (see build_buckets): the boxes whose centre bucket overlaps the
+            // sphere's AABB grown by the largest box half size, same bounding-sphere cull, same MPR;
+            // conservative, so the boolean equals modes 0 / 1.  The band uses the same candidates (a
+            // box outside them is farther than 1e-3 m from the sphere).
+            const EdgeBuckets& B = g_buckets;
+            double g = INFINITY;
+            int lo[3], hi[3];
+            bool empty = nb == 0;
+            for (int a = 0; a < 3 && !empty; ++a) {
+                const double ext = radius + B.max_half + 1e-3;
+                lo[a] = std::max(0, (int)std::floor((c[a] - ext - B.org[a]) / B.cell));
+                hi[a] = std::min(B.g[a] - 1, (int)std::floor((c[a] + ext - B.org[a]) / B.cell));
+                empty = lo[a] > hi[a];
+            }
+            for (int z = empty ? 1 : lo[2]; !empty && z <= hi[2]; ++z)
+                for (int y = lo[1]; y <= hi[1]; ++y) {
+                    const int64_t row = ((int64_t)z * B.g[1] + y) * B.g[0];
+                    for (int64_t k = B.start[(size_t)(row + lo[0])]; k < B.start[(size_t)(row + hi[0] + 1)]; ++k) {
+                        const double* bx = boxes + 6 * (int64_t)B.items[(size_t)k];
+                        const double R = radius + bx[3] * 0.8660254037844387 + 1e-3;
+                        const double dx = bx[0] - c[0], dy = bx[1] - c[1], dz = bx[2] - c[2];
+                        if (dx * dx + dy * dy + dz * dz > R * R) continue;
+                        if (band) g = std::min(g, gap_sphere_box(c, radius, bx, bx[3]));
+                        if (!flag && mpr(s, make_box(bx, bx[3]), 1e-6, nullptr)) flag = true;
+                    }
+                }
+            hit[i] = flag ? 1 : 0;
+            if (band) band[i] = std::fabs(g) <= band_tol ? 1 : 0;
+            continue;
+        }
+        for (int64_t b = 0; b < nb; ++b) {
+            const double* bx = boxes + 6 * b;
+            if (mode == 1) {
+                const double R = radius + bx[3] * 0.8660254037844387 + 1e-3;
+                const double dx = bx[0] - c[0], dy = bx[1] - c[1], dz = bx[2] - c[2];
+                if (dx * dx + dy * dy + dz * dz > R * R) continue;
+            }
+            if (mpr(s, make_box(bx, bx[3]), 1e-6, nullptr)) { flag = true; break; }   // MS:331-340
+        }
+        hit[i] = flag ? 1 : 0;
+        if (band) {
+            double g = INFINITY;
+            for (int64_t b = 0; b < nb; ++b) g = std::min(g, gap_sphere_box(c, radius, boxes + 6 * b, boxes[6 * b + 3]));
+            band[i] = std::fabs(g) <= band_tol ? 1 : 0;
+        }
+    }
+    return 0;
+}
 
 int orc_collide_edges(const double* boxes, int64_t nb, const float* p1, const float* p2,
                       int64_t m, double radius, int shape, int mode, double band_tol,

@@ -1,7 +1,7 @@
 // ORACLE (test infrastructure).  MT19937 restated from the published mt19937ar
 // algorithm; follows the reference's abb_manipulator/src/mtrand.cpp:12-50 (gen_state, seed,
 // seed(array)) and include/mtrand.h:77-104 (tempering, MTRand [0,1)).
-// Pinned against the reference's own mtrand.cpp through oracle/_ref (tests/test_mt.py).
+// Pinned against the reference's own mtrand.cpp through oracle/_ref (tests/test_oracle.py: test_mt_against_live_reference_build, test_mt_seeds_match_reference_fixture).
 #include "../oracle.h"
 #include <cmath>
 #include <cstdlib>

@@ -26,6 +26,7 @@ struct orc_planner {
     std::vector<int32_t> par;      // V[i][3]
     orc_mt* mt;
     int goal_reached;
+    int collision_mode = 1;        // oracle collision mode of the state / edge checks (orc_planner_set_collision_mode)
     int64_t stats[8];              // batches, candidates, rejected_state, rejected_edge, improved_parent,
                                    // rewired, band_events, goal_candidate
 };
@@ -87,6 +88,12 @@ void orc_planner_destroy(orc_planner* pl) {
     delete pl;
 }
 
+// 1 (default) = loop over every leaf box with a bounding cull, tolerance-band flags from the
+// independent distance; 2 = bucket-grid broadphase in front of the same MPR (same booleans; sphere
+// band flags kept, edge band flags not computed): what makes the 256^3 / batch-4096 shapes of
+// BASELINE configs[3] checkable in seconds.
+void orc_planner_set_collision_mode(orc_planner* pl, int mode) { pl->collision_mode = mode == 2 ? 2 : 1; }
+
 int64_t orc_planner_size(const orc_planner* pl) { return (int64_t)pl->par.size(); }
 
 void orc_planner_get_tree(const orc_planner* pl, float* xyz, int32_t* parent) {
@@ -127,13 +134,27 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
         std::memcpy(&prand[3 * c], src, 3 * sizeof(float));
     }
     // ---- Nearest + steer (against the snapshot)
+    // (the goal / milestone samples of a batch are the same point: their Nearest is computed once)
     std::vector<int32_t> near(B);
-    orc_nearest(pl->xyz.data(), N, prand.data(), B, near.data(), nullptr, 0);
+    {
+        std::vector<float> uq;
+        std::vector<int> uslot(B);
+        int fixed_u[4] = {-1, -1, -1, -1};
+        for (int c = 0; c < B; ++c) {
+            if (slot[c] >= 0 && fixed_u[slot[c]] >= 0) { uslot[c] = fixed_u[slot[c]]; continue; }
+            uslot[c] = (int)(uq.size() / 3);
+            if (slot[c] >= 0) fixed_u[slot[c]] = uslot[c];
+            uq.insert(uq.end(), &prand[3 * c], &prand[3 * c] + 3);
+        }
+        std::vector<int32_t> unear(uq.size() / 3);
+        orc_nearest(pl->xyz.data(), N, uq.data(), (int64_t)unear.size(), unear.data(), nullptr, 0);
+        for (int c = 0; c < B; ++c) near[c] = unear[(size_t)uslot[c]];
+    }
     for (int c = 0; c < B; ++c)
         found[c] = (uint8_t)orc_steer(&pl->xyz[3 * (size_t)near[c]], &prand[3 * c], P.eta, &pnew[3 * c]);
     // ---- isStateValid (true = collision)
     std::vector<uint8_t> hit(B), band(B);
-    orc_collide_spheres(pl->boxes.data(), nb, pnew.data(), B, P.state_radius, 1, 1e-6, hit.data(), band.data(), 0);
+    orc_collide_spheres(pl->boxes.data(), nb, pnew.data(), B, P.state_radius, pl->collision_mode, 1e-6, hit.data(), band.data(), 0);
     for (int c = 0; c < B; ++c) pl->stats[6] += band[c];
     // ORC_PLAN_DEDUP: the goal / milestone samples of one batch are the same point and, against one
     // snapshot, the same candidate: only the first of each is kept, the copies are rejected here
@@ -144,7 +165,21 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
     std::vector<int32_t> knn_idx((size_t)B * K, -1), parent(B);
     std::vector<float> knn_d2((size_t)B * K), cost(B), psi(B);
     const bool have_knn = N > K;                                                    // MS:1273 V.size() > 5 (K = 5)
-    if (have_knn) orc_knn_brute(pl->xyz.data(), N, pnew.data(), B, K, 0, INFINITY, nullptr, knn_idx.data(), knn_d2.data(), 0);
+    if (have_knn) {
+        // rejected candidates never read their rows (MS:1270 precedes MS:1312): search the others only
+        std::vector<float> kq;
+        std::vector<int> kc;
+        for (int c = 0; c < B; ++c)
+            if (!hit[c]) { kq.insert(kq.end(), &pnew[3 * c], &pnew[3 * c] + 3); kc.push_back(c); }
+        const int64_t m = (int64_t)kc.size();
+        std::vector<int32_t> ki((size_t)m * K);
+        std::vector<float> kd((size_t)m * K);
+        if (m) orc_knn_brute(pl->xyz.data(), N, kq.data(), m, K, 0, INFINITY, nullptr, ki.data(), kd.data(), 0);
+        for (int64_t i = 0; i < m; ++i) {
+            std::memcpy(&knn_idx[(size_t)kc[(size_t)i] * K], &ki[(size_t)i * K], (size_t)K * sizeof(int32_t));
+            std::memcpy(&knn_d2[(size_t)kc[(size_t)i] * K], &kd[(size_t)i * K], (size_t)K * sizeof(float));
+        }
+    }
     // candidate edges for the optional edge check: j < K neighbours, j == K the nearest node
     std::vector<uint8_t> ehit((size_t)B * (K + 1), 0);
     if (edge_check) {
@@ -162,7 +197,7 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
         }
         const int64_t m = (int64_t)slot.size();
         std::vector<uint8_t> h(m), bd(m);
-        if (m) orc_collide_edges(pl->boxes.data(), nb, e1.data(), e2.data(), m, P.edge_radius, P.edge_shape, 1, 1e-6, h.data(), bd.data(), 0);
+        if (m) orc_collide_edges(pl->boxes.data(), nb, e1.data(), e2.data(), m, P.edge_radius, P.edge_shape, pl->collision_mode, 1e-6, h.data(), bd.data(), 0);
         for (int64_t i = 0; i < m; ++i) {
             ehit[slot[i]] = h[i];
             pl->stats[6] += bd[i];
@@ -182,6 +217,7 @@ int orc_planner_step(orc_planner* pl, int* n_accepted, int* goal_reached) {
             int32_t pc = -5;                                                         // extend_tree MS:838-853
             for (int d = 0; d < K; ++d) {
                 const int32_t ind = knn_idx[(size_t)c * K + d];
+                if (ind < 0) continue;   // unfilled slot (libnabo's InvalidIndex): the reference would index tree[-1]
                 if (edge_check && ehit[(size_t)c * (K + 1) + d]) continue;
                 const float temp = chain_cost(pl, ind, &pnew[3 * c], &psi_tmp);
                 if (temp < lowest) { pc = ind; lowest = temp; psi_low = psi_tmp; }

@@ -48,19 +48,31 @@ def test_header_is_plain_c(tmp_path):
                            "-c", str(src), "-o", str(tmp_path / "t.o")])
 
 
-def test_nabo_shim_header_compiles(tmp_path):
-    """include/bgrrt/nabo_shim.hpp: the libnabo-shaped C++ class + isStateValid/isLineValid wrappers
-    compile against a minimal matrix type (no Eigen in this image) and link against libbgrrt.so."""
+def _build_and_run_shim(tmp_path):
     import bottleneck_guided_rrt_b200 as B
     src = os.path.join(ROOT, "tests", "cpp", "shim_compile_test.cpp")
     exe = tmp_path / "shim_test"
     subprocess.check_call(["g++", "-std=c++11", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), src,
                            "-o", str(exe), B.library_path(), "-Wl,-rpath," + os.path.dirname(B.library_path())])
-    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    return subprocess.run([str(exe)], capture_output=True, text=True)
+
+
+def test_nabo_shim_header_compiles(tmp_path):
+    """include/bgrrt/nabo_shim.hpp: the libnabo-shaped C++ class + isStateValid/isLineValid wrappers
+    compile against a minimal matrix type (no Eigen in this image) and link against libbgrrt.so."""
+    r = _build_and_run_shim(tmp_path)
     # exit code 0 = ran on a GPU and matched; 3 = no CUDA device: the shim must have thrown loudly
     assert r.returncode in ((0,) if _has_gpu() else (3,)), r.stdout + r.stderr
     if r.returncode == 3:
         assert "libbgrrt" in r.stdout and "CUDA" in r.stdout.upper()
+
+
+@pytest.mark.gpu
+def test_nabo_shim_runs_on_the_gpu(tmp_path):
+    """the same C++ program in the `-m gpu` selection: Nabo::NNSearchF::knn, isStateValid and isLineValid
+    through the header-only shim must run on the device and match its built-in expectations (exit 0)."""
+    r = _build_and_run_shim(tmp_path)
+    assert r.returncode == 0, r.stdout + r.stderr
 
 
 def test_argument_errors_need_no_device(bgr):

@@ -282,3 +282,40 @@ def test_knn_full_size_properties(bgr, oracle):
     di, dd, _ = nns.knn(torch.from_numpy(q).cuda(), k)
     torch.cuda.synchronize()
     assert np.array_equal(di.cpu().numpy(), gi) and np.array_equal(dd.cpu().numpy().view(np.uint32), gd.view(np.uint32))
+
+
+def test_knn_full_size_second_pass_self_match(bgr, oracle):
+    """BASELINE config 2, second pass (libnabo call site MS:1309-1312): queries = the
+    first 65,536 NODES of the 1 M-node tree, once with SORT_RESULTS|ALLOW_SELF_MATCH (every query finds
+    itself first, d2 = 0) and once with flags = 0 (the d2 <= FLT_EPSILON exclusion drops the node itself):
+    every row against the oracle's libnabo kd-tree restatement, a 256-row subsample against the oracle's
+    brute force, grid == ring search == device call."""
+    import torch
+    n, nq, k = 1_000_000, 65_536, 16
+    pts = oracle.points(2, n, 25.6)
+    q = np.ascontiguousarray(pts[:nq])
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    tree = oracle.NaboKDTree(pts)
+    for flags in (bgr.SORT_RESULTS | bgr.ALLOW_SELF_MATCH, 0):
+        nns.set_method(bgr.METHOD_GRID)
+        gi, gd, _ = nns.knn(q, k, optionFlags=flags)
+        assert (np.diff(gd, axis=1) >= 0).all() and (gi >= 0).all()
+        if flags & bgr.ALLOW_SELF_MATCH:
+            assert np.array_equal(gi[:, 0], np.arange(nq, dtype=np.int32)) and (gd[:, 0] == 0).all()
+        else:
+            assert (gi != np.arange(nq, dtype=np.int32)[:, None]).all() and (gd > np.finfo(np.float32).eps).all()
+        nns.set_method(bgr.METHOD_GRID_GENERAL)
+        ri, rd, _ = nns.knn(q, k, optionFlags=flags)
+        assert canon_equal(gi, gd, ri, rd)
+        oi, od = oracle.knn_brute(pts, q[:256], k, flags)
+        assert canon_equal(gi[:256], gd[:256], oi, od)
+        ti, td = tree.knn(q, k, flags=flags)
+        assert np.array_equal(td.view(np.uint32), gd.view(np.uint32))
+        for r in np.nonzero((ti != gi).any(axis=1))[0]:
+            for v in np.unique(gd[r]):
+                sel = gd[r] == v
+                assert set(ti[r][sel]) == set(gi[r][sel]) or sel[-1], "row %d differs beyond tie order" % r
+        nns.set_method(bgr.METHOD_GRID)
+        di, dd, _ = nns.knn(torch.from_numpy(q).cuda(), k, optionFlags=flags)
+        torch.cuda.synchronize()
+        assert np.array_equal(di.cpu().numpy(), gi) and np.array_equal(dd.cpu().numpy().view(np.uint32), gd.view(np.uint32))

@@ -23,17 +23,22 @@ def world(bgr, oracle):
     return m, boxes, table, ms.astype(np.float32)
 
 
-def _compare(bgr, oracle, world, max_nodes, max_batches, **kw):
-    m, boxes, table, ms = world
-    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), **kw)
-    gp = bgr.Planner(P, m, table, ms)
-    op = oracle.Planner(P, boxes, table, ms)
-    g_goal = gp.run(max_nodes, max_batches)
-    o_goal = op.run(max_nodes, max_batches)
+def _first_band_batch(gp, max_nodes, max_batches):
+    """steps a GPU planner and returns the index of the first batch that saw a collision result inside
+    the MPR tolerance band (None: no such batch before the run ended)"""
+    b = 0
+    while b < max_batches and len(gp) < max_nodes:
+        _, goal = gp.step()
+        if gp.stats()["in_band"]:
+            return b
+        if goal:
+            break
+        b += 1
+    return None
+
+
+def _assert_same_tree(gp, op, g_goal, o_goal):
     gs, os_ = gp.stats(), op.stats()
-    if gs["in_band"] or os_["in_band"]:
-        pytest.skip("a collision result fell inside the 1e-6 m MPR tolerance band (%d/%d): trees may "
-                    "legitimately diverge" % (gs["in_band"], os_["in_band"]))
     gx, gpar = gp.tree()
     ox, opar = op.tree()
     assert len(gp) == len(op) and g_goal == o_goal
@@ -48,6 +53,27 @@ def _compare(bgr, oracle, world, max_nodes, max_batches, **kw):
         while cur > 0 and steps < depth_guard:
             cur, steps = int(gpar[cur]), steps + 1
         assert cur == 0 or gpar[cur] == -1
+    return gs
+
+
+def _compare(bgr, oracle, world, max_nodes, max_batches, collision_mode=1, **kw):
+    """GPU planner vs the oracle's.  A collision result inside the 1e-6 m MPR tolerance band may
+    legitimately differ between the two, after which the trees diverge: every batch BEFORE the first
+    such event (found with a scouting run of the GPU planner) is compared, bit for bit."""
+    m, boxes, table, ms = world
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), **kw)
+    first = _first_band_batch(bgr.Planner(P, m, table, ms), max_nodes, max_batches)
+    if first is not None:
+        if first == 0:
+            pytest.skip("the very first batch holds an in-band collision result: nothing to compare")
+        max_batches = first
+    gp = bgr.Planner(P, m, table, ms)
+    op = oracle.Planner(P, boxes, table, ms, collision_mode=collision_mode)
+    g_goal = gp.run(max_nodes, max_batches)
+    o_goal = op.run(max_nodes, max_batches)
+    assert gp.stats()["in_band"] == 0
+    gs = _assert_same_tree(gp, op, g_goal, o_goal)
+    assert oracle.pow_sqrt_mismatches() == 0, "the oracle met a Norm where float(pow(s,0.5)) != float(sqrt(s))"
     return gp, gs
 
 
@@ -153,3 +179,80 @@ def test_run_many_equals_run(bgr, oracle):
         assert one.stats() == many[i].stats()
     with pytest.raises(RuntimeError):
         bgr.Planner.run_many([many[0], many[0]], 10, 1)
+
+
+def test_unfilled_neighbour_slots_are_skipped(bgr, oracle, world):
+    """Every sample is the same point P within eta of the start: from the second batch on the tree is the
+    root plus copies of P, the self-match rule (d2 <= FLT_EPSILON) leaves ONE admissible neighbour and
+    K-1 unfilled slots (index -1).  The parent choice must ignore them (their cost entries are stale or
+    uninitialised): identical to the oracle, and identical between two fresh planners."""
+    m, boxes, _, _ = world
+    P0 = np.array([[0.28, 0.22, 0.2]], dtype=np.float32)
+    ms = np.repeat(P0, 3, axis=0)
+    trees = []
+    for flags in (8, 8 | 3):
+        for rep in range(2):
+            P = bgr.PlannerParams((0.2, 0.2, 0.2), tuple(P0[0]), mode=bgr.PLAN_MODE_MS, k=5, batch=8, flags=flags, seed=17)
+            gp = bgr.Planner(P, m, P0, ms)
+            if rep == 0:
+                # poison the scratch a fresh planner would otherwise find zeroed: a batch on a real tree first
+                warm = bgr.Planner(bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_RS, k=5, batch=8,
+                                                     flags=8, seed=3), m, world[2], world[3])
+                warm.run(200, 40)
+            op = oracle.Planner(P, boxes, P0, ms)
+            gp.run(100, 6)
+            op.run(100, 6)
+            assert gp.stats()["in_band"] == 0
+            _assert_same_tree(gp, op, False, False)
+            trees.append(gp.tree())
+        assert np.array_equal(trees[-1][1], trees[-2][1])
+    x, par = trees[0]
+    assert len(x) == 1 + 6 * 8 and (par[1:] >= 0).all()
+
+
+def test_config3_shape_parity(bgr, oracle):
+    """BASELINE configs[3] shape: 256^3 narrow-passage map, MS sampler with the 3 door-centre
+    milestones, batch 4096, K = 16, edge checks + rewiring (the planner shape bench.py times), grown to
+    ~65 k nodes — where the tree is piled up at the milestones, so grid_knn_kernel<PILED>,
+    grid_knn_heavy_kernel, the tail-work index rebuilds and the distinct-sample Nearest run.  Trees bit
+    for bit against oracle/src/planner.cpp (bucket-grid collision mode: same booleans) on every batch
+    before the first in-band collision event."""
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(256, 5, n_walls=3, wall_thick=4, door_cells=5)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (256,) * 3)
+    m.set_boxes(boxes)
+    ms = []
+    for w in range(3):
+        x0 = (w + 1) * 256 // 4
+        zz, yy = np.nonzero(occ[:, :, x0] == 0)
+        ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
+    ms = np.asarray(ms, dtype=np.float32)
+    table = synth.points(9, 200_000, 12.8)
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (12.6, 12.6, 12.6), mode=bgr.PLAN_MODE_MS, k=16, batch=4096,
+                          flags=bgr.PLAN_EDGE_CHECK | bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL, seed=5489)
+    n_batches = 24
+    scout = bgr.Planner(P, m, table, ms)
+    heavy_max, first = 0, None
+    for b in range(n_batches):
+        scout.step()
+        heavy_max = max(heavy_max, scout.nns_debug_stats()["heavy_queries_last_launch"])
+        if scout.stats()["in_band"]:
+            first = b
+            break
+    dbg = scout.nns_debug_stats()
+    if first is None:
+        # the shape really exercises what it is here for
+        assert len(scout) > 40_000
+        assert dbg["index_builds"] >= 3 and dbg["grid_knn_piled_launches"] > 0 and heavy_max > 0, dbg
+    else:
+        assert first >= 8, "in-band event in batch %d: too early to exercise the crowded-index paths" % first
+        n_batches = first
+    gp = bgr.Planner(P, m, table, ms)
+    op = oracle.Planner(P, boxes, table, ms, collision_mode=2)
+    gp.run(1 << 30, n_batches)
+    op.run(1 << 30, n_batches)
+    assert gp.stats()["in_band"] == 0
+    gs = _assert_same_tree(gp, op, False, False)
+    assert gs["rewired"] > 0 and gs["improved_parent"] > 0 and gs["rejected_state"] > 0
+    assert oracle.pow_sqrt_mismatches() == 0

@@ -128,3 +128,28 @@ def test_dedup_keeps_one_candidate_per_fixed_sample(oracle, bgr):
     pfirst = set(map(tuple, pxyz[psizes[0]:psizes[1]].view(np.uint32).reshape(-1, 3).tolist()))
     assert first == pfirst and sizes[1] < psizes[1]
     assert op.stats()["rejected_state"] > plain.stats()["rejected_state"]
+
+
+def test_collision_mode_2_grows_the_same_tree(oracle, bgr):
+    """the bucket-grid collision mode of the oracle planner (used for the 256^3 / batch-4096 parity run)
+    only changes how the leaf boxes are visited: same booleans, so the same tree and the same counters
+    (edge band flags aside, which mode 2 does not compute)."""
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(64, 1, occupancy=0.03)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    table = synth.points(9, 20000, 3.2)
+    ms = np.array([[1.0, 0.5, 1.5], [2.0, 1.0, 2.0], [2.5, 2.0, 1.0]], np.float32)
+    trees = []
+    for mode in (1, 2):
+        P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_MS, k=8, batch=128,
+                              flags=bgr.PLAN_EDGE_CHECK | bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL, seed=23)
+        op = oracle.Planner(P, boxes, table, ms, collision_mode=mode)
+        op.run(1500, 20)
+        st = op.stats()
+        st.pop("in_band")
+        trees.append((op.tree(), st))
+    (x1, p1), s1 = trees[0]
+    (x2, p2), s2 = trees[1]
+    assert np.array_equal(x1.view(np.uint32), x2.view(np.uint32)) and np.array_equal(p1, p2) and s1 == s2
+    assert s1["rejected_state"] > 0 and s1["improved_parent"] > 0 and len(p1) > 500
+    assert oracle.pow_sqrt_mismatches() == 0
