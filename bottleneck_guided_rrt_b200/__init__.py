@@ -37,4 +37,5 @@ from .capi import (  # noqa: F401
     PLAN_DEDUP,
     PLAN_MODE_RS,
     PLAN_MODE_MS,
+    microbench_l2,
 )

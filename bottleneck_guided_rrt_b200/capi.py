@@ -49,6 +49,7 @@ def lib():
     L.bgr_launch_count.restype = C.c_uint64
     L.bgr_device_count.argtypes = [vp]
     L.bgr_device_info.argtypes = [vp, vp, vp]
+    L.bgr_microbench_l2.argtypes = [i64, i32, i32, vp]
     L.bgr_nns_create.argtypes = [vp, i64, i32, u32, vp]
     L.bgr_nns_create_dev.argtypes = [vp, i64, i32, u32, vp, vp]
     L.bgr_nns_append.argtypes = [vp, vp, i64]
@@ -112,6 +113,15 @@ def lib():
     L.bgr_planner_destroy.argtypes = [vp]
     _LIB = L
     return L
+
+
+def microbench_l2(nbytes, mode, reps=10):
+    """bgr_microbench_l2: measured L2 read bandwidth (GB/s) of the current device"""
+    v = C.c_double(0.0)
+    rc = lib().bgr_microbench_l2(int(nbytes), int(mode), int(reps), C.byref(v))
+    if rc != 0:
+        raise BgrError(rc, lib().bgr_last_error().decode("utf-8", "replace"))
+    return v.value
 
 
 PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP = 1, 2, 4, 8, 16

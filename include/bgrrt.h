@@ -54,6 +54,12 @@ int bgr_device_count(int* count);
 /* SM count, SM clock (kHz), L2 bytes of the current device */
 int bgr_device_info(int* sms, int* sm_clock_khz, int64_t* l2_bytes);
 
+/* measurement aid (no counterpart in the reference): L2 read bandwidth of the current device in GB/s,
+ * best of `reps` launches over a resident buffer of `bytes` (power of two).  mode 0 = coalesced
+ * LDG.128 rows, 1 = random 32-byte sectors (8-byte loads, 32 B counted per load), 2 = random 512-byte
+ * rows (LDG.128 per lane); L1 bypassed.  bench.py uses it as the peak of roofline.l2. */
+int bgr_microbench_l2(int64_t bytes, int mode, int reps, double* gb_per_s);
+
 /* ------------------------------------------------------------------ nearest neighbours */
 typedef struct bgr_nns bgr_nns;
 

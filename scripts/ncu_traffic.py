@@ -35,7 +35,16 @@ def main():
             rd, wr = val(r, "dram__bytes_read.sum"), val(r, "dram__bytes_write.sum")
             if rd is None or wr is None:
                 continue
-            out[name] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr, "l2_bytes": val(r, "lts__t_bytes.sum"),
+            sect = val(r, "lts__t_sectors.sum")
+            sect_rd = val(r, "lts__t_sectors_srcunit_tex_op_read.sum")
+            out[name] = {"dram_bytes": rd + wr, "dram_read": rd, "dram_write": wr,
+                         # L2 traffic of the launch: every sector the L2 slices served (32 B each), the sectors the
+                         # SMs' loads asked for, and the bytes the crossbar delivered to the L1s
+                         "l2_bytes": sect * 32.0 if sect is not None else None,
+                         "l2_read_sectors_from_sm": sect_rd,
+                         "l2_to_sm_read_bytes": val(r, "l1tex__m_xbar2l1tex_read_bytes.sum"),
+                         "l2_hit_rate_pct": val(r, "lts__t_sector_hit_rate.pct"),
+                         "l1_hit_rate_pct": val(r, "l1tex__t_sector_hit_rate.pct"),
                          "duration_us_under_ncu": (val(r, "gpu__time_duration.sum") or 0) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(units[hdr.index("gpu__time_duration.sum")], 1.0),
                          "source": os.path.basename(path), "grid": r[hdr.index("Grid Size")]}
     with open(out_path, "w") as f:

@@ -83,6 +83,9 @@ def test_spheres_match_mpr_oracle(bgr, oracle, max_level):
     diff = hit != ohit
     assert not (diff & (band == 0)).any(), "mismatch outside the tolerance band: %d" % int((diff & (band == 0)).sum())
     assert np.array_equal(band, oband)
+    # the sphere path is a closed-form distance, not FCL's MPR: inside the band (|gap| <= 1e-6) the two
+    # may answer differently; counted and reported, never silently dropped
+    print("spheres: %d in band, %d of them answered differently from the MPR restatement" % (int(band.sum()), int((diff & (band != 0)).sum())))
     assert 0.2 < hit.mean() < 0.98
 
 
@@ -132,6 +135,12 @@ def test_edges_match_mpr_oracle(bgr, oracle, shape, max_level):
     assert not (diff & (band == 0)).any(), "mismatch outside the band: %s" % np.nonzero(diff & (band == 0))[0][:10]
     assert not ((oband == 1) & (band == 0)).any(), "oracle-band contact not flagged"
     assert diff.sum() <= band.sum()
+    # the band flag must not hide a real divergence: the device narrow phase is libccd's MPR in the
+    # oracle's operation order (no FMA contraction), so flagged pairs agree as well unless the
+    # iteration cap fired (none here)
+    masked = int((diff & (band != 0)).sum())
+    print("edges shape %d: %d in band, %d oracle-band, %d mismatches masked by the band flag" % (shape, int(band.sum()), int(oband.sum()), masked))
+    assert masked == 0, "in-band mismatches: %s" % np.nonzero(diff & (band != 0))[0][:10]
     assert 0.1 < hit.mean() < 0.95
 
 
@@ -334,6 +343,7 @@ def test_edges_full_size_properties(bgr, oracle):
     bad = (oh != h) & (b == 0)
     assert not bad.any(), np.nonzero(bad)[0][:10]
     assert (oh != h).sum() <= b.sum()
+    assert int(((oh != h) & (b != 0)).sum()) == 0, "in-band mismatches hidden by the band flag"
     sub = np.arange(0, 1_000_000, 10000)
     ol, _ = oracle.collide_edges(boxes, p1[sub], p2[sub], 0.03, 0, mode=1, want_band=False)
     assert np.array_equal(ol, oh[sub])
