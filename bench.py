@@ -43,17 +43,38 @@ def peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "src": "fallback"}
 
 
-def ncu_traffic(kernel):
-    """per-launch dram__bytes_read.sum + dram__bytes_write.sum of `kernel` from the committed
-    `ncu --set full` capture of this workload (profiles/traffic.json, written by
-    scripts/ncu_traffic.py from the .ncu-rep), or None."""
+def ncu_entry(kernel):
+    """the entry of `kernel` in profiles/traffic.json (written by scripts/ncu_traffic.py from the committed
+    `ncu --set full` capture of this workload): per-launch DRAM and L2 traffic, or {}."""
     p = os.path.join(ROOT, "profiles", "traffic.json")
     if not os.path.exists(p):
-        return None
+        return {}
     with open(p) as f:
-        d = json.load(f)
-    e = d.get(kernel)
+        return json.load(f).get(kernel) or {}
+
+
+def ncu_traffic(kernel):
+    """per-launch dram__bytes_read.sum + dram__bytes_write.sum of `kernel`, or None"""
+    e = ncu_entry(kernel)
     return float(e["dram_bytes"]) if e else None
+
+
+def l2_roofline(kernel, kernel_ms, peak_gbs, peak_what):
+    """L2 roofline of an L2-resident kernel: bytes the L2 delivered to the SMs in one launch (ncu capture of
+    this workload, profiles/traffic.json) / the launch duration measured live / the L2 read bandwidth measured
+    live on this box with the access shape the kernel uses (bgr_microbench_l2)."""
+    e = ncu_entry(kernel)
+    b = e.get("l2_to_sm_read_bytes")
+    out = {"peak": peak_gbs, "unit": "GB/s", "peak_src": "bgr_microbench_l2 on this box, this run: " + peak_what,
+           "l2_to_sm_read_bytes_per_launch": b, "l2_sector_bytes_per_launch": e.get("l2_bytes"),
+           "bytes_src": "profiles/traffic.json (%s)" % e.get("source") if e else None,
+           "l2_hit_rate_pct": e.get("l2_hit_rate_pct"), "l1_hit_rate_pct": e.get("l1_hit_rate_pct")}
+    if b and kernel_ms > 0:
+        out["achieved"] = b / (kernel_ms * 1e-3) / 1e9
+        out["frac"] = out["achieved"] / peak_gbs if peak_gbs else None
+    else:
+        out["achieved"] = out["frac"] = None
+    return out
 
 
 class ClockSampler:
@@ -110,11 +131,15 @@ def dist_env():
 
 
 # ------------------------------------------------------------------------------ GPU arm
-def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s=0.25, prewarm_iters=None):
+def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s=0.25, prewarm_iters=None, run_ahead=True):
     """W warm-up steps, then exactly K timed steps; each step has its own CUDA event pair on
     `stream` and L2 is flushed (untimed) between steps.  Returns total ms of the K steps.
     A step that contains a collective must pass prewarm_iters: a wall-clock-bounded ramp would
-    run a different number of collectives on each rank (deadlock)."""
+    run a different number of collectives on each rank (deadlock).
+    run_ahead: the K (flush, event, step, event) groups are all enqueued behind a ~1.5 ms spin kernel, so
+    the host is done launching before the first timed kernel runs and no host launch gap (several ranks
+    share the box's cores under torchrun) can sit inside an event pair; steps that synchronise inside
+    (host-pointer calls) gain nothing from it."""
     if prewarm_iters is not None:
         for _ in range(prewarm_iters):
             step_fn()
@@ -131,6 +156,9 @@ def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s
     stream.synchronize()
     barrier()
     torch.cuda.synchronize()
+    if run_ahead:
+        with torch.cuda.stream(stream):
+            torch.cuda._sleep(3_000_000)
     for a, b in evs:
         flush()
         a.record(stream)
@@ -141,11 +169,28 @@ def timed_steps(torch, stream, step_fn, steps, warmup, flush, barrier, prewarm_s
     return sum(a.elapsed_time(b) for a, b in evs)
 
 
+def copy_only_ms(torch, stream, pairs, reps, barrier):
+    """average ms of the given (dst, src) tensor copies alone, issued together on `stream` (events on it);
+    all ranks start behind the same barrier, so at N > 1 the figure is the copy rate with every GPU's
+    copies in flight at once"""
+    for d, s_ in pairs:
+        d.copy_(s_, non_blocking=True)
+    stream.synchronize()
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(reps):
+        for d, s_ in pairs:
+            d.copy_(s_, non_blocking=True)
+    b.record(stream)
+    stream.synchronize()
+    return a.elapsed_time(b) / reps
+
+
 def run_ours(args):
     import torch
     import bottleneck_guided_rrt_b200 as B
     from bottleneck_guided_rrt_b200 import synth
-    from bottleneck_guided_rrt_b200.dist import ShardedNNSearch, shard_range
 
     rank, world, local = dist_env()
     assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
@@ -176,239 +221,352 @@ def run_ours(args):
             flush_buf.fill_(rank & 0xFF)
 
     out = {"metric": METRIC, "unit": "queries/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "parity_note": "oracle parity is UNPINNED against the real libnabo / FCL / octomap (absent offline); see DESIGN.md section 0"}
     sampler = ClockSampler(local)
+    ctx = dict(torch=torch, B=B, synth=synth, L=L, pk=pk, dev=dev, stream=stream, flush=flush, barrier=barrier,
+               max_over_ranks=max_over_ranks, rank=rank, world=world, dist=dist, args=args)
 
     with torch.cuda.stream(stream):
-        # ---------------------------------------------------------------- kNN (configs[1])
-        pts = synth.points(2, N_NODES, 25.6)
-        q_host = synth.points(3 + rank, N_QUERIES, 25.6)
-        d_pts = torch.from_numpy(pts).to(dev)
-        nns = B.NNSearchF.createKDTreeLinearHeap(d_pts, creationOptionFlags=B.TOUCH_STATISTICS,
-                                                 stream=stream.cuda_stream)
-        nns.set_method(B.METHOD_GRID if args.method == "grid" else B.METHOD_BRUTE if args.method == "brute" else B.METHOD_AUTO)
-        t0 = time.perf_counter()
-        nns.build_index()
-        stream.synchronize()
-        build_ms = (time.perf_counter() - t0) * 1e3
-        d_q = torch.from_numpy(q_host).to(dev)
-        d_idx = torch.empty((N_QUERIES, K_NN), dtype=torch.int32, device=dev)
-        d_d2 = torch.empty((N_QUERIES, K_NN), dtype=torch.float32, device=dev)
-        _, _, pairs = nns.knn(d_q, K_NN, indices=d_idx, dists2=d_d2)      # counts evaluated pairs
-        stream.synchronize()
-        nns_t = B.NNSearchF.createKDTreeLinearHeap(d_pts, stream=stream.cuda_stream)  # timed handle: no statistics
-        nns_t.set_method(B.METHOD_GRID if args.method == "grid" else B.METHOD_BRUTE if args.method == "brute" else B.METHOD_AUTO)
-        nns_t.build_index()
-
-        def knn_step():
-            nns_t.knn(d_q, K_NN, indices=d_idx, dists2=d_d2)
-
+        # on-box L2 read bandwidth for the access shapes of the three L2-resident kernels (roofline.l2 peaks)
+        l2_peak = {"rows_16MiB": B.microbench_l2(16 << 20, 2), "sectors_32MiB": B.microbench_l2(32 << 20, 1),
+                   "stream_16MiB": B.microbench_l2(16 << 20, 0)}
+        ctx["l2_peak"] = l2_peak
+        out["l2_microbench_gbs"] = dict(l2_peak, note="bgr_microbench_l2 (scripts/micro/l2_read_bench.cu): L1 bypassed; rows = random "
+                                        "512 B rows with LDG.128, sectors = random 32 B sectors with 8 B loads (32 B counted per load), "
+                                        "stream = consecutive rows; resident buffers")
         sampler.start()
-        l0 = L.bgr_launch_count()
-        knn_ms = max_over_ranks(timed_steps(torch, stream, knn_step, args.steps, args.warmup, flush, barrier))
-        del l0
-        # launches per step, counted on one isolated step
-        l1 = L.bgr_launch_count()
-        knn_step()
-        stream.synchronize()
-        per_step_launches = L.bgr_launch_count() - l1
-
-        # e2e: host (pinned) buffers through the host-pointer C ABI, H2D + D2H inside the timing
-        qh = torch.from_numpy(q_host).pin_memory()
-        ih = torch.empty((N_QUERIES, K_NN), dtype=torch.int32).pin_memory()
-        dh = torch.empty((N_QUERIES, K_NN), dtype=torch.float32).pin_memory()
-        qh_np, ih_np, dh_np = qh.numpy(), ih.numpy(), dh.numpy()
-
-        def knn_e2e_step():
-            nns_t.knn(qh_np, K_NN, indices=ih_np, dists2=dh_np)
-
-        e2e_ms = max_over_ranks(timed_steps(torch, stream, knn_e2e_step, args.steps, args.warmup, flush, barrier, 0.1))
-        clocks = sampler.stop()
-        assert np.array_equal(ih_np, d_idx.cpu().numpy()), "e2e and device-resident results differ"
-
-        ms_per_step = knn_ms / args.steps
-        value = world * N_QUERIES / (ms_per_step * 1e-3)
-        pairs_per_step = float(pairs)
-        sm_mhz = clocks["sm_mhz"] or pk["sm_max_mhz"]
-        fp32_peak = 148 * FP32_NOFMA_LANES * pk["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s, non-FMA
-        achieved = 8.0 * pairs_per_step / (ms_per_step * 1e-3) / 1e12
-        alg_bytes = 16.0 * N_NODES + 12.0 * N_QUERIES + 8.0 * K_NN * N_QUERIES
-        out.update({
-            "value": value, "ms_per_step": ms_per_step,
-            "config": {"workload": "configs[1]: batched kNN, 1,000,000-node 3-D tree (U[0,25.6)^3, MT19937 seed 2), "
-                                   "65,536 queries/GPU (seed 3+rank), k=16, eps=0, exact, method=%s" % args.method,
-                       "nodes": N_NODES, "queries_per_gpu": N_QUERIES, "k": K_NN,
-                       "l2": "flushed between steps (256 MiB fill on the same stream, untimed)",
-                       "prewarm": "0.25 s untimed clock ramp before the W warm-up steps",
-                       "index_build_ms": build_ms, "parallelism": "replicas x%d" % world},
-            "e2e": {"value": world * N_QUERIES / (e2e_ms / args.steps * 1e-3), "unit": "queries/s",
-                    "ms_per_step": e2e_ms / args.steps,
-                    "h2d_bytes_per_step": int(12 * N_QUERIES), "d2h_bytes_per_step": int(8 * K_NN * N_QUERIES)},
-            "gpu_launches": int(per_step_launches * args.steps),
-            "clocks": clocks,
-            # top-level figures: HBM roofline of the kernel (the contract's "hbm" bound: algorithmic bytes of
-            # SURVEY 8(d) / measured launch time / measured HBM peak).  The node index is L2 resident and the
-            # kernel is bound by the FP32 / issue pipes, not HBM: that (non-tensor) roofline is in "fp32".
-            "roofline": {"bound": "hbm", "kernel": "grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel<8>",
-                         "achieved": alg_bytes / (ms_per_step * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                         "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / pk["hbm_gbs"], "peak_src": pk["src"],
-                         "algorithmic_bytes": alg_bytes,
-                         "traffic": ncu_traffic("grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel"),
-                         "fp32": {"achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                                  "peak_src": "148 SM x 128 FP32 lanes x %s sm_max_mhz (non-FMA: the bit-exact contract "
-                                              "forbids FMA)" % pk["src"],
-                                  "pairs_evaluated_per_step": pairs_per_step, "flops_per_pair": 8, "sm_mhz_during_run": sm_mhz},
-                         "note": "node index L2 resident (DRAM traffic per L2-flushed launch = the index read once); the "
-                                 "kernel is issue / dependent-load bound (ncu: profiles/), see DESIGN.md 3.2"},
-        })
-
-        # ---------------------------------------------------------------- edges (configs[2])
+        pts, q_host = knn_section(ctx, out)
+        out["clocks"] = sampler.stop()
+        boxes = p1 = p2 = None
         if not args.skip_edges:
-            occ = synth.make_map(MAP_N, 4, n_walls=8, wall_thick=4, door_cells=5)
-            boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
-            omap = B.OccupancyMap(0.05, (0, 0, 0), (MAP_N,) * 3, stream=stream.cuda_stream)
-            omap.set_boxes(boxes)
-            p1, p2 = synth.edges(4 + rank, N_EDGES, occ)
-            d_p1, d_p2 = torch.from_numpy(p1).to(dev), torch.from_numpy(p2).to(dev)
-            d_hit = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
-            d_band = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
-
-            def edge_step():
-                omap.collide_edges(d_p1, d_p2, EDGE_R, B.SHAPE_CYLINDER, hit=d_hit, band=d_band)
-
-            l1 = L.bgr_launch_count()
-            edge_step()
-            stream.synchronize()
-            edge_launches = L.bgr_launch_count() - l1
-            stats = omap.last_stats()
-            stats.update(omap.gate_stats())
-            edge_ms = max_over_ranks(timed_steps(torch, stream, edge_step, args.steps, args.warmup, flush, barrier))
-            p1h, p2h = torch.from_numpy(p1).pin_memory(), torch.from_numpy(p2).pin_memory()
-            hh, bh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()
-            p1n, p2n, hn, bn = p1h.numpy(), p2h.numpy(), hh.numpy(), bh.numpy()
-
-            def edge_e2e_step():
-                omap.collide_edges(p1n, p2n, EDGE_R, B.SHAPE_CYLINDER, hit=hn, band=bn)
-
-            edge_e2e_ms = max_over_ranks(timed_steps(torch, stream, edge_e2e_step, args.steps, args.warmup, flush, barrier, 0.1))
-            ems = edge_ms / args.steps
-            map_bytes = (MAP_N ** 3) / 8
-            ebytes = 28.0 * N_EDGES + map_bytes
-            # per-kernel durations: CUDA events recorded by the library between its launches, on its stream
-            omap.set_timing(True)
-            kms = {}
-            for _ in range(args.steps):
-                flush()
-                edge_step()
-                for kname, v in omap.last_kernel_ms().items():
-                    kms[kname] = kms.get(kname, 0.0) + v / args.steps
-            omap.set_timing(False)
-            sweep_ms = kms["edges_sweep_kernel"]
-            out["edge_checks"] = {
-                "value": world * N_EDGES / (ems * 1e-3), "unit": "edge checks/s", "ms_per_step": ems,
-                "config": {"workload": "configs[2]: 1,000,000 cylinder edges/GPU (r=0.03, L log-uniform [0.15,3] m) vs 512^3 "
-                                       "occupancy map @0.05 m, %.1f%% occupied, %d leaf boxes" % (100 * occ.mean(), len(boxes)),
-                           "hit_fraction": float(d_hit.float().mean().item()), "in_band": int(d_band.sum().item()),
-                           "sweep": stats},
-                "e2e": {"value": world * N_EDGES / (edge_e2e_ms / args.steps * 1e-3), "unit": "edge checks/s",
-                        "ms_per_step": edge_e2e_ms / args.steps,
-                        "h2d_bytes_per_step": int(24 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
-                "gpu_launches": int(edge_launches * args.steps),
-                "roofline": {"bound": "hbm", "kernel": "edges_sweep_kernel", "achieved": ebytes / (sweep_ms * 1e-3) / 1e9,
-                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ebytes / (sweep_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
-                             "algorithmic_bytes": ebytes, "peak_src": pk["src"], "traffic": ncu_traffic("edges_sweep_kernel"),
-                             "kernel_ms": kms, "kernel_share_of_step": sweep_ms / max(sum(kms.values()), 1e-9),
-                             "note": "the 16 MiB bitmap is L2 resident: the sweep is bound by instruction issue and L2 latency, "
-                                     "not HBM (ncu: profiles/); the HBM figure is the contract of SURVEY 8(d)",
-                             "work_items_per_s": stats["work_items"] / (sweep_ms * 1e-3)},
-            }
-
-            # sphere state checks (isStateValid MS:310-351) on the same map: the edges' first endpoints
-            d_shit = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
-            d_sband = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
-
-            def sphere_step():
-                omap.collide_spheres(d_p1, 0.1, hit=d_shit, band=d_sband)
-
-            sphere_ms = max_over_ranks(timed_steps(torch, stream, sphere_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
-            # the same call with HOST buffers (pinned), copies inside the timed region
-            shh, sbh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()
-            shn, sbn = shh.numpy(), sbh.numpy()
-
-            def sphere_e2e_step():
-                omap.collide_spheres(p1n, 0.1, hit=shn, band=sbn)
-
-            sphere_e2e_ms = max_over_ranks(timed_steps(torch, stream, sphere_e2e_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
-            assert np.array_equal(shn, d_shit.cpu().numpy()) and np.array_equal(sbn, d_sband.cpu().numpy()), \
-                "sphere checks: host-buffer and device-resident results differ"
-            sbytes = 14.0 * N_EDGES + map_bytes
-            out["state_checks"] = {
-                "value": world * N_EDGES / (sphere_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_ms,
-                "config": {"workload": "1,000,000 spheres/GPU (r=0.1) vs the configs[2] map", "hit_fraction": float(d_shit.float().mean().item()),
-                           "in_band": int(d_sband.sum().item())},
-                "e2e": {"value": world * N_EDGES / (sphere_e2e_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_e2e_ms,
-                        "h2d_bytes_per_step": int(12 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
-                "roofline": {"bound": "hbm", "kernel": "collide_spheres_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
-                             "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": sbytes / (sphere_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
-                             "algorithmic_bytes": sbytes, "peak_src": pk["src"], "traffic": None}}
-
-        # ---------------------------------------------------------------- batched planner (configs[0], configs[3])
+            boxes, p1, p2 = edge_section(ctx, out)
         if not args.skip_planner:
-            out["planner"] = planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier)
-
-        # ---------------------------------------------------------------- sharded kNN (N>1)
-        if world > 1 and not args.skip_sharded:
-            lo, hi = shard_range(SHARD_NODES * world, rank, world)
-            shard = torch.from_numpy(synth.points(5 + 1000 * rank, hi - lo, 102.4)).to(dev)
-            sq = torch.from_numpy(synth.points(6, N_QUERIES, 102.4)).to(dev)
-            sh = {"nodes_total": SHARD_NODES * world, "nodes_per_gpu": SHARD_NODES, "queries": N_QUERIES, "k": K_NN,
-                  "unit": "queries/s"}
-            results = {}
-            for exch in ("nccl", "peer"):
-                try:
-                    snn = ShardedNNSearch(shard, lo, stream=stream.cuda_stream, exchange=exch, max_entries=N_QUERIES * K_NN)
-                    snn.nns.build_index()
-
-                    def shard_step():
-                        snn.knn(sq, K_NN)
-
-                    sh_ms = max_over_ranks(timed_steps(torch, stream, shard_step, args.steps, args.warmup, flush, barrier,
-                                                       prewarm_iters=20))
-                    ri, _ = snn.knn(sq, K_NN)
-                    stream.synchronize()
-                    results[exch] = ri.clone()
-                    sh[exch] = {"value": N_QUERIES / (sh_ms / args.steps * 1e-3), "ms_per_step": sh_ms / args.steps}
-                    if exch == "peer":
-                        sh[exch]["spin_timeouts"] = snn.peer.status(stream.cuda_stream)
-                    del snn
-                except Exception as ex:      # reported, never hidden: the other exchange still stands
-                    sh[exch] = {"error": repr(ex)[:300]}
-            if len(results) == 2:
-                sh["exchanges_identical"] = bool(torch.equal(results["nccl"], results["peer"]))
-            best = max((v for v in (sh.get("peer"), sh.get("nccl")) if v and "value" in v), key=lambda v: v["value"], default=None)
-            if best:
-                sh["value"], sh["ms_per_step"] = best["value"], best["ms_per_step"]
-            sh["exchange"] = {"nccl": "ONE all_gather_into_tensor of the packed (idx,d2) slabs (%d B per rank) + bgr_knn_merge_strided_dev" % (8 * K_NN * N_QUERIES),
-                              "peer": "bgr_peer_merge_dev: one kernel, peer loads of this rank's query slice from all slabs over NVLink, "
-                                      "merge by (d2,index), peer stores of the merged lists (%d B in + out per rank)" % (8 * K_NN * N_QUERIES * (world - 1) // world)}
-            out["sharded_knn"] = sh
+            out["planner"] = planner_bench(ctx)
+        if not args.skip_sharded:
+            out["sharded_knn"] = sharded_section(ctx)
 
     # -------------------------------------------------------------------- CPU baseline (N=1, rank 0)
     if rank == 0 and world == 1 and not args.skip_cpu:
         out["cpu_baseline"] = cpu_knn_baseline(pts, q_host, budget_s=8.0)
         if "edge_checks" in out:
             out["edge_checks"]["cpu_baseline"] = cpu_edge_baseline(boxes, p1, p2, budget_s=10.0)
+        if "planner" in out:
+            out["planner"]["cpu_baseline"] = cpu_planner_baseline(budget_s=12.0)
     if rank == 0:
         print(json.dumps(out))
     if dist is not None:
         dist.destroy_process_group()
 
 
-def planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier):
+def knn_section(c, out):
+    """configs[1]: 1 M-node tree, 65,536 queries, k = 16 (the headline)"""
+    torch, B, synth, L, pk, dev, stream = c["torch"], c["B"], c["synth"], c["L"], c["pk"], c["dev"], c["stream"]
+    args, rank, world, max_over_ranks, barrier, flush = c["args"], c["rank"], c["world"], c["max_over_ranks"], c["barrier"], c["flush"]
+    method = B.METHOD_GRID if args.method == "grid" else B.METHOD_BRUTE if args.method == "brute" else B.METHOD_AUTO
+    pts = synth.points(2, N_NODES, 25.6)
+    q_host = synth.points(3 + rank, N_QUERIES, 25.6)
+    d_pts = torch.from_numpy(pts).to(dev)
+    nns = B.NNSearchF.createKDTreeLinearHeap(d_pts, creationOptionFlags=B.TOUCH_STATISTICS, stream=stream.cuda_stream)
+    nns.set_method(method)
+    t0 = time.perf_counter()
+    nns.build_index()
+    stream.synchronize()
+    build_ms = (time.perf_counter() - t0) * 1e3
+    d_q = torch.from_numpy(q_host).to(dev)
+    d_idx = torch.empty((N_QUERIES, K_NN), dtype=torch.int32, device=dev)
+    d_d2 = torch.empty((N_QUERIES, K_NN), dtype=torch.float32, device=dev)
+    _, _, pairs = nns.knn(d_q, K_NN, indices=d_idx, dists2=d_d2)      # counts evaluated pairs
+    stream.synchronize()
+    nns_t = B.NNSearchF.createKDTreeLinearHeap(d_pts, stream=stream.cuda_stream)  # timed handle: no statistics
+    nns_t.set_method(method)
+    nns_t.build_index()
+
+    def knn_step():
+        nns_t.knn(d_q, K_NN, indices=d_idx, dists2=d_d2)
+
+    knn_ms = max_over_ranks(timed_steps(torch, stream, knn_step, args.steps, args.warmup, flush, barrier))
+    l1 = L.bgr_launch_count()                       # launches per step, counted on one isolated step
+    knn_step()
+    stream.synchronize()
+    per_step_launches = L.bgr_launch_count() - l1
+
+    # e2e: host (pinned) buffers through the host-pointer C ABI, H2D + D2H inside the timing
+    qh = torch.from_numpy(q_host).pin_memory()
+    ih = torch.empty((N_QUERIES, K_NN), dtype=torch.int32).pin_memory()
+    dh = torch.empty((N_QUERIES, K_NN), dtype=torch.float32).pin_memory()
+    qh_np, ih_np, dh_np = qh.numpy(), ih.numpy(), dh.numpy()
+
+    def knn_e2e_step():
+        nns_t.knn(qh_np, K_NN, indices=ih_np, dists2=dh_np)
+
+    def knn_e2e_idx_step():
+        nns_t.knn(qh_np, K_NN, indices=ih_np, want_dists2=False)
+
+    e2e_ms = max_over_ranks(timed_steps(torch, stream, knn_e2e_step, args.steps, args.warmup, flush, barrier, 0.1, run_ahead=False))
+    assert np.array_equal(ih_np, d_idx.cpu().numpy()), "e2e and device-resident results differ"
+    e2e_idx_ms = max_over_ranks(timed_steps(torch, stream, knn_e2e_idx_step, args.steps, args.warmup, flush, barrier, 0.1, run_ahead=False))
+    # the three legs of the e2e step alone (every rank at once): what the host link allows at this N
+    h2d_ms = max_over_ranks(copy_only_ms(torch, stream, [(d_q, qh)], 20, barrier))
+    d2h_ms = max_over_ranks(copy_only_ms(torch, stream, [(ih, d_idx), (dh, d_d2)], 20, barrier))
+
+    ms_per_step = knn_ms / args.steps
+    value = world * N_QUERIES / (ms_per_step * 1e-3)
+    pairs_per_step = float(pairs)
+    fp32_peak = 148 * FP32_NOFMA_LANES * pk["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s, non-FMA
+    achieved = 8.0 * pairs_per_step / (ms_per_step * 1e-3) / 1e12
+    alg_bytes = 12.0 * N_NODES + 12.0 * N_QUERIES + 8.0 * K_NN * N_QUERIES          # SURVEY 8(d)
+    kname = "grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel"
+    d2h_bytes = int(8 * K_NN * N_QUERIES)
+    out.update({
+        "value": value, "ms_per_step": ms_per_step,
+        "config": {"workload": "configs[1]: batched kNN, 1,000,000-node 3-D tree (U[0,25.6)^3, MT19937 seed 2), "
+                               "65,536 queries/GPU (seed 3+rank), k=16, eps=0, exact, method=%s" % args.method,
+                   "nodes": N_NODES, "queries_per_gpu": N_QUERIES, "k": K_NN,
+                   "l2": "flushed between steps (256 MiB fill on the same stream, untimed)",
+                   "prewarm": "0.25 s untimed clock ramp before the W warm-up steps; the K timed steps are enqueued "
+                              "behind a 1.5 ms spin kernel (no host launch gap inside an event pair)",
+                   "index_build_ms": build_ms, "parallelism": "replicas x%d" % world},
+        "e2e": {"value": world * N_QUERIES / (e2e_ms / args.steps * 1e-3), "unit": "queries/s",
+                "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": int(12 * N_QUERIES), "d2h_bytes_per_step": d2h_bytes,
+                "legs_alone_ms": {"h2d": h2d_ms, "kernel": ms_per_step, "d2h": d2h_ms,
+                                  "d2h_gb_per_s_per_gpu": d2h_bytes / (d2h_ms * 1e-3) / 1e9,
+                                  "note": "each leg timed alone with all %d GPUs' copies in flight at once (max over ranks); the "
+                                          "chunked call overlaps kernel and D2H, so its floor is about h2d + d2h" % world},
+                "indices_only": {"value": world * N_QUERIES / (e2e_idx_ms / args.steps * 1e-3), "ms_per_step": e2e_idx_ms / args.steps,
+                                 "d2h_bytes_per_step": d2h_bytes // 2,
+                                 "note": "bgr_nns_knn with d2 = NULL: the reference consumes only the indices (MS:1312-1319)"}},
+        "gpu_launches": int(per_step_launches * args.steps),
+        # top-level figures: HBM roofline of the kernel (the contract's "hbm" bound: algorithmic bytes of
+        # SURVEY 8(d) / measured launch time / measured HBM peak).  The node index is L2 resident and the
+        # kernel is bound by L2 row reads and the issue pipes, not HBM: those rooflines are in "l2" and "fp32".
+        "roofline": {"bound": "hbm", "kernel": kname,
+                     "achieved": alg_bytes / (ms_per_step * 1e-3) / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                     "frac": alg_bytes / (ms_per_step * 1e-3) / 1e9 / pk["hbm_gbs"], "peak_src": pk["src"],
+                     "algorithmic_bytes": alg_bytes, "algorithmic_bytes_def": "12 B/node + 12 B/query + 8 B x k per query (SURVEY 8(d))",
+                     "traffic": ncu_traffic(kname),
+                     "l2": l2_roofline(kname, ms_per_step, c["l2_peak"]["rows_16MiB"], "random 512 B rows, LDG.128, 16 MiB resident buffer"),
+                     "fp32": {"achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
+                              "peak_src": "148 SM x 128 FP32 lanes x %s sm_max_mhz (non-FMA: the bit-exact contract "
+                                          "forbids FMA)" % pk["src"],
+                              "pairs_evaluated_per_step": pairs_per_step, "flops_per_pair": 8},
+                     "note": "node index L2 resident (DRAM traffic per L2-flushed launch = the index read once); the "
+                             "kernel is bound by L2 row reads / dependent loads and instruction issue (ncu: profiles/), see DESIGN.md 3.2"},
+    })
+    return pts, q_host
+
+
+def edge_section(c, out):
+    """configs[2]: 1 M cylinder edges vs the 512^3 map; sphere state checks on the same map"""
+    torch, B, synth, L, pk, dev, stream = c["torch"], c["B"], c["synth"], c["L"], c["pk"], c["dev"], c["stream"]
+    args, rank, world, max_over_ranks, barrier, flush = c["args"], c["rank"], c["world"], c["max_over_ranks"], c["barrier"], c["flush"]
+    occ = synth.make_map(MAP_N, 4, n_walls=8, wall_thick=4, door_cells=5)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    omap = B.OccupancyMap(0.05, (0, 0, 0), (MAP_N,) * 3, stream=stream.cuda_stream)
+    omap.set_boxes(boxes)
+    p1, p2 = synth.edges(4 + rank, N_EDGES, occ)
+    d_p1, d_p2 = torch.from_numpy(p1).to(dev), torch.from_numpy(p2).to(dev)
+    d_hit = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+    d_band = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+
+    def edge_step():
+        omap.collide_edges(d_p1, d_p2, EDGE_R, B.SHAPE_CYLINDER, hit=d_hit, band=d_band)
+
+    l1 = L.bgr_launch_count()
+    edge_step()
+    stream.synchronize()
+    edge_launches = L.bgr_launch_count() - l1
+    stats = omap.last_stats()
+    stats.update(omap.gate_stats())
+    edge_ms = max_over_ranks(timed_steps(torch, stream, edge_step, args.steps, args.warmup, flush, barrier))
+    p1h, p2h = torch.from_numpy(p1).pin_memory(), torch.from_numpy(p2).pin_memory()
+    hh, bh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()
+    p1n, p2n, hn, bn = p1h.numpy(), p2h.numpy(), hh.numpy(), bh.numpy()
+
+    def edge_e2e_step():
+        omap.collide_edges(p1n, p2n, EDGE_R, B.SHAPE_CYLINDER, hit=hn, band=bn)
+
+    edge_e2e_ms = max_over_ranks(timed_steps(torch, stream, edge_e2e_step, args.steps, args.warmup, flush, barrier, 0.1, run_ahead=False))
+    assert np.array_equal(hn, d_hit.cpu().numpy()) and np.array_equal(bn, d_band.cpu().numpy()), \
+        "edge checks: host-buffer and device-resident results differ"
+    ems = edge_ms / args.steps
+    map_bytes = (MAP_N ** 3) / 8
+    ebytes = 28.0 * N_EDGES + map_bytes
+    # per-kernel durations: CUDA events recorded by the library between its launches, on its stream
+    omap.set_timing(True)
+    kms = {}
+    for _ in range(args.steps):
+        flush()
+        edge_step()
+        for kname, v in omap.last_kernel_ms().items():
+            kms[kname] = kms.get(kname, 0.0) + v / args.steps
+    omap.set_timing(False)
+    sweep_ms = kms["edges_sweep_kernel"]
+    out["edge_checks"] = {
+        "value": world * N_EDGES / (ems * 1e-3), "unit": "edge checks/s", "ms_per_step": ems,
+        "config": {"workload": "configs[2]: 1,000,000 cylinder edges/GPU (r=0.03, L log-uniform [0.15,3] m) vs 512^3 "
+                               "occupancy map @0.05 m, %.1f%% occupied, %d leaf boxes" % (100 * occ.mean(), len(boxes)),
+                   "hit_fraction": float(d_hit.float().mean().item()), "in_band": int(d_band.sum().item()),
+                   "sweep": stats},
+        "e2e": {"value": world * N_EDGES / (edge_e2e_ms / args.steps * 1e-3), "unit": "edge checks/s",
+                "ms_per_step": edge_e2e_ms / args.steps,
+                "h2d_bytes_per_step": int(24 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
+        "gpu_launches": int(edge_launches * args.steps),
+        "roofline": {"bound": "hbm", "kernel": "edges_sweep_kernel", "achieved": ebytes / (sweep_ms * 1e-3) / 1e9,
+                     "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ebytes / (sweep_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                     "algorithmic_bytes": ebytes, "algorithmic_bytes_def": "28 B/edge + the 16 MiB bitmap once (SURVEY 8(d))",
+                     "peak_src": pk["src"], "traffic": ncu_traffic("edges_sweep_kernel"),
+                     "l2": l2_roofline("edges_sweep_kernel", sweep_ms, c["l2_peak"]["sectors_32MiB"],
+                                       "random 32 B sectors (one 8 B brick word per load), 32 MiB resident buffer (both maps)"),
+                     "kernel_ms": kms, "kernel_share_of_step": sweep_ms / max(sum(kms.values()), 1e-9),
+                     "note": "both 16 MiB maps are L2 resident: the sweep is bound by instruction issue and the L1/L2 "
+                             "probe rate, not HBM (ncu: profiles/); the HBM figure is the contract of SURVEY 8(d)",
+                     "work_items_per_s": stats["work_items"] / (sweep_ms * 1e-3)},
+    }
+
+    # sphere state checks (isStateValid MS:310-351) on the same map: the edges' first endpoints
+    d_shit = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+    d_sband = torch.empty(N_EDGES, dtype=torch.uint8, device=dev)
+
+    def sphere_step():
+        omap.collide_spheres(d_p1, 0.1, hit=d_shit, band=d_sband)
+
+    sphere_ms = max_over_ranks(timed_steps(torch, stream, sphere_step, args.steps, args.warmup, flush, barrier, 0.1)) / args.steps
+    shh, sbh = torch.empty(N_EDGES, dtype=torch.uint8).pin_memory(), torch.empty(N_EDGES, dtype=torch.uint8).pin_memory()
+    shn, sbn = shh.numpy(), sbh.numpy()
+
+    def sphere_e2e_step():
+        omap.collide_spheres(p1n, 0.1, hit=shn, band=sbn)
+
+    sphere_e2e_ms = max_over_ranks(timed_steps(torch, stream, sphere_e2e_step, args.steps, args.warmup, flush, barrier, 0.1, run_ahead=False)) / args.steps
+    assert np.array_equal(shn, d_shit.cpu().numpy()) and np.array_equal(sbn, d_sband.cpu().numpy()), \
+        "sphere checks: host-buffer and device-resident results differ"
+    sbytes = 14.0 * N_EDGES + map_bytes
+    out["state_checks"] = {
+        "value": world * N_EDGES / (sphere_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_ms,
+        "config": {"workload": "1,000,000 spheres/GPU (r=0.1) vs the configs[2] map", "hit_fraction": float(d_shit.float().mean().item()),
+                   "in_band": int(d_sband.sum().item())},
+        "e2e": {"value": world * N_EDGES / (sphere_e2e_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_e2e_ms,
+                "h2d_bytes_per_step": int(12 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
+        "roofline": {"bound": "hbm", "kernel": "collide_spheres_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
+                     "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": sbytes / (sphere_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                     "algorithmic_bytes": sbytes, "algorithmic_bytes_def": "14 B/sphere + the 16 MiB bitmap once",
+                     "peak_src": pk["src"], "traffic": ncu_traffic("collide_spheres_kernel"),
+                     "l2": l2_roofline("collide_spheres_kernel", sphere_ms, c["l2_peak"]["sectors_32MiB"],
+                                       "random 32 B sectors (one 8 B brick word per load), 32 MiB resident buffer (both maps)")}}
+    return boxes, p1, p2
+
+
+def sharded_section(c):
+    """configs[4](ii): index-range-sharded kNN, 6.25 M nodes per GPU (50 M at N = 8), 65,536 replicated queries,
+    k = 16: local search + ONE exchange (NCCL all-gather + merge kernel | NVLink peer-memory merge kernel).
+    N = 1 runs the one-shard search without an exchange (the base of the weak-scaling curve).  Every rank count
+    checks a 128-query subsample against the oracle's brute force over the same nodes."""
+    torch, B, synth, dev, stream = c["torch"], c["B"], c["synth"], c["dev"], c["stream"]
+    args, rank, world, max_over_ranks, barrier, flush, dist = c["args"], c["rank"], c["world"], c["max_over_ranks"], c["barrier"], c["flush"], c["dist"]
+    from bottleneck_guided_rrt_b200.dist import ShardedNNSearch, shard_range, merge_slabs_host
+    lo, hi = shard_range(SHARD_NODES * world, rank, world)
+    shard_host = synth.points(5 + 1000 * rank, hi - lo, 102.4)
+    shard = torch.from_numpy(shard_host).to(dev)
+    sq_host = synth.points(6, N_QUERIES, 102.4)
+    sq = torch.from_numpy(sq_host).to(dev)
+    sh = {"nodes_total": SHARD_NODES * world, "nodes_per_gpu": SHARD_NODES, "queries": N_QUERIES, "k": K_NN, "unit": "queries/s"}
+    results = {}
+    for exch in (("nccl", "peer") if world > 1 else ("none",)):
+        try:
+            snn = ShardedNNSearch(shard, lo, stream=stream.cuda_stream, exchange=exch, max_entries=N_QUERIES * K_NN)
+            snn.nns.build_index()
+
+            def shard_step():
+                snn.knn(sq, K_NN)
+
+            sh_ms = max_over_ranks(timed_steps(torch, stream, shard_step, args.steps, args.warmup, flush, barrier,
+                                               prewarm_iters=20, run_ahead=False))
+            # local search and exchange + merge apart: events inside the call, same flush discipline
+            loc_ms = exc_ms = 0.0
+            for _ in range(args.steps):
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+                flush()
+                snn.knn(sq, K_NN, events=ev)
+                stream.synchronize()
+                loc_ms += ev[0].elapsed_time(ev[1]) / args.steps
+                exc_ms += ev[1].elapsed_time(ev[2]) / args.steps
+            ri, rd = snn.knn(sq, K_NN)
+            stream.synchronize()
+            results[exch] = (ri.clone(), rd.clone())
+            sh[exch] = {"value": N_QUERIES / (sh_ms / args.steps * 1e-3), "ms_per_step": sh_ms / args.steps,
+                        "local_ms": max_over_ranks(loc_ms), "exchange_ms": max_over_ranks(exc_ms)}
+            if exch == "peer":
+                sh[exch]["spin_timeouts"] = snn.peer.status(stream.cuda_stream)
+            del snn
+        except Exception as ex:      # reported, never hidden: the other exchange still stands
+            sh[exch] = {"error": repr(ex)[:300]}
+    if len(results) == 2:
+        sh["exchanges_identical"] = bool(torch.equal(results["nccl"][0], results["peer"][0]) and
+                                         torch.equal(results["nccl"][1], results["peer"][1]))
+    # parity against the oracle on the real nodes: every rank brute-forces the subsample over ITS shard (global
+    # indices), the per-shard lists are gathered and merged by the numpy statement of the merge rule
+    if not args.skip_cpu and results:
+        from oracle import oracle as O
+        sub = np.arange(0, N_QUERIES, N_QUERIES // 128)[:128]
+        oi, od = O.knn_brute(shard_host, sq_host[sub], K_NN, threads=max(1, host_cores() // world))
+        oi = np.where(oi >= 0, oi + lo, oi).astype(np.int32)
+        if dist is not None:
+            gi = [torch.empty((128, K_NN), dtype=torch.int32, device=dev) for _ in range(world)]
+            gd = [torch.empty((128, K_NN), dtype=torch.float32, device=dev) for _ in range(world)]
+            dist.all_gather(gi, torch.from_numpy(oi).to(dev))
+            dist.all_gather(gd, torch.from_numpy(od).to(dev))
+            mi, md = merge_slabs_host(np.stack([t.cpu().numpy() for t in gi]), np.stack([t.cpu().numpy() for t in gd]))
+        else:
+            mi, md = oi, od
+        par = {"checked": int(len(sub)), "oracle": "oracle.knn_brute over each rank's 6.25 M nodes + numpy merge by (d2, index)"}
+        for exch, (ri, rd) in results.items():
+            gi_, gd_ = ri.cpu().numpy()[sub], rd.cpu().numpy()[sub]
+            bad = int(((gi_ != mi).any(axis=1) | (gd_.view(np.uint32) != md.view(np.uint32)).any(axis=1)).sum())
+            par["mismatches_" + exch] = bad
+        par["mismatches"] = int(max_over_ranks(float(sum(v for k_, v in par.items() if k_.startswith("mismatches_")))))
+        sh["parity"] = par
+    best = max((v for v in (sh.get("peer"), sh.get("nccl"), sh.get("none")) if v and "value" in v), key=lambda v: v["value"], default=None)
+    if best:
+        sh["value"], sh["ms_per_step"] = best["value"], best["ms_per_step"]
+        sh["local_ms"], sh["exchange_ms"] = best["local_ms"], best["exchange_ms"]
+        # the local search is the grid kNN over a 6.25 M-node index (100 MB: L2 resident at the edge); its HBM-contract
+        # roofline on SURVEY 8(d) bytes per GPU
+        alg = 12.0 * SHARD_NODES + 12.0 * N_QUERIES + 8.0 * K_NN * N_QUERIES
+        sh["roofline"] = {"bound": "hbm", "kernel": "grid_knn_kernel (local search)", "achieved": alg / (best["local_ms"] * 1e-3) / 1e9,
+                          "peak": c["pk"]["hbm_gbs"], "unit": "GB/s", "frac": alg / (best["local_ms"] * 1e-3) / 1e9 / c["pk"]["hbm_gbs"],
+                          "algorithmic_bytes": alg, "exchange_bytes_per_rank": int(8 * K_NN * N_QUERIES * (world - 1) // max(world, 1))}
+    sh["exchange"] = {"nccl": "ONE all_gather_into_tensor of the packed (idx,d2) slabs (%d B per rank) + bgr_knn_merge_strided_dev" % (8 * K_NN * N_QUERIES),
+                      "peer": "bgr_peer_merge_dev: one kernel, peer loads of this rank's query slice from all slabs over NVLink, "
+                              "merge by (d2,index), peer stores of the merged lists (%d B in + out per rank)" % (8 * K_NN * N_QUERIES * (world - 1) // world)}
+    return sh
+
+
+def door_milestones(occ, n_map, n_walls=3):
+    """the 3 milestone points = the door centres of the 3 walls (what the CNN is trained to predict)"""
+    ms = []
+    for w in range(n_walls):
+        x0 = (w + 1) * n_map // (n_walls + 1)
+        zz, yy = np.nonzero(occ[:, :, x0] == 0)
+        ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
+    return np.asarray(ms, dtype=np.float32)
+
+
+QUERY_OCCUPANCY = 0.065   # configs[4](i) maps: 3 walls (4.7 % of the cells) with one 0.4 m door each + 1.8 % clutter
+QUERY_DOOR_CELLS = 8      # (see planner_bench for why these differ from the configs[3] map)
+QUERIES_PER_GPU = 512
+QUERY_MAX_NODES = 60_000
+
+
+def planner_bench(c):
     """Tree growth of the batched planner (bgr_planner_*): configs[0] = RRT* with 10 % goal bias on a
     64^3 map to 5,000 nodes, k=10 (batch 1 = the reference's sequential loop, and batch 256);
     configs[3] = bottleneck-guided RRT* (3 milestones) on a 256^3 narrow-passage map to 200,000 nodes,
-    batch 4096, K=16, edge checks + rewiring.  One independent planning query per GPU (replicas)."""
+    batch 4096, K=16, edge checks + rewiring; configs[4](i) = 512 independent start/goal queries per GPU on a
+    256^3 map (one distinct map per GPU), each run to the goal."""
+    torch, B, synth, stream = c["torch"], c["B"], c["synth"], c["stream"]
+    rank, world, max_over_ranks, barrier = c["rank"], c["world"], c["max_over_ranks"], c["barrier"]
     res = {}
 
     def grow(n_map, seed, walls, door, mode, k, batch, flags, max_nodes, milestones, goal):
@@ -436,69 +594,88 @@ def planner_bench(torch, B, synth, stream, rank, world, max_over_ranks, barrier)
     g64 = (3.0, 3.0, 3.0)
     res["config0_rrtstar_64_batch1"] = grow(64, 1, 3, 6, B.PLAN_MODE_RS, 10, 1, B.PLAN_QUIRKS, 5000, None, g64)
     res["config0_rrtstar_64_batch256"] = grow(64, 1, 3, 6, B.PLAN_MODE_RS, 10, 256, 0, 5000, None, g64)
-    # the 3 milestone points = the door centres of the 3 walls (what the CNN is trained to predict)
     occ3 = synth.make_map(256, 5, n_walls=3, wall_thick=4, door_cells=5)
-    ms = []
-    for w in range(3):
-        x0 = (w + 1) * 256 // 4
-        zz, yy = np.nonzero(occ3[:, :, x0] == 0)
-        ms.append([(x0 + 0.5) * 0.05, (yy.mean() + 0.5) * 0.05, (zz.mean() + 0.5) * 0.05])
-    ms = np.asarray(ms, dtype=np.float32)
-    # wall clock of ~860 host-driven steps: sensitive to whatever else the host is doing, so the growth is
+    ms = door_milestones(occ3, 256)
+    # wall clock of ~860 steps: sensitive to whatever else the host is doing, so the growth is
     # repeated (same seed, same tree) and every run is listed; the headline is the fastest
     runs3 = [grow(256, 5, 3, 5, B.PLAN_MODE_MS, 16, 4096, B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, 200_000, ms, (12.6, 12.6, 12.6))
              for _ in range(3)]
     best3 = min(runs3, key=lambda r: r["seconds"])
     best3["seconds_all_runs"] = [r["seconds"] for r in runs3]
     res["config3_bottleneck_256_batch4096"] = best3
-    # configs[4](i): independent start/goal planning queries on a 256^3 map, each run to the goal
-    # (bounded sample: 8 queries per GPU instead of 512; cap 60,000 nodes per query).  The queries
-    # are stepped round-robin by bgr_planner_run_many, each on its own stream and map handle, so
-    # their small per-step kernels overlap; the same queries one after the other are timed beside.
-    boxes3 = synth.grid_to_boxes(occ3, 0.05, (0, 0, 0), 3)
-    nq_local = 8
-    qstreams = [torch.cuda.Stream() for _ in range(nq_local)]
+
+    # configs[4](i): QUERIES_PER_GPU independent start/goal planning queries per GPU, each run to the goal (or to
+    # QUERY_MAX_NODES nodes), on one 256^3 map per GPU (map seed 5 + rank: 8 distinct maps at N = 8).
+    # Measured on this planner (scripts/try_queries2.py, 32 random start/goal pairs, profiles/r2_queries_*.txt):
+    #   * the configs[3] map (0.25 m doors, 10 % clutter): 9 of 32 reach the goal.  Two causes: with 10 % clutter the
+    #     free space of a 0.1 m sphere is ~30 % of the volume, at the percolation threshold, so many pairs are not
+    #     connected at all; and a 0.25 m door leaves the 0.1 m sphere a +-0.025 m corridor, which a point-validity
+    #     RRT with 0.15 m steps (the reference's extension rule) enters only from a ~6 degree cone in front of it;
+    #   * 0.4 m doors, 1.8 % clutter, no BGR_PLAN_DEDUP: 6 of 32 — every batch appends hundreds of copies of the goal /
+    #     milestone candidates (the reference's sequential loop piles them up too) and the node budget is spent on piles;
+    #   * the same with BGR_PLAN_DEDUP: 29-30 of 32.
+    # So the queries run on 0.4 m doors / 1.8 % clutter with BGR_PLAN_DEDUP on.
+    occq = synth.make_map(256, 5 + rank, n_walls=3, wall_thick=4, door_cells=QUERY_DOOR_CELLS, occupancy=QUERY_OCCUPANCY)
+    msq = door_milestones(occq, 256)
+    boxesq = synth.grid_to_boxes(occq, 0.05, (0, 0, 0), 3)
+    nconc = 16
+    qstreams = [torch.cuda.Stream() for _ in range(nconc)]
     qmaps = []
     for qs in qstreams:
         qm = B.OccupancyMap(0.05, (0, 0, 0), (256,) * 3, stream=qs.cuda_stream)
-        qm.set_boxes(boxes3)
+        qm.set_boxes(boxesq)
         qmaps.append(qm)
-    cand = synth.points(77 + rank, 4000, 12.8)
+    cand = synth.points(77 + rank, 4 * QUERIES_PER_GPU + 2000, 12.8)
     chit, _ = qmaps[0].collide_spheres(cand, 0.1)
     free = cand[np.asarray(chit) == 0]
+    assert len(free) >= 2 * QUERIES_PER_GPU
     table = synth.points(9 + rank, 200_000, 12.8)
 
-    def make_queries():
-        out = []
-        for qi in range(nq_local):
-            P = B.PlannerParams(tuple(free[2 * qi]), tuple(free[2 * qi + 1]), mode=B.PLAN_MODE_MS, k=16, batch=1024,
-                                flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE, seed=100 + rank * 512 + qi)
-            out.append(B.Planner(P, qmaps[qi], table, ms, stream=qstreams[qi].cuda_stream))
-        return out
+    def run_queries(q0, q1, seq=False):
+        """queries [q0, q1) in groups of nconc through bgr_planner_run_many (or one after the other)"""
+        reached, nodes = [], []
+        for g0 in range(q0, q1, nconc):
+            pls = []
+            for j, qi in enumerate(range(g0, min(q1, g0 + nconc))):
+                P = B.PlannerParams(tuple(free[2 * qi]), tuple(free[2 * qi + 1]), mode=B.PLAN_MODE_MS, k=16, batch=1024,
+                                    flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | B.PLAN_DEDUP, seed=100 + rank * QUERIES_PER_GPU + qi)
+                pls.append(B.Planner(P, qmaps[j], table, msq, stream=qstreams[j].cuda_stream))
+            if seq:
+                fl = [p.run(QUERY_MAX_NODES) for p in pls]
+            else:
+                fl = B.Planner.run_many(pls, QUERY_MAX_NODES)
+            torch.cuda.synchronize()
+            reached += [bool(f) for f in fl]
+            nodes += [len(p) for p in pls]
+            del pls
+        return reached, nodes
 
-    pls = make_queries()
+    run_queries(0, nconc)                                   # warm-up: allocations, first launches
     torch.cuda.synchronize()
     barrier()
     t0 = time.perf_counter()
-    flags = B.Planner.run_many(pls, 60_000)
-    torch.cuda.synchronize()
+    reached, nodes = run_queries(0, QUERIES_PER_GPU)
     el = max_over_ranks(time.perf_counter() - t0)
-    nodes = sum(len(p) for p in pls)
-    del pls
-    pls = make_queries()
-    torch.cuda.synchronize()
     barrier()
     t0 = time.perf_counter()
-    for p in pls:
-        p.run(60_000)
-    torch.cuda.synchronize()
+    run_queries(0, 2 * nconc, seq=True)
     el_seq = max_over_ranks(time.perf_counter() - t0)
+    ok_nodes = [n for n, r in zip(nodes, reached) if r]
+    n_ok = int(max_over_ranks(float(sum(reached))))        # max over ranks would overstate: report rank 0 and say so
     res["config4_independent_queries_256"] = {
-        "queries": world * nq_local, "queries_per_gpu": nq_local, "seconds": el, "queries_per_s": world * nq_local / el,
-        "one_after_the_other": {"seconds": el_seq, "queries_per_s": world * nq_local / el_seq},
-        "reached_goal_rank0": int(sum(flags)), "mean_nodes_rank0": nodes / nq_local, "batch": 1024, "k": 16, "max_nodes": 60_000,
-        "sample": "8 of the 512 queries per GPU of configs[4](i); random free start/goal pairs, 3 milestones at the door "
-                  "centres; bgr_planner_run_many (round-robin steps, one stream + map handle per query)"}
+        "queries": world * QUERIES_PER_GPU, "queries_per_gpu": QUERIES_PER_GPU, "seconds": el,
+        "queries_per_s": world * QUERIES_PER_GPU / el,
+        "reached_goal_rank0": int(sum(reached)), "success_rate_rank0": float(np.mean(reached)), "reached_goal_max_over_ranks": n_ok,
+        "successful_queries_per_s": world * float(sum(reached)) / el,
+        "median_nodes_to_goal_rank0": int(np.median(ok_nodes)) if ok_nodes else None,
+        "median_nodes_all_rank0": int(np.median(nodes)),
+        "one_after_the_other": {"queries": 2 * nconc, "seconds": el_seq, "queries_per_s": world * 2 * nconc / el_seq},
+        "batch": 1024, "k": 16, "max_nodes": QUERY_MAX_NODES, "concurrent_queries": nconc,
+        "map": "256^3 @0.05 m, 3 walls with one %.2f m door each, %.1f%% occupied, %d leaf boxes, map seed 5 + rank"
+               % (0.05 * QUERY_DOOR_CELLS, 100 * occq.mean(), len(boxesq)),
+        "workload": "configs[4](i): %d independent (start, goal) pairs per GPU (random free points, sphere r = 0.1), planner seeds "
+                    "100 + 512 rank + q, MS sampler with the 3 door-centre milestones, edge checks + rewiring + BGR_PLAN_DEDUP; bgr_planner_run_many, "
+                    "%d queries in flight (one stream + map handle each)" % (QUERIES_PER_GPU, nconc)}
     res["note"] = ("wall clock of bgr_planner_run (host loop + device kernels, one sync per batch); nodes_per_s is the "
                    "aggregate over %d independent planning queries (one per GPU)" % world)
     return res
@@ -578,6 +755,52 @@ def cpu_edge_baseline(boxes, p1, p2, budget_s):
     return out
 
 
+def cpu_planner_baseline(budget_s):
+    """the oracle's restatement of the planner loop (oracle/src/planner.cpp, rrt_star_milestones.cpp:1160-1406 /
+    rrt_star.cpp:1140-1300) timed on the host: configs[0] in full (batch 1 = the reference's own sequential
+    loop, literal loop over every leaf box in the state check), and a bounded number of batches of the
+    configs[3] shape (bucket-grid broadphase in front of the same MPR: the literal loop over 795 k boxes
+    would take hours)."""
+    import bottleneck_guided_rrt_b200 as B
+    from bottleneck_guided_rrt_b200 import synth
+    from oracle import oracle as O
+    cores = host_cores()
+    out = {}
+    occ = synth.make_map(64, 1, n_walls=3, wall_thick=2, door_cells=6)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    table = synth.points(9, 200_000, 3.2)
+    for batch, flags, key in ((1, B.PLAN_QUIRKS, "config0_rrtstar_64_batch1"), (256, 0, "config0_rrtstar_64_batch256")):
+        P = B.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=B.PLAN_MODE_RS, k=10, batch=batch, flags=flags | B.PLAN_NO_GOAL, seed=5489)
+        op = O.Planner(P, boxes, table)
+        t0 = time.perf_counter()
+        while len(op) < 5000 and time.perf_counter() - t0 < budget_s:
+            op.run(5000, 64 if batch == 1 else 1)
+        el = time.perf_counter() - t0
+        out[key] = {"value": (len(op) - 1) / el, "unit": "nodes/s", "nodes": len(op), "seconds": el, "cores": 1 if batch == 1 else cores,
+                    "kind": "port", "sample": "configs[0] %s: %d of 5000 nodes, %d leaf boxes, k=10, batch %d; state check = the "
+                    "reference's loop over every leaf box + MPR (oracle mode 1)" % ("in full" if len(op) >= 5000 else "bounded by the time budget",
+                                                                                     len(op), len(boxes), batch)}
+    occ3 = synth.make_map(256, 5, n_walls=3, wall_thick=4, door_cells=5)
+    boxes3 = synth.grid_to_boxes(occ3, 0.05, (0, 0, 0), 3)
+    ms = door_milestones(occ3, 256)
+    table3 = synth.points(9, 200_000, 12.8)
+    P = B.PlannerParams((0.2, 0.2, 0.2), (12.6, 12.6, 12.6), mode=B.PLAN_MODE_MS, k=16, batch=4096,
+                        flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | B.PLAN_NO_GOAL, seed=5489)
+    op = O.Planner(P, boxes3, table3, ms, collision_mode=2)
+    op.step()                                               # builds the bucket grid (untimed, as the GPU map upload is)
+    n0, t0, nb = len(op), time.perf_counter(), 0
+    while time.perf_counter() - t0 < budget_s and len(op) < 200_000:
+        op.step()
+        nb += 1
+    el = time.perf_counter() - t0
+    out["config3_bottleneck_256_batch4096"] = {
+        "value": (len(op) - n0) / el, "unit": "nodes/s", "nodes": len(op), "batches": nb, "seconds": el, "cores": cores, "kind": "port",
+        "sample": "configs[3] shape, the first %d batches after the first (%d of 200,000 nodes; the per-batch cost grows with "
+                  "the tree, so this flatters the CPU): brute-force Nearest / kNN over the tree, bucket-grid broadphase + MPR "
+                  "collision (oracle mode 2), OpenMP over candidates" % (nb, len(op))}
+    return out
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
@@ -600,8 +823,9 @@ def run_reference(args):
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": "configs[1]: batched kNN, 1,000,000-node 3-D tree, 65,536 queries, k=16, eps=0 "
-                                  "(CPU: libnabo 1.0.7 algorithm restated in oracle/, OpenMP over queries, %d threads)" % cores},
+           "config": {"workload": "configs[1]: batched kNN, 1,000,000-node 3-D tree (U[0,25.6)^3, MT19937 seed 2), "
+                                  "65,536 queries/GPU (seed 3+rank), k=16, eps=0, exact, method=%s" % args.method,
+                      "cpu_arm": "libnabo 1.0.7 algorithm restated in oracle/ (kind: port), OpenMP over queries, %d threads" % cores},
            "cpu_baseline": cb,
            "e2e": {"value": value, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     if not args.skip_edges:
@@ -609,6 +833,8 @@ def run_reference(args):
         boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
         p1, p2 = synth.edges(4, N_EDGES, occ)
         out["edge_checks"] = cpu_edge_baseline(boxes, p1, p2, budget_s=15.0)
+    if not args.skip_planner:
+        out["planner"] = {"cpu_baseline": cpu_planner_baseline(budget_s=12.0)}
     print(json.dumps(out))
 
 

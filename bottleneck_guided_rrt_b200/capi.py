@@ -239,7 +239,7 @@ class NNSearchF:
         _check(lib().bgr_nns_build_index(self._h))
 
     def knn(self, query, k=1, epsilon=0.0, optionFlags=0, maxRadius=float("inf"), maxRadii=None,
-            indices=None, dists2=None):
+            indices=None, dists2=None, want_dists2=True):
         """Returns (indices (Q,k) int32, dists2 (Q,k) float32, touched).  Host arrays in,
         host arrays out; CUDA tensors in, CUDA tensors out (asynchronous on the stream)."""
         touched = C.c_uint64(0)
@@ -257,10 +257,10 @@ class NNSearchF:
         nq = q.shape[0]
         if indices is None:
             indices = np.empty((nq, k), dtype=np.int32)
-        if dists2 is None:
+        if dists2 is None and want_dists2:
             dists2 = np.empty((nq, k), dtype=np.float32)
         # libnabo checkSizesKnn: result matrices must be k x Q
-        if indices.shape != (nq, k) or dists2.shape != (nq, k):
+        if indices.shape != (nq, k) or (dists2 is not None and dists2.shape != (nq, k)):
             raise RuntimeError("Index/distance matrix has wrong shape: expected %dx%d" % (k, nq))
         mr = None
         if maxRadii is not None:

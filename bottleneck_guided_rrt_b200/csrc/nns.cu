@@ -362,7 +362,7 @@ int bgr_nns_knn_skip_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsign
 int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsigned flags,
                 float max_radius, const float* max_radii, int32_t* idx, float* d2, uint64_t* touched) {
     BGR_CHECK(check_knn_args(h, nq, k, eps, flags, max_radius));
-    BGR_ARG(nq == 0 || (q && idx && d2), "null query/result buffer");
+    BGR_ARG(nq == 0 || (q && idx), "null query/result buffer");
     if (touched) *touched = 0;
     if (nq == 0) return BGR_OK;
     BGR_CHECK(h->q_dev.reserve(3 * nq, h->stream, false));
@@ -387,7 +387,7 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
         BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
                                   h->d2_dev.p, touched));
         BGR_CUDA(cudaMemcpyAsync(idx, h->idx_dev.p, (size_t)nq * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
-        BGR_CUDA(cudaMemcpyAsync(d2, h->d2_dev.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        if (d2) BGR_CUDA(cudaMemcpyAsync(d2, h->d2_dev.p, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
         BGR_CUDA(cudaStreamSynchronize(h->stream));
         return BGR_OK;
     }
@@ -401,7 +401,7 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
         BGR_CUDA(cudaEventRecord(h->pipe.ev_out[c], h->stream));
         BGR_CUDA(cudaStreamWaitEvent(h->pipe.s_out, h->pipe.ev_out[c], 0));
         BGR_CUDA(cudaMemcpyAsync(idx + s0 * k, h->idx_dev.p + s0 * k, (size_t)m * k * sizeof(int32_t), cudaMemcpyDeviceToHost, h->pipe.s_out));
-        BGR_CUDA(cudaMemcpyAsync(d2 + s0 * k, h->d2_dev.p + s0 * k, (size_t)m * k * sizeof(float), cudaMemcpyDeviceToHost, h->pipe.s_out));
+        if (d2) BGR_CUDA(cudaMemcpyAsync(d2 + s0 * k, h->d2_dev.p + s0 * k, (size_t)m * k * sizeof(float), cudaMemcpyDeviceToHost, h->pipe.s_out));
     }
     BGR_CUDA(cudaStreamSynchronize(h->pipe.s_out));
     BGR_CUDA(cudaStreamSynchronize(h->stream));

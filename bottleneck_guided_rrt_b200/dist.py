@@ -54,19 +54,31 @@ class ShardedNNSearch:
         self.merge = merge
         self._slabs = None
 
-    def knn(self, query, k, optionFlags=0, maxRadius=float("inf")):
-        """query: replicated (Q,3) CUDA tensor.  Returns merged (idx, d2) on every rank."""
+    def knn(self, query, k, optionFlags=0, maxRadius=float("inf"), events=None):
+        """query: replicated (Q,3) CUDA tensor.  Returns merged (idx, d2) on every rank.
+        events: optional 3 torch.cuda.Event objects recorded on the current stream before the local
+        search, after it, and after the exchange + merge (measurement aid: local vs exchange time)."""
         import torch
         nq = query.shape[0]
+
+        def mark(i):
+            if events is not None:
+                events[i].record(torch.cuda.current_stream())
+
+        mark(0)
         if self.exchange == "peer":
             pi, pd = self.peer.slab_ptrs()
             self.nns.knn(query, k, 0.0, optionFlags, maxRadius, indices=pi, dists2=pd)
+            mark(1)
             self.peer.merge(nq, k, self.stream)
+            mark(2)
             if self._slabs is None or self._slabs[0] != (nq, k):
                 self._slabs = ((nq, k),) + tuple(self.peer.result(nq, k))    # views of the window, made once
             return self._slabs[1], self._slabs[2]
         if self.world == 1:
             idx, d2, _ = self.nns.knn(query, k, 0.0, optionFlags, maxRadius)
+            mark(1)
+            mark(2)
             return idx, d2
         key = (nq, k, query.device)
         if self._slabs is None or self._slabs[0] != key:
@@ -78,9 +90,11 @@ class ShardedNNSearch:
                            torch.empty((nq, k), dtype=torch.float32, device=query.device))
         _, loc, slabs, oi, od = self._slabs
         self.nns.knn(query, k, 0.0, optionFlags, maxRadius, indices=loc[0], dists2=loc[1].view(torch.float32))
+        mark(1)
         # concatenated-rows form (G*2*Q, k): accepted by both NCCL and gloo
         self.dist.all_gather_into_tensor(slabs.view(self.world * 2 * nq, k), loc.view(2 * nq, k), group=self.group)
         self.merge(slabs[:, 0], slabs[:, 1].view(torch.float32), oi, od)
+        mark(2)
         return oi, od
 
 

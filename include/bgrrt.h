@@ -97,7 +97,9 @@ int bgr_nns_build_index(bgr_nns* nns);
  * d2<=maxRadius^2 && (ALLOW_SELF_MATCH || d2>FLT_EPSILON); output ascending by (d2,index);
  * unfilled slots idx=-1, d2=+inf.  Errors like libnabo's checkSizesKnn: k > N (or N-1
  * without self match), unknown flag bits.  max_radii (Q floats) may be NULL.
- * touched (may be NULL) receives the number of (query,node) pairs evaluated. */
+ * touched (may be NULL) receives the number of (query,node) pairs evaluated.
+ * Host-pointer form only: d2_kxQ may be NULL when the caller consumes the indices alone (the
+ * reference does, MS:1312-1319): the distances are then not copied back (half the D2H bytes). */
 int bgr_nns_knn(bgr_nns* nns, const float* q_3xQ, int64_t nq, int k, float eps,
                 unsigned flags, float max_radius, const float* max_radii,
                 int32_t* idx_kxQ, float* d2_kxQ, uint64_t* touched);
