@@ -65,6 +65,9 @@ def lib():
     L.bgr_nns_nearest.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_debug_stats.argtypes = [vp, vp]
+    L.bgr_nns_knn_skip_dev.argtypes = [vp, vp, i64, i32, C.c_uint, vp, vp, vp]
+    L.bgr_nns_set_tile.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
+    L.bgr_nns_tile_stats.argtypes = [vp, vp]
     L.bgr_nns_destroy.argtypes = [vp]
     L.bgr_knn_merge_dev.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
     L.bgr_knn_merge_strided_dev.argtypes = [vp, vp, i32, i64, i64, i32, vp, vp, vp]
@@ -238,6 +241,23 @@ class NNSearchF:
     def build_index(self):
         _check(lib().bgr_nns_build_index(self._h))
 
+    def knn_skip(self, d_query, k, d_skip, d_indices, d_dists2, optionFlags=0):
+        """bgr_nns_knn_skip_dev: CUDA tensors only; rows of queries with a non-zero skip byte are left untouched"""
+        _check(lib().bgr_nns_knn_skip_dev(self._h, _ptr(d_query), d_query.shape[0], k, optionFlags, _ptr(d_skip),
+                                          _ptr(d_indices), _ptr(d_dists2)))
+
+    def set_tile(self, tx=0, ty=0, tz=0, warps=0):
+        """tile kNN tuning (bgr_nns_set_tile): all 0 = automatic, tx < 0 = tile search off"""
+        _check(lib().bgr_nns_set_tile(self._h, tx, ty, tz, warps))
+
+    def tile_stats(self):
+        """bgr_nns_tile_stats: tile searches so far, queries the last one handed back, its tile shape / count"""
+        s = np.zeros(4, dtype=np.uint64)
+        _check(lib().bgr_nns_tile_stats(self._h, _ptr(s)))
+        sh = int(s[2])
+        return {"tile_searches": int(s[0]), "fallback_queries_last": int(s[1]),
+                "tile": (sh & 255, (sh >> 8) & 255, (sh >> 16) & 255), "warps": sh >> 24, "tiles": int(s[3])}
+
     def knn(self, query, k=1, epsilon=0.0, optionFlags=0, maxRadius=float("inf"), maxRadii=None,
             indices=None, dists2=None, want_dists2=True):
         """Returns (indices (Q,k) int32, dists2 (Q,k) float32, touched).  Host arrays in,
@@ -250,6 +270,8 @@ class NNSearchF:
                 indices = torch.empty((nq, k), dtype=torch.int32, device=query.device)
             if dists2 is None:
                 dists2 = torch.empty((nq, k), dtype=torch.float32, device=query.device)
+            if maxRadii is not None and not _is_dev(maxRadii):      # per-query radii must live where the queries do
+                maxRadii = torch.from_numpy(np.ascontiguousarray(maxRadii, dtype=np.float32)).to(query.device)
             _check(lib().bgr_nns_knn_dev(self._h, _ptr(query), nq, k, epsilon, optionFlags, maxRadius,
                                          _ptr(maxRadii), _ptr(indices), _ptr(dists2), C.byref(touched)))
             return indices, dists2, touched.value

@@ -41,6 +41,14 @@ struct GridIndex {
     DevBuf<int32_t> block_sums;
     DevBuf<float> partial;        // bbox partials
     DevBuf<double> sumsq;         // build scratch
+    DevBuf<long long> tile_prof;
+    DevBuf<int32_t> tile_count, tile_list, tile_fb;   // tile kNN (tile_knn.cuh): per-tile query lists, fallback list
+    int64_t tile_zeroed = 0;      // tile counters known to be zero (every call leaves them zeroed)
+    int tile_parity = 0;          // which of the two fallback counts the next call uses
+    uint64_t n_tile = 0;          // tile_knn_kernel launches
+    int tile_shape[3] = {-1, 0, 0};  // tile kNN: -1 = off (the default, see tile_knn.cuh), 0 = tile size chosen from the query density, else forced
+    int tile_warps = 0;           // forced warps per tile CTA (0 = default)
+    uint64_t tile_last_shape = 0, tile_last_count = 0;   // of the last tile search (bgr_nns_tile_stats)
     DevBuf<int32_t> heavy;        // queries handed to grid_knn_heavy_kernel and its scratch (layout: kHeavyInts)
     double crowd = 0.0;           // sum(cell count^2) / n: the occupancy of the cell an average NODE sits in
                                   // (~kPtsPerCell+1 for a uniform cloud, thousands for a piled-up tree)
@@ -280,6 +288,7 @@ inline int grid_build(GridIndex& G, const float* x, const float* y, const float*
 inline void grid_release(GridIndex& G) {
     G.pts.release(); G.cell_start.release(); G.cell_id.release(); G.cursor.release();
     G.block_sums.release(); G.partial.release(); G.sumsq.release(); G.heavy.release();
+    G.tile_count.release(); G.tile_list.release(); G.tile_fb.release(); G.tile_prof.release(); G.tile_zeroed = 0;
     G.n_indexed = 0;
 }
 
@@ -335,12 +344,7 @@ constexpr int kFastTries = 3;
 // and the long scans (unsorted tail, rows longer than a warp) keep 3 x 32 nodes in flight; the lean
 // instantiation serves uniform clouds, where neither occurs and the extra registers would spill.
 template <bool PILED>
-__global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kernel(GridKnnArgs a) {
-    __shared__ unsigned long long cand[kGridWarps][kFastCap];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-    if (qi >= a.nq) return;
-    if (a.skip && __ldg(a.skip + qi)) return;
+__device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64_t qi, unsigned long long* cand_w, const int lane) {
     const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
     const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
     const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
@@ -418,7 +422,7 @@ __global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kerne
                     const unsigned m = __ballot_sync(kFull, pass);
                     if (pass) {
                         const int slot = c + __popc(m & ((1u << lane) - 1u));
-                        if (slot < kFastCap) cand[wib][slot] = pack_key(__float_as_uint(d), pidx);
+                        if (slot < kFastCap) cand_w[slot] = pack_key(__float_as_uint(d), pidx);
                     }
                     c += __popc(m);
                 };
@@ -487,10 +491,10 @@ __global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kerne
                 touched += (unsigned long long)(n27 + (a.n - a.n_indexed));
                 if (c <= kFastCap && (c >= a.k || (tau >= tmax && tmax >= lim))) {
                     __syncwarp();
-                    unsigned long long key = lane < c ? cand[wib][lane] : kKey64Max;
+                    unsigned long long key = lane < c ? cand_w[lane] : kKey64Max;
                     warp_sort32_u64(key, lane);
                     if (c > 32) {
-                        unsigned long long k2 = 32 + lane < c ? cand[wib][32 + lane] : kKey64Max;
+                        unsigned long long k2 = 32 + lane < c ? cand_w[32 + lane] : kKey64Max;
                         warp_sort32_u64(k2, lane);
                         warp_merge32_u64(key, k2, lane);
                     }
@@ -632,6 +636,29 @@ __global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kerne
         a.d2[qi * a.k + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
     }
     if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+}
+
+template <bool PILED>
+__global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kernel(GridKnnArgs a) {
+    __shared__ unsigned long long cand[kGridWarps][kFastCap];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    if (qi >= a.nq) return;
+    if (a.skip && __ldg(a.skip + qi)) return;
+    grid_knn_query<PILED>(a, qi, cand[wib], lane);
+}
+
+// The same search for a device-side list of query numbers (the queries tile_knn_kernel hands back:
+// a handful per thousand): persistent warps stride over the list.
+__global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_list_kernel(GridKnnArgs a, const int32_t* __restrict__ list,
+                                                                           const int32_t* __restrict__ count) {
+    __shared__ unsigned long long cand[kGridWarps][kFastCap];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int n = *count;
+    for (int w = blockIdx.x * kGridWarps + wib; w < n; w += gridDim.x * kGridWarps) {
+        grid_knn_query<false>(a, (int64_t)list[w], cand[wib], lane);
+        __syncwarp();
+    }
 }
 
 // Queries the main kernel set aside because their ring-1 block is piled up (a planner tree holds
@@ -895,42 +922,6 @@ inline int grid_nearest(GridIndex& G, const float* x, const float* y, const floa
     grid_nearest_kernel<<<(unsigned)div_up(nq, kGridWarps), kGridWarps * 32, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
     G.n_grid_nearest++;
-    return BGR_OK;
-}
-
-inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z, int64_t n,
-                    const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
-                    const float* d_radii, int32_t* d_idx, float* d_d2, int64_t index_base,
-                    unsigned long long* counter, int fast, cudaStream_t st, const uint8_t* d_skip = nullptr) {
-    GridKnnArgs a;
-    a.gm = G.geom;
-    a.pts = G.pts.p;
-    a.cell_start = G.cell_start.p;
-    a.n_indexed = G.n_indexed;
-    a.x = x; a.y = y; a.z = z; a.n = n;
-    a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
-    a.max_radius = max_radius; a.max_radii = d_radii;
-    a.idx = d_idx; a.d2 = d_d2; a.index_base = index_base; a.counter = counter;
-    a.fast = fast;
-    a.skip = d_skip;
-    a.fast_target = (float)k + 2.5f * sqrtf((float)k) + 1.f;
-    // piled-up index (crowd: occupancy of the cell an average node sits in; ~9 for a uniform cloud):
-    // queries whose ring-1 block is a pile go to the CTA-per-query scan
-    a.heavy = nullptr; a.heavy_cap = 0; a.heavy_min = 0;
-    if (fast && G.n_indexed > 0 && G.crowd > 64.0) {
-        BGR_CHECK(G.heavy.reserve(kHeavyInts, st, false));
-        BGR_CUDA(cudaMemsetAsync(G.heavy.p, 0, (1 + 2 * kHeavyCap) * sizeof(int32_t), st));
-        a.heavy = G.heavy.p; a.heavy_cap = kHeavyCap;
-        a.heavy_min = std::max<int64_t>(2048, n / 128);
-    }
-    if (a.heavy) grid_knn_kernel<true><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
-    else grid_knn_kernel<false><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
-    BGR_LAUNCH_CHECK();
-    if (a.heavy) G.n_piled++; else G.n_lean++;
-    if (a.heavy) {
-        grid_knn_heavy_kernel<<<dim3(kHeavyCap, kHeavySlices), kHeavyWarps * 32, 0, st>>>(a);
-        BGR_LAUNCH_CHECK();
-    }
     return BGR_OK;
 }
 

@@ -5,7 +5,7 @@
 #include <cmath>
 #include <cstring>
 #include <vector>
-#include "grid.cuh"
+#include "tile_knn.cuh"
 #include "knn_brute.cuh"
 #include "nearest.cuh"
 #include "internal.cuh"
@@ -334,7 +334,7 @@ static int knn_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int k, float e
             BGR_CUDA(cudaMemsetAsync(h->counter.p, 0, sizeof(unsigned long long), h->stream));
         }
         BGR_CHECK(grid_knn(h->grid, h->x.p, h->y.p, h->z.p, h->n, d_q, nq, k, flags, max_radius, d_radii,
-                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, grid_fast, h->stream, d_skip));
+                           d_idx, d_d2, h->index_base, stats ? h->counter.p : nullptr, grid_fast, h->device, h->stream, d_skip));
         if (stats) {
             unsigned long long c = 0;
             BGR_CUDA(cudaMemcpyAsync(&c, h->counter.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
@@ -383,6 +383,7 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
     int chunks = 1;
     if ((method == BGR_METHOD_GRID || method == BGR_METHOD_GRID_GENERAL) && !want_stats && !pipe_disabled())
         chunks = (int)std::min<int64_t>(4, nq / 8192);
+    if (const char* e = getenv("BGR_KNN_CHUNKS")) chunks = std::max(1, std::min(atoi(e), (int)CopyPipe::kMaxChunks));   // measurement aid
     if (chunks <= 1) {
         BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
                                   h->d2_dev.p, touched));
@@ -480,6 +481,28 @@ int bgr_nns_debug_stats(bgr_nns* h, uint64_t out[8]) {
         BGR_CUDA(cudaMemcpyAsync(&cnt, h->grid.heavy.p, sizeof(cnt), cudaMemcpyDeviceToHost, h->stream));
         BGR_CUDA(cudaStreamSynchronize(h->stream));
         out[3] = (uint64_t)std::max(0, cnt);
+    }
+    return BGR_OK;
+}
+
+int bgr_nns_set_tile(bgr_nns* h, int tx, int ty, int tz, int warps) {
+    BGR_ARG(h != nullptr, "null handle");
+    BGR_ARG(tx < 0 || (tx == 0 && ty == 0 && tz == 0) || (tx >= 1 && tx <= kTileMaxT0 && ty >= 1 && ty <= 6 && tz >= 1 && tz <= 6),
+            "tile size out of range (1..%d, 1..6, 1..6)", kTileMaxT0);
+    BGR_ARG(warps >= 0 && warps <= kTileMaxWarps, "warps per tile CTA out of range (0..%d)", kTileMaxWarps);
+    h->grid.tile_shape[0] = tx; h->grid.tile_shape[1] = ty; h->grid.tile_shape[2] = tz;
+    h->grid.tile_warps = warps;
+    return BGR_OK;
+}
+
+int bgr_nns_tile_stats(bgr_nns* h, uint64_t out[4]) {
+    BGR_ARG(h != nullptr && out != nullptr, "bad arguments");
+    out[0] = h->grid.n_tile; out[1] = 0; out[2] = h->grid.tile_last_shape; out[3] = h->grid.tile_last_count;
+    if (h->grid.n_tile && h->grid.tile_fb.p) {
+        int32_t cnt = 0;
+        BGR_CUDA(cudaMemcpyAsync(&cnt, h->grid.tile_fb.p + (h->grid.tile_parity ^ 1), sizeof(cnt), cudaMemcpyDeviceToHost, h->stream));
+        BGR_CUDA(cudaStreamSynchronize(h->stream));
+        out[1] = (uint64_t)std::max(0, cnt);
     }
     return BGR_OK;
 }

@@ -125,6 +125,16 @@ int bgr_nns_nearest_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int32_t*
  * rest ran the ring search), [4] grid_nearest_kernel launches, [5] nearest_kernel (plain scan)
  * launches, [6] knn_brute_kernel launches, [7] nodes covered by the current index */
 int bgr_nns_debug_stats(bgr_nns* nns, uint64_t out[8]);
+/* Tile kNN (csrc/tile_knn.cuh): an alternative exact search for large query batches over a fully indexed,
+ * uncrowded cloud — one lane per query out of shared-memory tiles.  OFF by default: measured on the
+ * configs[1] workload it is slower than the warp-per-query grid search (0.143 ms against 0.100 ms, DESIGN.md
+ * section 3.2b), so it is kept as a tested option.  set_tile: tx < 0 = off, all 0 = tile size chosen from the
+ * query density, else the tile size in grid cells and the warps per tile CTA.
+ * tile_stats: [0] tile searches run so far, [1] queries the LAST one handed back to the warp-per-query
+ * search (threshold misses, 26-bit distance ties, overfull tiles), [2] tx | ty<<8 | tz<<16 | warps<<24 of
+ * the last one, [3] its tile count.  Results never depend on any of this. */
+int bgr_nns_set_tile(bgr_nns* nns, int tx, int ty, int tz, int warps);
+int bgr_nns_tile_stats(bgr_nns* nns, uint64_t out[4]);
 int bgr_nns_destroy(bgr_nns* nns);
 
 /* Merge G per-shard top-k slabs (each k x Q, ascending, global indices) into one top-k by
