@@ -94,6 +94,8 @@ def lib():
     L.bgr_map_set_timing.argtypes = [vp, i32]
     L.bgr_map_set_gate.argtypes = [vp, i32]
     L.bgr_map_last_gate_stats.argtypes = [vp, vp]
+    L.bgr_map_dilation_stats.argtypes = [vp, vp]
+    L.bgr_map_download_gate.argtypes = [vp, i32, vp, vp]
     L.bgr_map_last_kernel_ms.argtypes = [vp, vp]
     L.bgr_map_destroy.argtypes = [vp]
     L.bgr_map_refresh_boxes.argtypes = [vp, vp, i64, vp, vp]
@@ -519,6 +521,20 @@ class OccupancyMap:
         s = np.zeros(2, dtype=np.uint64)
         _check(lib().bgr_map_last_gate_stats(self._h, _ptr(s)))
         return {"rect_items": int(s[0]), "dilation_cells": int(s[1])}
+
+    def download_gate(self, d):
+        """level 0 dilated by d cells (the gate map of the queries), brick words as download_bitmap"""
+        nw = C.c_int64(0)
+        _check(lib().bgr_map_download_gate(self._h, d, None, C.byref(nw)))
+        out = np.empty(nw.value, dtype=np.uint64)
+        _check(lib().bgr_map_download_gate(self._h, d, _ptr(out), C.byref(nw)))
+        return out
+
+    def dilation_stats(self):
+        """bgr_map_dilation_stats: full three-pass dilations / incremental updates of a cached gate map so far"""
+        s = np.zeros(2, dtype=np.uint64)
+        _check(lib().bgr_map_dilation_stats(self._h, _ptr(s)))
+        return {"full": int(s[0]), "incremental": int(s[1])}
 
     # ---- path post-processing (PrunePlan MS:562-643, find_labels MS:943-1011)
     def prune_path(self, path, radius=0.03, shape=SHAPE_CYLINDER):

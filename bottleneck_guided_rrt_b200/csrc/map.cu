@@ -297,11 +297,16 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
 
     const MapView& m = a.m;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t e0 = (int64_t)blockIdx.x * kEdgesPerCta;
-    const int ne = (int)min((int64_t)kEdgesPerCta, a.n - e0);
     if (a.only_overflow && a.n_overflow && __ldg(a.n_overflow) == 0u) return;
+    // blocks of kEdgesPerCta edges, strided over the grid (the overflow pass runs on a small grid: it
+    // almost always returns on the line above, and 3,907 empty CTAs cost 12 us)
+    const int64_t nblk = (a.n + kEdgesPerCta - 1) / kEdgesPerCta;
+    for (int64_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+    __syncthreads();                       // the previous block's shared state has been consumed
+    const int64_t e0 = blk * kEdgesPerCta;
+    const int ne = (int)min((int64_t)kEdgesPerCta, a.n - e0);
     const bool mine = tid < ne && (!a.only_overflow || (a.gflags[e0 + tid] & F_OVERFLOW));
-    if (!__syncthreads_or(mine)) return;
+    if (!__syncthreads_or(mine)) continue;
     if (tid == 0) { qcount = 0; st_items = st_cand = st_mpr = st_cap = 0; }
 
     // ---- phase 0: per-edge setup (thread per edge)
@@ -507,6 +512,7 @@ __global__ void __launch_bounds__(kEdgeThreads) collide_edges_kernel(EdgeArgs a)
             atomicAdd(a.stats + 3, st_cap);
         }
     }
+    }   // for blk
 }
 
 // ------------------------------------------------------------------ edges, fast path
@@ -548,6 +554,7 @@ struct Edge2Args {
     uint8_t* band;
     LevelGrid dil;               // level 0 dilated by gate_d cells (Chebyshev), same brick layout
     int gate_d;                  // 0 = gate off (every slab runs the rectangle phase)
+    int gate_seg, gate_rounds;   // slabs per gate item (divides 64, <= 32); segments per edge walked in early-out rounds
     int64_t e_begin;             // first edge of this launch (n = one past its last edge): chunked host calls
 };
 
@@ -558,16 +565,10 @@ struct Edge2Args {
 __device__ __forceinline__ uint64_t axis_mask_eq(int axis, int v) {
     return axis == 0 ? (0x1111111111111111ull << v) : axis == 1 ? (0x000F000F000F000Full << (4 * v)) : (0xFFFFull << (16 * v));
 }
-__global__ void dilate_axis_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int nbx, int nby,
-                                   int nbz, int axis, int d) {
-    const int64_t total = (int64_t)nbx * nby * nbz;
-    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w >= total) return;
-    const int bx = (int)(w % nbx), by = (int)((w / nbx) % nby), bz = (int)(w / ((int64_t)nbx * nby));
-    const int pos = axis == 0 ? bx : (axis == 1 ? by : bz), n = axis == 0 ? nbx : (axis == 1 ? nby : nbz);
-    const int64_t stride = axis == 0 ? 1 : (axis == 1 ? nbx : (int64_t)nbx * nby);
+// `W` OR-ed with its copies shifted by -d..+d cells along `axis`; Wm / Wp = the neighbouring brick words
+// on the low / high side (0 outside the map)
+__device__ __forceinline__ uint64_t dilate_word(int axis, int d, uint64_t W, uint64_t Wm, uint64_t Wp) {
     const int unit = axis == 0 ? 1 : (axis == 1 ? 4 : 16);
-    const uint64_t W = in[w], Wm = pos > 0 ? in[w - stride] : 0ull, Wp = pos + 1 < n ? in[w + stride] : 0ull;
     uint64_t r = W;
     for (int s = 1; s <= d; ++s) {
         uint64_t lt = 0, ge = 0;   // cells with coordinate < 4-s / >= s along the axis
@@ -580,7 +581,52 @@ __global__ void dilate_axis_kernel(const uint64_t* __restrict__ in, uint64_t* __
         r |= (W & ge) >> (unit * s);
         r |= (Wp & ~ge) << (unit * (4 - s));
     }
-    out[w] = r;
+    return r;
+}
+__global__ void dilate_axis_kernel(const uint64_t* __restrict__ in, uint64_t* __restrict__ out, int nbx, int nby,
+                                   int nbz, int axis, int d) {
+    const int64_t total = (int64_t)nbx * nby * nbz;
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= total) return;
+    const int bx = (int)(w % nbx), by = (int)((w / nbx) % nby), bz = (int)(w / ((int64_t)nbx * nby));
+    const int pos = axis == 0 ? bx : (axis == 1 ? by : bz), n = axis == 0 ? nbx : (axis == 1 ? nby : nbz);
+    const int64_t stride = axis == 0 ? 1 : (axis == 1 ? nbx : (int64_t)nbx * nby);
+    out[w] = dilate_word(axis, d, in[w], pos > 0 ? in[w - stride] : 0ull, pos + 1 < n ? in[w + stride] : 0ull);
+}
+
+// Incremental form (map updates): the dilated words of the bricks within d cells of each changed leaf are
+// recomputed from level 0 — the same three separable steps, on the brick's 3x3x3 neighbourhood in registers —
+// so a map update touches a few bricks per changed leaf instead of re-dilating all of level 0.
+// One thread per (leaf, brick slot); leaves larger than the slot count loop.  Two leaves may recompute the
+// same brick: both write the same word.
+constexpr int kRedilateSlots = 27;
+__global__ void redilate_kernel(const uint64_t* __restrict__ lv0, uint64_t* __restrict__ dil, int nbx, int nby, int nbz,
+                                int d, const LeafRec* __restrict__ recs, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * kRedilateSlots) return;
+    const LeafRec r = recs[i / kRedilateSlots];
+    const int s = 1 << r.level;
+    const int b0[3] = {max(0, (r.x - d) >> 2), max(0, (r.y - d) >> 2), max(0, (r.z - d) >> 2)};
+    const int b1[3] = {min(nbx - 1, (r.x + s - 1 + d) >> 2), min(nby - 1, (r.y + s - 1 + d) >> 2), min(nbz - 1, (r.z + s - 1 + d) >> 2)};
+    const int c0 = b1[0] - b0[0] + 1, c1 = b1[1] - b0[1] + 1, c2 = b1[2] - b0[2] + 1;
+    if (c0 <= 0 || c1 <= 0 || c2 <= 0) return;
+    auto load = [&](int bx, int by, int bz) -> uint64_t {
+        if (bx < 0 || bx >= nbx || by < 0 || by >= nby || bz < 0 || bz >= nbz) return 0ull;
+        return lv0[((int64_t)bz * nby + by) * nbx + bx];
+    };
+    for (int t = (int)(i % kRedilateSlots); t < c0 * c1 * c2; t += kRedilateSlots) {
+        const int bx = b0[0] + t % c0, by = b0[1] + (t / c0) % c1, bz = b0[2] + t / (c0 * c1);
+        uint64_t yw[3];
+#pragma unroll
+        for (int dz = -1; dz <= 1; ++dz) {
+            uint64_t xw[3];
+#pragma unroll
+            for (int dy = -1; dy <= 1; ++dy)
+                xw[dy + 1] = dilate_word(0, d, load(bx, by + dy, bz + dz), load(bx - 1, by + dy, bz + dz), load(bx + 1, by + dy, bz + dz));
+            yw[dz + 1] = dilate_word(1, d, xw[1], xw[0], xw[2]);
+        }
+        dil[((int64_t)bz * nby + by) * nbx + bx] = dilate_word(2, d, yw[1], yw[0], yw[2]);
+    }
 }
 
 // CTA-wide: move the shared-memory queue to the global queue, dropping the pairs of edges
@@ -756,6 +802,8 @@ __device__ __forceinline__ void cta_prefix(int val, int* prefix, int* warp_sums)
 constexpr int kGateSlabs = 128;   // slabs per edge the gate tracks (longer edges run every slab)
 constexpr float kGateSlop = 2e-3f;   // cells: covers the f32 rounding of the gate walk
 constexpr int kGateSeg = 8;           // slabs one thread walks (64 % kGateSeg == 0)
+constexpr int kGateRounds = 2;        // segments of an edge walked in early-out rounds before the flat list (measured:
+                                      // profiles/r2_gate_rounds_tune.txt; more rounds cost more in barriers than they skip)
 struct GateEdge {                     // the axis line in cell units relative to the edge's first slab
     float tlo, thi;                   // extent of the segment along ax
     float sb, sc, beta_b, beta_c;     // lateral cell coordinate = beta + slope * t
@@ -780,6 +828,7 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
     __shared__ unsigned eflags[kSweepEdges];
     __shared__ int warp_sums[kSweepThreads / 32];
     __shared__ GateEdge ge[kSweepEdges];
+    __shared__ uint8_t alist[2][kSweepEdges];   // undecided edges of the current / next gate round
     __shared__ int sq_count;
     __shared__ unsigned long long st_cand;
 
@@ -841,39 +890,31 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
     const int total = prefix[kSweepEdges];
     unsigned long long n_cand = 0;
 
-    // ---- gate pass: items = (edge, segment of kGateSeg consecutive slabs), one per thread, walked
+    // ---- gate pass: an item = (edge, segment of gate_seg consecutive slabs), walked by one thread
     // serially in f32 cell units relative to the edge's first slab (|values| <= 4096, error
-    // < 5e-4 cell, covered by kGateSlop).  Short equal-length chains keep the lanes of a warp in
-    // step and the CTA barrier that follows short.
+    // < 5e-4 cell, covered by kGateSlop).  The first gate_rounds segments of every edge run in
+    // ROUNDS (round r = segment r of every edge that is still undecided, compacted so that whole
+    // warps stay busy): a deep hit on the axis ends the edge, and half of all edges are such hits
+    // found within their first ~10 slabs — the later segments of those edges are never walked
+    // (17.6 M -> ~9 M slabs on configs[2]).  The segments left after the rounds run as one flat
+    // item list.  The order only decides how much is skipped: an edge ends with F_DEEP (hit, not in
+    // the band) whichever deep cell is found first, and undecided edges have walked every segment.
     if (gate) {
-        const int nseg_mine = (min(myslabs, kGateSlabs) + kGateSeg - 1) / kGateSeg;
-        cta_prefix(nseg_mine, prefix2, warp_sums);
-        const int total_seg = prefix2[kSweepEdges];
+        const int kSeg = a.gate_seg, kRounds = a.gate_rounds;
         const unsigned nbx = (unsigned)a.dil.nb[0], nbxy = (unsigned)a.dil.nb[0] * (unsigned)a.dil.nb[1];
         // deep-hit certificate on an axis cell needs a ball of radius >= 1e-3 m around the axis
         // point inside the shape: radius >= 1e-3 and the point >= 0.05 cell (res >= 0.02) from both ends
         const bool allow_deep = a.radius >= 1e-3 && m.res >= 0.02;
         const float rm_c = (float)(rm * m.inv_res) + kGateSlop;
-        for (int w0 = 0; w0 < total_seg; w0 += kSweepThreads) {
-            const int w = w0 + tid;
-            if (w >= total_seg) break;
-            int lo = 0, hi = kSweepEdges;
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (prefix2[mid] <= w) lo = mid; else hi = mid;
-            }
-            const int el = lo;
-            if (eflags[el] & F_DEEP) continue;
-            const int k0 = (w - prefix2[el]) * kGateSeg;
-            const int k1 = min(k0 + kGateSeg, min(prefix[el + 1] - prefix[el], kGateSlabs));
+        // walks slabs [k0, k1) of edge el; returns true on a deep hit, else the fired slabs in fired_mask
+        auto gate_segment = [&](const int el, const int k0, const int k1, unsigned& fired_mask) -> bool {
             const GateEdge g = ge[el];
             const int ax = es[el].ax, bx = ax == 0 ? 1 : 0, cx = ax == 2 ? 1 : 2;
             const int i_lo = es[el].i_lo, dim_a = m.dims[ax], dim_b = m.dims[bx], dim_c = m.dims[cx];
             // brick strides / log2 bit units of the permuted axes
             const unsigned Si = ax == 0 ? 1u : (ax == 1 ? nbx : nbxy), Sb = bx == 0 ? 1u : nbx, Sc = cx == 1 ? nbx : nbxy;
             const int Ui = ax == 0 ? 0 : (ax == 1 ? 2 : 4), Ub = bx == 0 ? 0 : 2, Uc = cx == 1 ? 2 : 4;
-            unsigned fired_mask = 0;
-            bool deep = false;
+            fired_mask = 0;
             for (int k = k0; k < k1; ++k) {
                 const int i = i_lo + k;
                 const float t0 = i == 0 ? (float)k - rm_c : (float)k;
@@ -905,6 +946,7 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
             // deep-hit probe of the fired slabs (after the walk, so that the lanes that fired run it
             // together): the cell holding the axis at the middle of the slab portion (kept 0.05 cell
             // inside the segment and inside the slab) is occupied => the shapes overlap by ~radius
+            bool deep = false;
             if (allow_deep) {
                 unsigned fm = fired_mask;
                 while (fm && !deep) {
@@ -922,8 +964,61 @@ __global__ void __launch_bounds__(kSweepThreads, 4) edges_sweep_kernel(Edge2Args
                     }
                 }
             }
-            if (deep) atomicOr(&eflags[el], F_HIT | F_DEEP);
-            else if (fired_mask) atomicOr(&emask[el][k0 >> 6], (unsigned long long)fired_mask << (k0 & 63));
+            return deep;
+        };
+        // ---- rounds: alist = the undecided edges that still have a segment to walk
+        const int gslabs_mine = min(myslabs, kGateSlabs);
+        cta_prefix(gslabs_mine > 0 ? 1 : 0, prefix2, warp_sums);
+        if (gslabs_mine > 0) alist[0][prefix2[tid]] = (uint8_t)tid;
+        int n_alive = prefix2[kSweepEdges];
+        __syncthreads();
+        int cur = 0;
+        for (int r = 0; r < kRounds && n_alive > 0; ++r) {
+            int el = 0;
+            bool go_on = false;
+            if (tid < n_alive) {
+                el = alist[cur][tid];
+                const int gs = min(prefix[el + 1] - prefix[el], kGateSlabs);
+                const int k0 = r * kSeg, k1 = min(k0 + kSeg, gs);
+                unsigned fired_mask;
+                if (gate_segment(el, k0, k1, fired_mask)) eflags[el] = F_HIT | F_DEEP;    // one thread per edge and round
+                else {
+                    if (fired_mask) emask[el][k0 >> 6] |= (unsigned long long)fired_mask << (k0 & 63);
+                    go_on = k1 < gs;
+                }
+            }
+            cta_prefix(go_on ? 1 : 0, prefix2, warp_sums);
+            if (go_on) alist[cur ^ 1][prefix2[tid]] = (uint8_t)el;
+            n_alive = prefix2[kSweepEdges];
+            cur ^= 1;
+            __syncthreads();
+        }
+        // ---- the segments left: one flat item list over the edges still undecided
+        if (n_alive > 0) {
+            int nseg_left = 0;
+            if (tid < n_alive) {
+                const int el = alist[cur][tid];
+                const int gs = min(prefix[el + 1] - prefix[el], kGateSlabs);
+                nseg_left = (gs + kSeg - 1) / kSeg - kRounds;
+            }
+            cta_prefix(nseg_left, prefix2, warp_sums);
+            const int total_seg = prefix2[kSweepEdges];
+            for (int w0 = 0; w0 < total_seg; w0 += kSweepThreads) {
+                const int w = w0 + tid;
+                if (w >= total_seg) break;
+                int lo = 0, hi = n_alive;
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (prefix2[mid] <= w) lo = mid; else hi = mid;
+                }
+                const int el = alist[cur][lo];
+                if (eflags[el] & F_DEEP) continue;
+                const int k0 = (kRounds + w - prefix2[lo]) * kSeg;
+                const int k1 = min(k0 + kSeg, min(prefix[el + 1] - prefix[el], kGateSlabs));
+                unsigned fired_mask;
+                if (gate_segment(el, k0, k1, fired_mask)) atomicOr(&eflags[el], F_HIT | F_DEEP);
+                else if (fired_mask) atomicOr(&emask[el][k0 >> 6], (unsigned long long)fired_mask << (k0 & 63));
+            }
         }
         __syncthreads();
         // slabs of the rectangle pass: within d of a fired slab; none for finished edges
@@ -1214,6 +1309,7 @@ struct bgr_map {
     DevBuf<uint64_t> dil[2], dil_tmp;  // level 0 dilated by dil_cells[s] cells (0 = stale): the gate maps of the
     int dil_cells[2] = {0, 0};         // edge sweep and of the sphere check, rebuilt lazily after a map change
     int dil_next = 0;
+    uint64_t n_dilate_full = 0, n_dilate_incr = 0;   // full three-pass dilations / incremental updates of a cached one
     int last_gate_d = 0;
     bool gate_on = true;
     int pipe_chunks = 0;               // > 1: the sweep of chunk c waits for pipe.ev_in[c] (host-pointer call)
@@ -1303,13 +1399,28 @@ void keys_of(const std::vector<LeafRec>& recs, std::vector<uint64_t>& keys) {
 }
 
 int raster(bgr_map* h, const std::vector<LeafRec>& recs, int set) {
-    h->dil_cells[0] = h->dil_cells[1] = 0;
     if (recs.empty()) return BGR_OK;
+    // the cached dilations (gate maps) follow the change: a small update re-dilates only the bricks within d
+    // cells of the changed leaves (redilate_kernel); a large one marks them stale and the next query rebuilds
+    // them in three passes over level 0.  Stale until the update below has gone through.
+    const int keep[2] = {h->dil_cells[0], h->dil_cells[1]};
+    h->dil_cells[0] = h->dil_cells[1] = 0;
     BGR_CHECK(check_device(h->device));
     BGR_CHECK(h->recs.reserve((int64_t)recs.size(), h->stream, false));
     BGR_CUDA(cudaMemcpyAsync(h->recs.p, recs.data(), recs.size() * sizeof(LeafRec), cudaMemcpyHostToDevice, h->stream));
     raster_kernel<<<(unsigned)div_up((int64_t)recs.size(), 256), 256, 0, h->stream>>>(h->view(), h->recs.p, (int64_t)recs.size(), set);
     BGR_LAUNCH_CHECK();
+    int64_t big = 0;                                   // leaves whose region exceeds the slot count: they loop
+    for (const LeafRec& r : recs) big += r.level >= 2;
+    const bool incremental = (int64_t)recs.size() * kRedilateSlots + big * 512 < h->words[0] / 4;
+    for (int k = 0; k < 2; ++k) {
+        if (keep[k] <= 0 || !incremental) continue;
+        redilate_kernel<<<(unsigned)div_up((int64_t)recs.size() * kRedilateSlots, 256), 256, 0, h->stream>>>(
+            h->bits[0].p, h->dil[k].p, h->nb[0][0], h->nb[0][1], h->nb[0][2], keep[k], h->recs.p, (int64_t)recs.size());
+        BGR_LAUNCH_CHECK();
+        h->dil_cells[k] = keep[k];
+        h->n_dilate_incr++;
+    }
     BGR_CUDA(cudaStreamSynchronize(h->stream));   // recs is a host temporary
     return BGR_OK;
 }
@@ -1333,6 +1444,7 @@ int ensure_dilated(bgr_map* h, int d, const uint64_t** out) {
     dilate_axis_kernel<<<nblk, 256, 0, h->stream>>>(h->dil_tmp.p, h->dil[k].p, h->nb[0][0], h->nb[0][1], h->nb[0][2], 2, d);
     BGR_LAUNCH_CHECK();
     h->dil_cells[k] = d;
+    h->n_dilate_full++;
     *out = h->dil[k].p;
     return BGR_OK;
 }
@@ -1396,6 +1508,7 @@ int bgr_map_set_boxes(bgr_map* h, const double* boxes, int64_t nb) {
         BGR_CUDA(cudaMemsetAsync(h->bits[L].p, 0, (size_t)h->words[L] * 8, h->stream));
         h->level_count[L] = 0;
     }
+    h->dil_cells[0] = h->dil_cells[1] = 0;   // level 0 was cleared: the cached dilations are rebuilt in full
     for (uint64_t k : keys) h->level_count[(int)(k >> 48)] += 1;
     refresh_mask(h);
     // the leaf list is trusted by refresh_boxes only once the bitmap really holds it
@@ -1603,6 +1716,11 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         a.queue = h->queue.p; a.queue_cap = (unsigned)std::min<int64_t>(cap, 0x7fffffff);
         a.qctl = h->qctl.p; a.stats = h->stats.p; a.hit = d_hit; a.band = d_band;
         a.gate_d = gate ? gate_d : 0;
+        a.gate_seg = kGateSeg; a.gate_rounds = kGateRounds;
+        if (const char* e = getenv("BGR_GATE")) {          // measurement aid: "seg,rounds"
+            int sg = 0, rd = 0;
+            if (sscanf(e, "%d,%d", &sg, &rd) == 2 && sg >= 1 && sg <= 32 && 64 % sg == 0 && rd >= 0) { a.gate_seg = sg; a.gate_rounds = rd; }
+        }
         a.dil.bits = const_cast<uint64_t*>(dil_bits);
         for (int ax = 0; ax < 3; ++ax) a.dil.nb[ax] = h->nb[0][ax];
         // one sweep launch per chunk of a chunked host call (each waits for its H2D copy), one
@@ -1631,7 +1749,7 @@ int bgr_map_collide_edges_dev(bgr_map* h, const float* d_p1, const float* d_p2, 
         if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[1], h->stream));
     }
     if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[2], h->stream));
-    collide_edges_kernel<<<(unsigned)div_up(n, kEdgesPerCta), kEdgeThreads, 0, h->stream>>>(ma);
+    collide_edges_kernel<<<(unsigned)std::min<int64_t>(div_up(n, kEdgesPerCta), ma.only_overflow ? 2LL * num_sms() : (1LL << 30)), kEdgeThreads, 0, h->stream>>>(ma);
     BGR_LAUNCH_CHECK();
     if (h->timing) BGR_CUDA(cudaEventRecord(h->tev[3], h->stream));
     edges_finalize_kernel<<<(unsigned)div_up(n, 256), 256, 0, h->stream>>>(h->eflags.p, n, d_hit, d_band);
@@ -1736,6 +1854,25 @@ int bgr_map_last_gate_stats(bgr_map* h, uint64_t out[2]) {
     BGR_CUDA(cudaMemcpyAsync(&s, h->stats.p + 4, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
     BGR_CUDA(cudaStreamSynchronize(h->stream));
     out[0] = s;
+    return BGR_OK;
+}
+
+int bgr_map_download_gate(bgr_map* h, int d, uint64_t* out, int64_t* n_words) {
+    BGR_ARG(h != nullptr && n_words && d >= 1 && d <= 3, "bad arguments (d in 1..3)");
+    *n_words = h->words[0];
+    if (!out) return BGR_OK;
+    BGR_CHECK(check_device(h->device));
+    const uint64_t* bits = nullptr;
+    BGR_CHECK(ensure_dilated(h, d, &bits));
+    BGR_CUDA(cudaMemcpyAsync(out, bits, (size_t)h->words[0] * 8, cudaMemcpyDeviceToHost, h->stream));
+    BGR_CUDA(cudaStreamSynchronize(h->stream));
+    return BGR_OK;
+}
+
+int bgr_map_dilation_stats(bgr_map* h, uint64_t out[2]) {
+    BGR_ARG(h != nullptr && out, "bad arguments");
+    out[0] = h->n_dilate_full;
+    out[1] = h->n_dilate_incr;
     return BGR_OK;
 }
 

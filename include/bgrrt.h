@@ -221,6 +221,14 @@ int bgr_map_last_stats(bgr_map* map, uint64_t out[4]);
  * call, [1] d of the dilated map currently built (0 = none). */
 int bgr_map_set_gate(bgr_map* map, int on);
 int bgr_map_last_gate_stats(bgr_map* map, uint64_t out[2]);
+/* The gate maps (level 0 dilated by the query radius, one cached per radius class) follow map updates
+ * incrementally: update_boxes / refresh_boxes re-dilate only the bricks within d cells of the changed leaves;
+ * set_boxes and very large updates rebuild them in full at the next query.  out[0] = full dilations,
+ * out[1] = incremental updates so far (test / measurement aid). */
+int bgr_map_dilation_stats(bgr_map* map, uint64_t out[2]);
+/* the gate map for dilation d (1..3 cells; built or brought up to date if need be), same word layout as
+ * bgr_map_download_bitmap (test aid) */
+int bgr_map_download_gate(bgr_map* map, int d, uint64_t* out, int64_t* n_words);
 /* measurement aid: with timing on, collide_edges records CUDA events between its kernels on the
  * map's stream; last_kernel_ms returns the durations of the last call: [0] edges_sweep_kernel,
  * [1] edges_narrow_kernel, [2] collide_edges_kernel (general / overflow path), [3] finalize */

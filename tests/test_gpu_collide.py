@@ -52,6 +52,74 @@ def test_incremental_update(bgr, oracle):
     assert np.array_equal(_bits_to_occ(m.download_bitmap(), 64), occ2)
 
 
+def _dilate_np(occ, d):
+    """box dilation by d cells (Chebyshev), zero outside the map"""
+    out = occ.astype(bool)
+    for axis in range(3):
+        acc = out.copy()
+        for s in range(1, d + 1):
+            sl_a = [slice(None)] * 3
+            sl_b = [slice(None)] * 3
+            sl_a[axis], sl_b[axis] = slice(s, None), slice(None, -s)
+            acc[tuple(sl_a)] |= out[tuple(sl_b)]
+            acc[tuple(sl_b)] |= out[tuple(sl_a)]
+        out = acc
+    return out.astype(np.uint8)
+
+
+@pytest.mark.parametrize("n", [100, 128])
+def test_gate_maps_follow_updates_incrementally(bgr, oracle, n):
+    """north_star (1) "rebuilt incrementally when the map updates", for the gate maps too: after update_boxes /
+    refresh_boxes the cached dilations (d = 1 for the 0.03 m edges, d = 3 for the 0.1 m state sphere) are
+    brought up to date by re-dilating only the bricks near the changed leaves — compared cell by cell with a
+    numpy dilation of the new occupancy, and counted (no full re-dilation after the first one)."""
+    occ = oracle.make_map(n, seed=3, n_walls=2, wall_thick=2, door_cells=4)
+    boxes = oracle.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (n, n, n))
+    m.set_boxes(boxes)
+    for d in (1, 3):
+        assert np.array_equal(_bits_to_occ(m.download_gate(d), n), _dilate_np(occ, d))
+    assert m.dilation_stats() == {"full": 2, "incremental": 0}
+    rng = np.random.default_rng(5)
+    cur = occ.copy()
+    for step in range(6):
+        # remove some leaves (any level), add single cells and a few 2^3 / 4^3 blocks, some at the map border
+        ridx = rng.choice(len(boxes), 20, replace=False) if step % 2 == 0 else np.zeros(0, dtype=np.int64)
+        rem = boxes[ridx]
+        for b in rem:
+            s_ = int(round(b[3] / 0.05))
+            x0, y0, z0 = (int(round(b[a] / 0.05 - s_ / 2)) for a in range(3))
+            cur[z0:z0 + s_, y0:y0 + s_, x0:x0 + s_] = 0
+        boxes = np.delete(boxes, ridx, axis=0)
+        add = []
+        for _ in range(20):
+            L = int(rng.integers(0, 3))
+            s_ = 1 << L
+            c = (rng.integers(0, (n - s_) // s_ + 1, 3) * s_) if rng.random() < 0.8 else np.array([0, n - s_ - (n - s_) % s_, 0])
+            x0, y0, z0 = int(c[0]), int(c[1]), int(c[2])
+            if cur[z0:z0 + s_, y0:y0 + s_, x0:x0 + s_].any():
+                continue
+            cur[z0:z0 + s_, y0:y0 + s_, x0:x0 + s_] = 1
+            add.append([(x0 + s_ / 2) * 0.05, (y0 + s_ / 2) * 0.05, (z0 + s_ / 2) * 0.05, s_ * 0.05, 1.0, 0.5])
+        add = np.asarray(add, dtype=np.float64).reshape(-1, 6)
+        m.update_boxes(add if len(add) else None, rem if len(rem) else None)
+        boxes = np.concatenate([boxes, add])
+        assert np.array_equal(_bits_to_occ(m.download_bitmap(), n), cur)
+        for d in (1, 3):
+            assert np.array_equal(_bits_to_occ(m.download_gate(d), n), _dilate_np(cur, d)), "step %d d %d" % (step, d)
+    st = m.dilation_stats()
+    assert st["full"] == 2 and st["incremental"] >= 12, st
+    # refresh_boxes (whole-tree republish, diffed) keeps them current the same way
+    m2 = bgr.OccupancyMap(0.05, (0, 0, 0), (n, n, n))
+    m2.set_boxes(oracle.grid_to_boxes(occ, 0.05, (0, 0, 0), 3))
+    m2.download_gate(1)
+    occ_b = occ.copy()
+    occ_b[n // 2:n // 2 + 6, 3:9, 5:11] ^= 1
+    m2.refresh_boxes(oracle.grid_to_boxes(occ_b, 0.05, (0, 0, 0), 3))
+    assert np.array_equal(_bits_to_occ(m2.download_gate(1), n), _dilate_np(occ_b, 1))
+    assert m2.dilation_stats()["full"] == 1 and m2.dilation_stats()["incremental"] >= 1
+
+
 def test_box_validation(bgr, oracle):
     m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64))
     with pytest.raises(RuntimeError):
