@@ -412,18 +412,22 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
                       nzr = min(cz + 1, gm.g[2] - 1) - max(cz - 1, 0) + 1;
             const float vol = (float)(nxr * nyr * nzr) * gm.cs * gm.cs * gm.cs;
             const float r3 = a.fast_target * vol / (4.18879f * (float)n27);
-            const float r0 = cbrtf(r3);
+            const float r0 = exp2f(__log2f(r3) * 0.33333334f);      // the threshold only steers the work: any value is exact
             float tau = fminf(r0 * r0, tmax);
+            const uint32_t cand_s = smem_u32(cand_w);
+            const unsigned lt_mask = (1u << lane) - 1u;
+            const float eps_lo = self ? -1.f : FLT_EPSILON;         // the self-match rule d2 > FLT_EPSILON as one comparison (d2 >= 0 > -1)
+            const int last = (int)a.n_indexed - 1;
             for (int attempt = 0; attempt < kFastTries; ++attempt) {
                 int c = 0;
                 auto consider = [&](float px, float py, float pz, uint32_t pidx, bool valid) {
                     const float d = dist2(px, py, pz);
-                    const bool pass = valid && (d <= tau) && (self || d > FLT_EPSILON);
+                    const bool pass = valid && (d <= tau) && (d > eps_lo);
                     const unsigned m = __ballot_sync(kFull, pass);
-                    if (pass) {
-                        const int slot = c + __popc(m & ((1u << lane) - 1u));
-                        if (slot < kFastCap) cand_w[slot] = pack_key(__float_as_uint(d), pidx);
-                    }
+                    const int slot = c + __popc(m & lt_mask);
+                    // key = (d2 bits << 32) | index: low word first
+                    if (pass && slot < kFastCap)
+                        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(cand_s + 8u * (unsigned)slot), "r"(pidx), "r"(__float_as_uint(d)) : "memory");
                     c += __popc(m);
                 };
                 if (PILED) {
@@ -457,8 +461,7 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
                     for (int i = 0; i < 3; ++i) {
                         s0[i] = __shfl_sync(kFull, rs, g + i);
                         e0[i] = __shfl_sync(kFull, re, g + i);
-                        p[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (s0[i] + lane < e0[i]) p[i] = __ldg(a.pts + s0[i] + lane);
+                        p[i] = __ldg(a.pts + min(s0[i] + lane, last));      // lanes past the row's end load a node they ignore
                     }
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
@@ -492,6 +495,29 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
                 if (c <= kFastCap && (c >= a.k || (tau >= tmax && tmax >= lim))) {
                     __syncwarp();
                     unsigned long long key = lane < c ? cand_w[lane] : kKey64Max;
+                    if (c <= 32) {
+                        // rank by counting (d2 alone orders the survivors unless two of them share a d2: then
+                        // the bitonic sort below breaks the tie by index): lane -> row position directly
+                        const uint32_t kd = (uint32_t)(key >> 32);
+                        const unsigned peers = __match_any_sync(kFull, kd);
+                        if (!__any_sync(kFull, lane < c && (peers & (peers - 1u)) != 0u)) {
+                            const uint32_t* cd = reinterpret_cast<const uint32_t*>(cand_w) + 1;
+                            int rank = 0;
+#pragma unroll 4
+                            for (int j = 0; j < c; ++j) rank += cd[2 * j] < kd ? 1 : 0;
+                            if (lane < c) {
+                                if (rank < a.k) {
+                                    a.idx[qi * a.k + rank] = (int32_t)((int64_t)(uint32_t)key + a.index_base);
+                                    a.d2[qi * a.k + rank] = __uint_as_float(kd);
+                                }
+                            } else if (lane < a.k) {                 // fewer than k inside the radius limit
+                                a.idx[qi * a.k + lane] = -1;
+                                a.d2[qi * a.k + lane] = __uint_as_float(kInfBits);
+                            }
+                            if (a.counter && lane == 0) atomicAdd(a.counter, touched);
+                            return;
+                        }
+                    }
                     warp_sort32_u64(key, lane);
                     if (c > 32) {
                         unsigned long long k2 = 32 + lane < c ? cand_w[32 + lane] : kKey64Max;
@@ -508,11 +534,11 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
                 }
                 __syncwarp();
                 if (c > kFastCap) {
-                    const float f = cbrtf(a.fast_target / (float)c);
+                    const float f = exp2f(__log2f(a.fast_target / (float)c) * 0.33333334f);
                     tau = tau * f * f;
                 } else {
                     if (tau >= tmax) break;                       // needs ring 2: general search
-                    const float f = c > 0 ? cbrtf((a.fast_target + 6.f) / (float)c) : 2.f;
+                    const float f = c > 0 ? exp2f(__log2f((a.fast_target + 6.f) / (float)c) * 0.33333334f) : 2.f;
                     tau = fminf(tmax, tau * f * f * 1.15f);
                 }
             }
@@ -639,7 +665,7 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
 }
 
 template <bool PILED>
-__global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kernel(GridKnnArgs a) {
+__global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArgs a) {
     __shared__ unsigned long long cand[kGridWarps][kFastCap];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
