@@ -35,6 +35,7 @@ from .capi import (  # noqa: F401
     PLAN_QUIRKS,
     PLAN_NO_GOAL,
     PLAN_DEDUP,
+    PLAN_NO_PERSIST,
     PLAN_MODE_RS,
     PLAN_MODE_MS,
     microbench_l2,

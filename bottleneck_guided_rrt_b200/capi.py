@@ -114,6 +114,7 @@ def lib():
     L.bgr_planner_get_tree.argtypes = [vp, vp, vp]
     L.bgr_planner_get_path.argtypes = [vp, vp, vp]
     L.bgr_planner_stats.argtypes = [vp, vp]
+    L.bgr_planner_persist_stats.argtypes = [vp, vp]
     L.bgr_planner_nns.argtypes = [vp, vp]
     L.bgr_planner_destroy.argtypes = [vp]
     _LIB = L
@@ -129,7 +130,7 @@ def microbench_l2(nbytes, mode, reps=10):
     return v.value
 
 
-PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP = 1, 2, 4, 8, 16
+PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP, PLAN_NO_PERSIST = 1, 2, 4, 8, 16, 32
 PLAN_MODE_RS, PLAN_MODE_MS = 0, 1
 
 
@@ -662,6 +663,12 @@ class Planner:
         h = C.c_void_p()
         _check(lib().bgr_planner_nns(self._h, C.byref(h)))
         return _nns_debug(h)
+
+    def persist_stats(self):
+        """bgr_planner_persist_stats: launches of the persistent small-batch kernel and the steps they ran"""
+        s = np.zeros(2, dtype=np.uint64)
+        _check(lib().bgr_planner_persist_stats(self._h, _ptr(s)))
+        return {"launches": int(s[0]), "steps": int(s[1])}
 
     def stats(self):
         s = np.zeros(8, dtype=np.int64)

@@ -62,4 +62,7 @@ cudaStream_t map_stream(const bgr_map* h);
 int map_device(const bgr_map* h);
 // slot for scratch memory another translation unit keeps per map (freed with free_fn by bgr_map_destroy)
 void** map_aux(bgr_map* h, void (*free_fn)(void*));
+// gate map of a sphere query of this radius (level 0 dilated; built / brought up to date if need be); bits = nullptr
+// when the gate does not apply
+int map_sphere_gate(bgr_map* h, double radius, LevelGrid* dil);
 }  // namespace bgr

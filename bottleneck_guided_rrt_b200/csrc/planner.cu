@@ -17,6 +17,8 @@
 #include <thread>
 #include <vector>
 #include "internal.cuh"
+#include "spheres.cuh"
+#include "warp_topk.cuh"
 
 using namespace bgr;
 
@@ -69,12 +71,10 @@ __device__ __forceinline__ uint32_t mt_temper(uint32_t x) {              // mtra
     return x ^ (x >> 18);
 }
 // state: [0..623] words, [624] position.  Produces n tempered words in stream order.
-__global__ void __launch_bounds__(256) mt_fill_kernel(uint32_t* __restrict__ state, uint32_t* __restrict__ out, int n) {
-    __shared__ uint32_t s[kMtN];
+// s = the state in shared memory, pos = its position; every thread of the CTA calls this (barriers
+// inside); returns the new position.  out may be global or shared memory.
+__device__ __forceinline__ int mt_generate(uint32_t* s, int pos, uint32_t* out, int n) {
     const int tid = threadIdx.x;
-    for (int i = tid; i < kMtN; i += blockDim.x) s[i] = state[i];
-    int pos = (int)state[kMtN];
-    __syncthreads();
     int done = 0;
     while (done < n) {
         if (pos == kMtN) {                    // gen_state (mtrand.cpp:12-19), three dependent phases
@@ -104,6 +104,15 @@ __global__ void __launch_bounds__(256) mt_fill_kernel(uint32_t* __restrict__ sta
         pos += take;
         __syncthreads();
     }
+    return pos;
+}
+__global__ void __launch_bounds__(256) mt_fill_kernel(uint32_t* __restrict__ state, uint32_t* __restrict__ out, int n) {
+    __shared__ uint32_t s[kMtN];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < kMtN; i += blockDim.x) s[i] = state[i];
+    int pos = (int)state[kMtN];
+    __syncthreads();
+    pos = mt_generate(s, pos, out, n);
     for (int i = tid; i < kMtN; i += blockDim.x) state[i] = s[i];
     if (tid == 0) state[kMtN] = (uint32_t)pos;
 }
@@ -126,9 +135,8 @@ __device__ __forceinline__ float norm_ref(float ax, float ay, float az, float bx
 }
 
 // ------------------------------------------------------------------ per-candidate kernels
-__global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 | RS:1155-1178
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
+// whole warps call this (c >= B: a lane that only takes part in the ballots)
+__device__ __forceinline__ void plan_sample_body(const PlanDev& d, const int c, const int lane) {   // MS:1182-1219 | RS:1155-1178
     const bool live = c < d.B;
     const float* src = d.p.goal;
     int slot = 0;                                               // goal
@@ -175,14 +183,15 @@ __global__ void plan_sample_kernel(PlanDev d) {                // MS:1182-1219 |
         }
     }
 }
+__global__ void plan_sample_kernel(PlanDev d) { plan_sample_body(d, blockIdx.x * blockDim.x + threadIdx.x, threadIdx.x & 31); }
 
 // BGR_PLAN_DEDUP: copies of a goal / milestone candidate are rejected like a failed state check
-__global__ void plan_dedup_kernel(PlanDev d) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void plan_dedup_body(const PlanDev& d, const int c) {
     if (c >= d.B) return;
     const int slot = d.qslot[c];
     if (slot < d.n_fixed && (long long)(d.B - c) != d.counters[11 + slot]) d.hit[c] = 1;
 }
+__global__ void plan_dedup_kernel(PlanDev d) { plan_dedup_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
 // The goal / milestone candidates of a batch that share a sample slot share the nearest node, the
 // steered point and therefore the neighbour rows: the search runs for the first of them only
@@ -207,8 +216,7 @@ __global__ void plan_knn_spread_kernel(PlanDev d, float* __restrict__ knn_d2) {
     knn_d2[(size_t)c * d.K + j] = knn_d2[(size_t)first * d.K + j];
 }
 
-__global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void plan_steer_body(const PlanDev& d, const int c) {   // MS:1233-1268
     if (c >= d.B) return;
     const int32_t ni = d.u_near[d.qslot[c]];
     d.near[c] = ni;
@@ -232,6 +240,7 @@ __global__ void plan_steer_kernel(PlanDev d) {                 // MS:1233-1268
     d.pnew[3 * c] = ox; d.pnew[3 * c + 1] = oy; d.pnew[3 * c + 2] = oz;
     d.found[c] = found;
 }
+__global__ void plan_steer_kernel(PlanDev d) { plan_steer_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
 // candidate parent of slot j of candidate c: j < K the j-th neighbour, j == K the Nearest node
 __device__ __forceinline__ int32_t slot_node(const PlanDev& d, int c, int j) {
@@ -276,8 +285,7 @@ __device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, flo
     return cost;
 }
 
-__global__ void plan_cost_kernel(PlanDev d) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void plan_cost_body(const PlanDev& d, const int t) {
     if (t >= d.B * (d.K + 1)) return;
     const int c = t / (d.K + 1), j = t % (d.K + 1);
     if (d.hit[c]) return;
@@ -285,9 +293,9 @@ __global__ void plan_cost_kernel(PlanDev d) {
     if (ind < 0) return;
     d.costs[t] = chain_cost(d, ind, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2], &d.psis[t]);
 }
+__global__ void plan_cost_kernel(PlanDev d) { plan_cost_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
-__global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS:838-853 + MS:1322-1323
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void plan_select_body(const PlanDev& d, const int c) {   // extend_tree MS:838-853 + MS:1322-1323
     if (c >= d.B) return;
     const bool edge_check = d.p.flags & BGR_PLAN_EDGE_CHECK, quirks = d.p.flags & BGR_PLAN_QUIRKS;
     const int K1 = d.K + 1;
@@ -327,10 +335,12 @@ __global__ void plan_select_kernel(PlanDev d) {                // extend_tree MS
     d.psi[c] = d.psis[(size_t)c * K1 + (keep_near ? d.K : slot)];   // follows the pointer actually committed
     d.ok[c] = 1;
 }
+__global__ void plan_select_kernel(PlanDev d) { plan_select_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
 // One CTA: goal cut (first accepted candidate within goal_tol, MS:1340), ordered compaction,
 // append to the store (MS:1325-1327) and the goal node (MS:1346-1347).
-__global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, float* y, float* z, float4* f4) {
+// every thread of ONE CTA calls this (barriers inside)
+__device__ __forceinline__ void plan_commit_body(const PlanDev& d, float* x, float* y, float* z, float4* f4) {
     __shared__ int s_goal;
     __shared__ int warp_tot[32];
     __shared__ int s_base;
@@ -388,6 +398,9 @@ __global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, 
         }
     }
 }
+__global__ void __launch_bounds__(1024) plan_commit_kernel(PlanDev d, float* x, float* y, float* z, float4* f4) {
+    plan_commit_body(d, x, y, z, f4);
+}
 
 // rewiring (beyond reference): neighbour `ind` adopts the new node when
 // cost(new) + Norm(tree[ind], new) < cost(ind) (and the edge is free); one proposal per node
@@ -415,15 +428,14 @@ __device__ __forceinline__ bool rewire_proposal(const PlanDev& d, int t, int32_t
     *key = ((unsigned long long)__float_as_uint(nc) << 32) | (unsigned)ni;
     return true;
 }
-__global__ void plan_rewire_propose_kernel(PlanDev d) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void plan_rewire_propose_body(const PlanDev& d, const int t) {
     if (t >= d.B * d.K) return;
     int32_t ind;
     unsigned long long key;
     if (rewire_proposal(d, t, &ind, &key)) atomicMin(&d.rkey[ind], key);
 }
-__global__ void plan_rewire_apply_kernel(PlanDev d, const int32_t* __restrict__ par_snapshot_unused) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void plan_rewire_propose_kernel(PlanDev d) { plan_rewire_propose_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
+__device__ __forceinline__ void plan_rewire_apply_body(const PlanDev& d, const int t) {
     if (t >= d.B * d.K) return;
     const int c = t / d.K, j = t % d.K;
     const int32_t ni = d.new_index[c];
@@ -436,11 +448,199 @@ __global__ void plan_rewire_apply_kernel(PlanDev d, const int32_t* __restrict__ 
     d.par[ind] = ni;
     atomicAdd((unsigned long long*)&d.counters[7], 1ull);
 }
-__global__ void plan_rewire_clear_kernel(PlanDev d) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void plan_rewire_apply_kernel(PlanDev d, const int32_t* __restrict__ par_snapshot_unused) {
+    plan_rewire_apply_body(d, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__device__ __forceinline__ void plan_rewire_clear_body(const PlanDev& d, const int t) {
     if (t >= d.B * d.K) return;
     const int32_t ind = d.knn_idx[(size_t)t];
     if (ind > 0 && ind < d.n) d.rkey[ind] = ~0ull;
+}
+__global__ void plan_rewire_clear_kernel(PlanDev d) { plan_rewire_clear_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
+
+// ------------------------------------------------------------------ persistent small-batch steps
+// A step of a small batch is ~15 tiny dependent launches and a host round trip (88 us at batch 1: the
+// reference's sequential loop).  For batches of at most kPersistMaxB candidates without edge checks, on trees
+// below kPersistMaxNodes nodes, ONE CTA runs whole steps back to back inside a single launch: the same device
+// functions as the per-step kernels above (sample, steer, state check, cost, select, commit, rewire), a
+// CTA-wide Nearest and a CTA-wide exact kNN in place of the library launches, barriers in place of kernel
+// boundaries, the MT19937 state kept in shared memory.  The tree it grows is the same, bit for bit
+// (tests/test_gpu_planner.py); the host reads one control block back per launch instead of per step.
+constexpr int kPersistMaxB = 8;
+constexpr int kPersistMaxNodes = 16384;
+constexpr int kPersistThreads = 1024;
+
+struct PersistCtl {
+    long long n;          // tree size (in / out)
+    long long steps;      // steps run by this launch (out)
+    long long goal;       // goal candidate of the last step, or -1 (out)
+    long long stats[5];   // sums over the launch: rejected by state / by edge, parent improved, rewired, in-band events
+    long long unique;     // distinct table samples of the last step
+};
+
+// Nearest (MS:138-154) over the whole tree for one query: every thread of the CTA calls this
+__device__ void nearest_cta(const PlanDev& d, const float* q, int32_t* out_i, float* s_f, int32_t* s_i) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float qx = q[0], qy = q[1], qz = q[2];
+    float bf = __uint_as_float(kInfBits);
+    int32_t bi = -1;
+    for (int64_t i = tid; i < d.n; i += blockDim.x) {           // ascending: `<=` keeps the last index of equal Norms
+        const float f = norm_ref(d.x[i], d.y[i], d.z[i], qx, qy, qz);
+        if (f <= bf) { bf = f; bi = (int32_t)i; }
+    }
+    auto better = [](float of, int32_t oi, float f, int32_t i) { return oi >= 0 && (i < 0 || of < f || (of == f && oi > i)); };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float of = __shfl_xor_sync(kFull, bf, o);
+        const int32_t oi = __shfl_xor_sync(kFull, bi, o);
+        if (better(of, oi, bf, bi)) { bf = of; bi = oi; }
+    }
+    if (lane == 0) { s_f[warp] = bf; s_i[warp] = bi; }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        bf = lane < nw ? s_f[lane] : __uint_as_float(kInfBits);
+        bi = lane < nw ? s_i[lane] : -1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float of = __shfl_xor_sync(kFull, bf, o);
+            const int32_t oi = __shfl_xor_sync(kFull, bi, o);
+            if (better(of, oi, bf, bi)) { bf = of; bi = oi; }
+        }
+        if (lane == 0) *out_i = bi;
+    }
+    __syncthreads();
+}
+
+// exact kNN of candidate c over the whole tree (libnabo semantics of the planner's call: no self match,
+// no radius limit, (d2, index) order): every thread of the CTA calls this
+__device__ void knn_cta(const PlanDev& d, const int c, float* knn_d2, uint32_t (*sd)[32], uint32_t (*si)[32]) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+    const float qx = d.pnew[3 * c], qy = d.pnew[3 * c + 1], qz = d.pnew[3 * c + 2];
+    const uint32_t sent = kInfBits;                               // bits(FLT_MAX) + 1: every finite d2 is below it
+    WarpList L;
+    L.init(sent);
+    uint32_t tau_d = sent, tau_i = 0u;
+    float tau_f = __uint_as_float(sent);
+    for (int64_t j0 = (int64_t)warp * 32; j0 < d.n; j0 += blockDim.x) {
+        const int64_t j = j0 + lane;
+        const bool valid = j < d.n;
+        const float px = valid ? d.x[j] : 0.f, py = valid ? d.y[j] : 0.f, pz = valid ? d.z[j] : 0.f;
+        const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
+        const float dd = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+        const bool pass = valid && (dd <= tau_f) && (dd > FLT_EPSILON);
+        if (__any_sync(kFull, pass)) {
+            warp_offer(L, pass, __float_as_uint(dd), (uint32_t)j, tau_d, tau_i, d.K, lane);
+            tau_f = __uint_as_float(tau_d);
+        }
+    }
+    sd[warp][lane] = L.d;
+    si[warp][lane] = L.i;
+    __syncthreads();
+    if (warp == 0) {
+        for (int w = 1; w < nw; ++w) {
+            const uint32_t cd = sd[w][lane], ci = si[w][lane];
+            const bool pass = lane < d.K && cd != sent;
+            if (__any_sync(kFull, pass)) warp_offer(L, pass, cd, ci, tau_d, tau_i, d.K, lane);
+        }
+        if (lane < d.K) {
+            const bool empty = L.d == sent;
+            d.knn_idx[(size_t)c * d.K + lane] = empty ? -1 : (int32_t)L.i;
+            knn_d2[(size_t)c * d.K + lane] = empty ? __uint_as_float(kInfBits) : __uint_as_float(L.d);
+        }
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kPersistThreads) plan_persist_kernel(PlanDev d0, float* x, float* y, float* z, float4* f4,
+                                                                       uint32_t* mt_state, const uint32_t* first_words,
+                                                                       float* knn_d2, float* u_dist_unused, int32_t* u_near,
+                                                                       MapView m, LevelGrid dil, int max_steps, long long max_nodes,
+                                                                       PersistCtl* ctl) {
+    __shared__ PlanDev d;
+    __shared__ uint32_t mts[kMtN];
+    __shared__ uint32_t words[kPersistMaxB * 6];
+    __shared__ uint32_t sd[kPersistThreads / 32][32], si[kPersistThreads / 32][32];
+    __shared__ float s_f[32];
+    __shared__ int32_t s_i[32];
+    __shared__ int s_stop;
+    __shared__ long long s_stats[5];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        d = d0;
+        d.n = ctl->n;
+        d.words = words;
+        d.u_near = u_near;
+        for (int i = 0; i < 5; ++i) s_stats[i] = 0;
+    }
+    for (int i = tid; i < kMtN; i += blockDim.x) mts[i] = mt_state[i];
+    int mt_pos = (int)mt_state[kMtN];
+    __syncthreads();
+    const bool rewire = d.p.flags & BGR_PLAN_REWIRE;
+    const int B = d.B, K = d.K, K1 = K + 1;
+    int steps = 0;
+    long long goal = -1, unique = 0;
+    for (; steps < max_steps; ++steps) {
+        if (tid == 0) {
+            s_stop = d.n >= max_nodes;
+            d.have_knn = d.n > K;                                  // MS:1273
+            for (int i = 0; i < 16; ++i) d.counters[i] = 0;
+        }
+        __syncthreads();
+        if (s_stop) break;
+        // sample-stream words of this step (the step the host had prepared ahead comes first)
+        if (steps == 0 && first_words) {
+            for (int i = tid; i < B * d.W; i += blockDim.x) words[i] = first_words[i];
+            __syncthreads();
+        } else {
+            mt_pos = mt_generate(mts, mt_pos, words, B * d.W);
+        }
+        if (warp == 0) plan_sample_body(d, lane, lane);            // B <= 32: one warp
+        __syncthreads();
+        const int nq_u = d.n_fixed + (int)d.counters[10];
+        for (int u = 0; u < nq_u; ++u) nearest_cta(d, d.uq + 3 * u, u_near + u, s_f, s_i);
+        if (tid < B) plan_steer_body(d, tid);
+        __syncthreads();
+        if (warp < B) collide_spheres_warp<1>(m, d.pnew, B, d.p.state_radius, d.hit, d.band, dil, warp, lane);
+        __syncthreads();
+        if ((d.p.flags & BGR_PLAN_DEDUP) && tid < B) plan_dedup_body(d, tid);
+        __syncthreads();
+        if (d.have_knn)
+            for (int c = 0; c < B; ++c)
+                if (!d.hit[c]) knn_cta(d, c, knn_d2, sd, si);      // d.hit[c] is CTA-uniform
+        for (int t = tid; t < B * K1; t += blockDim.x) plan_cost_body(d, t);
+        __syncthreads();
+        if (tid < B) plan_select_body(d, tid);
+        __syncthreads();
+        plan_commit_body(d, x, y, z, f4);
+        __syncthreads();
+        if (rewire && d.have_knn) {
+            for (int t = tid; t < B * K; t += blockDim.x) plan_rewire_propose_body(d, t);
+            __syncthreads();
+            for (int t = tid; t < B * K; t += blockDim.x) plan_rewire_apply_body(d, t);
+            __syncthreads();
+            for (int t = tid; t < B * K; t += blockDim.x) plan_rewire_clear_body(d, t);
+            __syncthreads();
+        }
+        if (tid == 0) {
+            goal = d.counters[1];
+            unique = d.counters[10];
+            d.n += d.counters[0] + (goal >= 0 ? 1 : 0);
+            for (int i = 0; i < 5; ++i) s_stats[i] += d.counters[4 + i];
+            s_stop = goal >= 0;
+        }
+        __syncthreads();
+        if (s_stop) { ++steps; break; }
+    }
+    for (int i = tid; i < kMtN; i += blockDim.x) mt_state[i] = mts[i];
+    if (tid == 0) {
+        mt_state[kMtN] = (uint32_t)mt_pos;
+        ctl->n = d.n;
+        ctl->steps = steps;
+        ctl->goal = goal;
+        ctl->unique = unique;
+        for (int i = 0; i < 5; ++i) ctl->stats[i] = s_stats[i];
+    }
 }
 
 void mt_seed_host(uint32_t* s, uint32_t seed) {               // mtrand.cpp:21-31
@@ -474,6 +674,9 @@ struct bgr_planner {
     int64_t rkey_init = 0;       // entries of rkey already set to ~0
     DevBuf<long long> counters;
     PinBuf host_counters;
+    DevBuf<PersistCtl> pctl;     // control block of the persistent small-batch kernel
+    PinBuf host_pctl;
+    uint64_t n_persist_launches = 0, n_persist_steps = 0;
 };
 
 extern "C" {
@@ -489,6 +692,7 @@ int bgr_planner_destroy(bgr_planner* pl) {
     pl->found.release(); pl->hit.release(); pl->kskip.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
     pl->ok.release(); pl->par.release(); pl->near.release(); pl->knn_idx.release(); pl->parent.release();
     pl->new_index.release(); pl->rkey.release(); pl->counters.release(); pl->host_counters.release();
+    pl->pctl.release(); pl->host_pctl.release();
     delete pl;
     return BGR_OK;
 }
@@ -503,7 +707,7 @@ int bgr_planner_create(const bgr_planner_params* p, bgr_map* map, const float* t
     BGR_ARG(p->batch >= 1 && p->batch <= 65536, "batch must be in 1..65536");
     BGR_ARG(p->mode == BGR_PLAN_MODE_RS || p->mode == BGR_PLAN_MODE_MS, "unknown sampler mode %d", p->mode);
     BGR_ARG(p->mode != BGR_PLAN_MODE_MS || (milestones != nullptr && nm >= 3), "mode MS needs >= 3 milestone points");
-    BGR_ARG((p->flags & ~31u) == 0, "unknown planner flags %u", p->flags);
+    BGR_ARG((p->flags & ~63u) == 0, "unknown planner flags %u", p->flags);
     BGR_ARG(p->eta > 0.f && p->state_radius >= 0 && p->edge_radius >= 0, "bad eta / radii");
     bgr_planner* pl = new bgr_planner;
     pl->p = *p;
@@ -555,18 +759,17 @@ int bgr_planner_nns(bgr_planner* pl, bgr_nns** out) {
 // One step = step_launch (everything enqueued on the planner's stream, counters copied back
 // asynchronously) + step_finish (wait for the stream, host bookkeeping).  bgr_planner_run_many
 // launches the steps of several independent planners before it waits for any of them.
-static int step_launch(bgr_planner* pl) {
+// buffers of a step on a tree that may grow to n_cap nodes during it (capacity only)
+static int step_reserve(bgr_planner* pl, int64_t n_cap) {
     const bgr_planner_params& P = pl->p;
     const int B = P.batch, K = P.k, K1 = K + 1;
     const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
     const int64_t N = bgr_nns_size(pl->nns);
     const bool edge_check = P.flags & BGR_PLAN_EDGE_CHECK, rewire = P.flags & BGR_PLAN_REWIRE;
-    const bool have_knn = N > K;                                               // MS:1273
     cudaStream_t st = pl->stream;
-    BGR_ARG(N + B + 1 < ((int64_t)1 << 31), "tree too large");
-    // capacity for this step's appends (+ the goal node)
-    BGR_CHECK(nns_reserve(pl->nns, N + B + 1));
-    BGR_CHECK(pl->par.reserve(N + B + 1, st, true, N));
+    BGR_ARG(n_cap < ((int64_t)1 << 31), "tree too large");
+    BGR_CHECK(nns_reserve(pl->nns, n_cap));
+    BGR_CHECK(pl->par.reserve(n_cap, st, true, N));
     BGR_CHECK(pl->words.reserve((int64_t)B * W, st, false));
     BGR_CHECK(pl->words2.reserve((int64_t)B * W, st, false));
     BGR_CHECK(pl->prand.reserve(3 * (int64_t)B, st, false));
@@ -599,12 +802,18 @@ static int step_launch(bgr_planner* pl) {
     }
     if (rewire) {
         const int64_t old_cap = pl->rkey.cap;
-        BGR_CHECK(pl->rkey.reserve(N + B + 1, st, true, pl->rkey_init));
+        BGR_CHECK(pl->rkey.reserve(n_cap, st, true, pl->rkey_init));
         if (pl->rkey.cap != old_cap || pl->rkey_init < pl->rkey.cap) {
             BGR_CUDA(cudaMemsetAsync(pl->rkey.p + pl->rkey_init, 0xFF, (size_t)(pl->rkey.cap - pl->rkey_init) * sizeof(unsigned long long), st));
             pl->rkey_init = pl->rkey.cap;
         }
     }
+    return BGR_OK;
+}
+
+// device view of the planner's buffers for a step on the tree of N nodes (call after step_reserve)
+static PlanDev step_view(bgr_planner* pl, int64_t N, uint32_t* words_now) {
+    const bgr_planner_params& P = pl->p;
     PlanDev d;
     d.p = P;
     float *x, *y, *z;
@@ -612,16 +821,34 @@ static int step_launch(bgr_planner* pl) {
     nns_soa(pl->nns, &x, &y, &z, &f4);
     d.x = x; d.y = y; d.z = z;
     d.par = pl->par.p;
-    d.n = N; d.B = B; d.K = K; d.W = W; d.have_knn = have_knn;
-    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
-    uint32_t* words_next = pl->words_cur ? pl->words.p : pl->words2.p;
+    d.n = N; d.B = P.batch; d.K = P.k; d.W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4; d.have_knn = N > P.k;   // MS:1273
     d.words = words_now; d.table = pl->table.p; d.nt = pl->nt; d.milestones = pl->milestones.p;
     d.prand = pl->prand.p; d.pnew = pl->pnew.p; d.found = pl->found.p; d.near = pl->near.p;
     d.hit = pl->hit.p; d.band = pl->band.p; d.knn_idx = pl->knn_idx.p;
     d.e1 = pl->e1.p; d.e2 = pl->e2.p; d.ehit = pl->ehit.p; d.eband = pl->eband.p;
     d.costs = pl->costs.p; d.psis = pl->psis.p; d.psi = pl->psi.p; d.ok = pl->ok.p; d.parent = pl->parent.p; d.new_index = pl->new_index.p;
     d.cost = pl->cost.p; d.rkey = pl->rkey.p; d.counters = pl->counters.p;
-    d.uq = pl->uq.p; d.qslot = pl->qslot.p; d.u_near = pl->u_near.p; d.n_fixed = n_fixed;
+    d.uq = pl->uq.p; d.qslot = pl->qslot.p; d.u_near = pl->u_near.p; d.n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    return d;
+}
+
+static int step_launch(bgr_planner* pl) {
+    const bgr_planner_params& P = pl->p;
+    const int B = P.batch, K = P.k, K1 = K + 1;
+    const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
+    const int64_t N = bgr_nns_size(pl->nns);
+    const bool edge_check = P.flags & BGR_PLAN_EDGE_CHECK, rewire = P.flags & BGR_PLAN_REWIRE;
+    const bool have_knn = N > K;                                               // MS:1273
+    const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    cudaStream_t st = pl->stream;
+    // capacity for this step's appends (+ the goal node)
+    BGR_CHECK(step_reserve(pl, N + B + 1));
+    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
+    uint32_t* words_next = pl->words_cur ? pl->words.p : pl->words2.p;
+    const PlanDev d = step_view(pl, N, words_now);
+    float *x, *y, *z;
+    float4* f4;
+    nns_soa(pl->nns, &x, &y, &z, &f4);
 
     const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);
     BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
@@ -710,6 +937,78 @@ static int step_finish(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     return BGR_OK;
 }
 
+// Small batches on small trees without edge checks: whole steps inside one launch (plan_persist_kernel).
+static bool persist_ok(const bgr_planner* pl) {
+    const bgr_planner_params& P = pl->p;
+    return P.batch <= kPersistMaxB && !(P.flags & (BGR_PLAN_EDGE_CHECK | BGR_PLAN_NO_PERSIST)) &&
+           bgr_nns_size(pl->nns) + 2 * (P.batch + 1) <= kPersistMaxNodes;
+}
+
+// runs up to max_steps steps (fewer when the tree reaches max_nodes / the persistent regime's node limit, or
+// the goal is reached); *steps_done = the number it ran
+static int persist_run(bgr_planner* pl, int64_t max_nodes, int64_t max_steps, int64_t* steps_done) {
+    const bgr_planner_params& P = pl->p;
+    const int B = P.batch;
+    const int64_t N = bgr_nns_size(pl->nns);
+    cudaStream_t st = pl->stream;
+    *steps_done = 0;
+    BGR_CHECK(check_device(map_device(pl->map)));
+    // a launch runs at most as many steps as the reserved capacity can absorb
+    int64_t steps = std::min<int64_t>(max_steps, 4096);
+    steps = std::min<int64_t>(steps, (kPersistMaxNodes - N) / (B + 1));
+    if (steps <= 0) return BGR_OK;
+    BGR_CHECK(step_reserve(pl, N + steps * (B + 1)));
+    BGR_CHECK(pl->pctl.reserve(1, st, false));
+    BGR_CHECK(pl->host_pctl.reserve(sizeof(PersistCtl)));
+    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
+    const PlanDev d = step_view(pl, N, words_now);
+    float *x, *y, *z;
+    float4* f4;
+    nns_soa(pl->nns, &x, &y, &z, &f4);
+    LevelGrid dil;
+    BGR_CHECK(map_sphere_gate(pl->map, P.state_radius, &dil));
+    PersistCtl* hc = (PersistCtl*)pl->host_pctl.p;
+    std::memset(hc, 0, sizeof(PersistCtl));
+    hc->n = N;
+    hc->goal = -1;
+    BGR_CUDA(cudaMemcpyAsync(pl->pctl.p, hc, sizeof(PersistCtl), cudaMemcpyHostToDevice, st));
+    // the map's stream and the planner's are the same stream (bgr_planner_set_stream keeps them so)
+    plan_persist_kernel<<<1, kPersistThreads, 0, st>>>(d, x, y, z, f4, pl->mt_state.p, pl->words_ahead ? words_now : nullptr,
+                                                      pl->knn_d2.p, pl->u_dist.p, pl->u_near.p, map_view(pl->map), dil,
+                                                      (int)steps, (long long)max_nodes, pl->pctl.p);
+    BGR_LAUNCH_CHECK();
+    BGR_CUDA(cudaMemcpyAsync(hc, pl->pctl.p, sizeof(PersistCtl), cudaMemcpyDeviceToHost, st));
+    BGR_CUDA(cudaStreamSynchronize(st));
+    pl->n_persist_launches++;
+    if (hc->steps <= 0) return BGR_OK;                 // nothing ran: the prepared words (if any) are still unused
+    pl->n_persist_steps += (uint64_t)hc->steps;
+    pl->words_ahead = false;                           // consumed by the first step; the kernel left the MT state at the stream position
+    const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    pl->unique_hint = hc->unique + n_fixed;
+    nns_set_size(pl->nns, hc->n);
+    pl->stats[0] += hc->steps;
+    pl->stats[1] += hc->steps * B;
+    for (int i = 0; i < 5; ++i) pl->stats[2 + i] += hc->stats[i];
+    if (hc->goal >= 0) {
+        pl->goal_reached = 1;
+        pl->stats[7] = hc->goal;
+    }
+    *steps_done = hc->steps;
+    return BGR_OK;
+}
+
+// advances the planner: one host-driven step, or a launch of persistent steps where they apply
+static int advance(bgr_planner* pl, int64_t max_nodes, int64_t batches_left, int64_t* steps_done) {
+    if (persist_ok(pl)) {
+        BGR_CHECK(persist_run(pl, max_nodes, batches_left, steps_done));
+        if (*steps_done > 0) return BGR_OK;
+    }
+    BGR_CHECK(step_launch(pl));
+    BGR_CHECK(step_finish(pl, nullptr, nullptr));
+    *steps_done = 1;
+    return BGR_OK;
+}
+
 int bgr_planner_step(bgr_planner* pl, int* n_accepted, int* goal_reached) {
     BGR_ARG(pl != nullptr, "null planner");
     if (n_accepted) *n_accepted = 0;
@@ -743,9 +1042,10 @@ int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t ma
         if (cudaSetDevice(dev) != cudaSuccess) return;
         for (int i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
             bgr_planner* pl = pls[i];
-            for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes; ++b) {
-                int rc = step_launch(pl);
-                if (rc == BGR_OK) rc = step_finish(pl, nullptr, nullptr);
+            for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes;) {
+                int64_t done = 0;
+                const int rc = advance(pl, max_nodes, max_batches - b, &done);
+                b += done;
                 if (rc != BGR_OK) {
                     rcs[(size_t)i] = rc;
                     errs[(size_t)i] = get_error();
@@ -773,8 +1073,11 @@ int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t ma
 
 int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached) {
     BGR_ARG(pl != nullptr, "null planner");
-    for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes; ++b)
-        BGR_CHECK(bgr_planner_step(pl, nullptr, nullptr));
+    for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes;) {
+        int64_t done = 0;
+        BGR_CHECK(advance(pl, max_nodes, max_batches - b, &done));
+        b += done;
+    }
     if (goal_reached) *goal_reached = pl->goal_reached;
     return BGR_OK;
 }
@@ -814,6 +1117,13 @@ int bgr_planner_get_path(bgr_planner* pl, int32_t* path, int64_t* n_out) {   // 
         for (int64_t i = 0; i < len; ++i) path[i] = rev[len - 1 - i];
     }
     *n_out = len;
+    return BGR_OK;
+}
+
+int bgr_planner_persist_stats(bgr_planner* pl, uint64_t out[2]) {
+    BGR_ARG(pl != nullptr && out != nullptr, "bad arguments");
+    out[0] = pl->n_persist_launches;
+    out[1] = pl->n_persist_steps;
     return BGR_OK;
 }
 

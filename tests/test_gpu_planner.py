@@ -256,3 +256,64 @@ def test_config3_shape_parity(bgr, oracle):
     gs = _assert_same_tree(gp, op, False, False)
     assert gs["improved_parent"] > 0 and gs["rejected_state"] > 0 and gs["candidates"] == n_batches * 4096
     assert oracle.pow_sqrt_mismatches() == 0
+
+
+def _same_gpu_trees(a, b):
+    ax, ap = a.tree()
+    bx, bp = b.tree()
+    assert len(a) == len(b)
+    assert np.array_equal(ax.view(np.uint32), bx.view(np.uint32)) and np.array_equal(ap, bp)
+    sa, sb = a.stats(), b.stats()
+    for key in ("batches", "candidates", "rejected_state", "rejected_edge", "improved_parent", "rewired", "in_band", "goal_candidate"):
+        assert sa[key] == sb[key], (key, sa, sb)
+
+
+@pytest.mark.parametrize("mode,k,batch,flags,seed", [(0, 5, 1, 4, 5489), (1, 5, 1, 4, 7), (0, 10, 4, 0, 11), (1, 10, 3, 2, 3),
+                                                     (1, 8, 2, 16 | 2, 5), (0, 5, 1, 8, 1), (1, 16, 4, 2 | 8, 9), (1, 10, 8, 2, 13), (0, 6, 7, 0, 2)])
+def test_persistent_steps_equal_host_driven_steps(bgr, oracle, world, mode, k, batch, flags, seed):
+    """small batches without edge checks run whole steps inside one launch (plan_persist_kernel): the tree, the
+    statistics and the sample stream position are those of the host-driven steps (BGR_PLAN_NO_PERSIST) and of the
+    oracle, also when run() and step() calls are mixed (the step() path prepares the next step's words ahead)."""
+    m, boxes, table, ms = world
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=mode, k=k, batch=batch, flags=flags, seed=seed)
+    Q = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=mode, k=k, batch=batch, flags=flags | bgr.PLAN_NO_PERSIST, seed=seed)
+    a, b = bgr.Planner(P, m, table, ms), bgr.Planner(Q, m, table, ms)
+    op = oracle.Planner(P, boxes, table, ms)
+    ga, gb, go = a.run(150, 400), b.run(150, 400), op.run(150, 400)
+    assert a.persist_stats()["launches"] >= 1 and a.persist_stats()["steps"] == a.stats()["batches"]
+    assert b.persist_stats()["launches"] == 0
+    assert ga == gb
+    _same_gpu_trees(a, b)
+    if a.stats()["in_band"] == 0:
+        _assert_same_tree(a, op, ga, go)
+    # mixed: single steps (host-driven, words prepared ahead), then persistent runs again
+    for _ in range(7):
+        if not ga:
+            ga = a.step()[1]
+            gb = b.step()[1]
+    if not ga:
+        ga, gb = a.run(400, 300), b.run(400, 300)
+        assert ga == gb
+    for _ in range(3):
+        if not ga:
+            ga = a.step()[1]
+            gb = b.step()[1]
+    if not ga:
+        ga, gb = a.run(len(a) + 40, 10_000), b.run(len(b) + 40, 10_000)
+    assert ga == gb
+    _same_gpu_trees(a, b)
+    assert 0 < a.persist_stats()["steps"] <= a.stats()["batches"]
+
+
+def test_persistent_steps_reach_the_goal(bgr, oracle, world):
+    """batch 1 to the goal: goal cut, goal node and path as the host-driven loop's"""
+    m, boxes, table, ms = world
+    for seed in (3, 4):
+        P = bgr.PlannerParams((0.2, 0.2, 0.2), (0.6, 0.6, 0.6), mode=bgr.PLAN_MODE_RS, k=5, batch=1, flags=0, seed=seed, goal_tol=0.2)
+        Q = bgr.PlannerParams((0.2, 0.2, 0.2), (0.6, 0.6, 0.6), mode=bgr.PLAN_MODE_RS, k=5, batch=1, flags=bgr.PLAN_NO_PERSIST, seed=seed, goal_tol=0.2)
+        a, b = bgr.Planner(P, m, table, ms), bgr.Planner(Q, m, table, ms)
+        ga, gb = a.run(4000, 20_000), b.run(4000, 20_000)
+        assert ga and gb
+        _same_gpu_trees(a, b)
+        assert np.array_equal(a.path(), b.path())
+        assert a.persist_stats()["launches"] >= 1
