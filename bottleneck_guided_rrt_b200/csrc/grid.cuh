@@ -665,7 +665,7 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
 }
 
 template <bool PILED>
-__global__ void __launch_bounds__(kGridWarps * 32, 5) grid_knn_kernel(GridKnnArgs a) {
+__global__ void __launch_bounds__(kGridWarps * 32, PILED ? 4 : 5) grid_knn_kernel(GridKnnArgs a) {
     __shared__ unsigned long long cand[kGridWarps][kFastCap];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t qi = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;

@@ -111,12 +111,14 @@ int launch_nearest(bgr_nns* h, NearestArgs a, int chunks) {
 // queries per warp and node chunks so that the grid fills the machine for >= ~2 waves
 void plan_scan(int64_t nq, int64_t n, int* R, int* chunks, int64_t* chunk_nodes) {
     const int sms = num_sms();
+    // (measured and dropped: preferring R = 4 with many node chunks for the planner's ~800-query Nearest — every
+    // chunk restarts its running bound, the f32 filter passes more nodes to the fp64 path: cfg 3 0.40 -> 0.48 s)
     int r = 8;
     while (r > 1 && div_up(nq, (int64_t)kConsumerWarps * r) < 2 * sms) r >>= 1;
     const int64_t qblocks = div_up(nq, (int64_t)kConsumerWarps * r);
     const int64_t tiles = div_up(n > 0 ? n : 1, kTile);
-    int64_t c = 1;
     const int64_t resident = 3LL * sms;
+    int64_t c = 1;
     if (qblocks < 2 * resident) c = div_up(2 * resident, qblocks);
     c = std::min<int64_t>(c, std::max<int64_t>(1, tiles / 4));
     c = std::min<int64_t>(c, 64);

@@ -467,7 +467,7 @@ __global__ void plan_rewire_clear_kernel(PlanDev d) { plan_rewire_clear_body(d, 
 // boundaries, the MT19937 state kept in shared memory.  The tree it grows is the same, bit for bit
 // (tests/test_gpu_planner.py); the host reads one control block back per launch instead of per step.
 constexpr int kPersistMaxB = 8;
-constexpr int kPersistMaxNodes = 16384;
+constexpr int kPersistMaxNodes = 65536;
 constexpr int kPersistThreads = 1024;
 
 struct PersistCtl {

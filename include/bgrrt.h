@@ -302,7 +302,7 @@ int bgr_map_find_labels(bgr_map* map, const double* path_3xP, int64_t p, double 
                                  * point and, against one snapshot, the same candidate; keep the first of each and
                                  * reject the copies (counted in rejected_state) instead of appending coincident nodes */
 #define BGR_PLAN_NO_PERSIST 32u  /* measurement / test aid: never run steps in the persistent small-batch kernel (batch <= 8,
-                                 * no edge checks, tree < 16,384 nodes: whole steps inside one launch, same tree bit for bit) */
+                                 * no edge checks, tree < 65,536 nodes: whole steps inside one launch, same tree bit for bit) */
 #define BGR_PLAN_MODE_RS 0      /* rrt_star.cpp sampler: rand_chance > goal_chance ? table : goal */
 #define BGR_PLAN_MODE_MS 1      /* rrt_star_milestones.cpp sampler: >0.8 table, (0.5,0.8) goal, else milestone[int z] */
 

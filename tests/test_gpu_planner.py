@@ -317,3 +317,16 @@ def test_persistent_steps_reach_the_goal(bgr, oracle, world):
         _same_gpu_trees(a, b)
         assert np.array_equal(a.path(), b.path())
         assert a.persist_stats()["launches"] >= 1
+
+
+def test_persistent_steps_large_tree(bgr, oracle, world):
+    """batch 4 to 24,000 nodes: past the size where the host-driven path switches from the plain scans to the grid
+    index (16,384 nodes), the persistent kernel keeps scanning — same tree"""
+    m, boxes, table, ms = world
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_RS, k=10, batch=4, flags=bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL, seed=21)
+    Q = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_RS, k=10, batch=4, flags=bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL | bgr.PLAN_NO_PERSIST, seed=21)
+    a, b = bgr.Planner(P, m, table, ms), bgr.Planner(Q, m, table, ms)
+    a.run(24_000)
+    b.run(24_000)
+    _same_gpu_trees(a, b)
+    assert a.persist_stats()["steps"] == a.stats()["batches"] and a.stats()["rewired"] > 0
