@@ -216,6 +216,15 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def per_rank(x):
+        """the value of every rank, in rank order"""
+        if dist is None:
+            return [x]
+        t = torch.zeros(world, dtype=torch.float64, device=dev)
+        t[rank] = x
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(v) for v in t.tolist()]
+
     def flush():
         with torch.cuda.stream(stream):
             flush_buf.fill_(rank & 0xFF)
@@ -225,7 +234,7 @@ def run_ours(args):
            "parity_note": "oracle parity is UNPINNED against the real libnabo / FCL / octomap (absent offline); see DESIGN.md section 0"}
     sampler = ClockSampler(local)
     ctx = dict(torch=torch, B=B, synth=synth, L=L, pk=pk, dev=dev, stream=stream, flush=flush, barrier=barrier,
-               max_over_ranks=max_over_ranks, rank=rank, world=world, dist=dist, args=args)
+               max_over_ranks=max_over_ranks, per_rank=per_rank, rank=rank, world=world, dist=dist, args=args)
 
     with torch.cuda.stream(stream):
         # on-box L2 read bandwidth for the access shapes of the three L2-resident kernels (roofline.l2 peaks)
@@ -285,7 +294,33 @@ def knn_section(c, out):
     def knn_step():
         nns_t.knn(d_q, K_NN, indices=d_idx, dists2=d_d2)
 
-    knn_ms = max_over_ranks(timed_steps(torch, stream, knn_step, args.steps, args.warmup, flush, barrier))
+    knn_ms_mine = timed_steps(torch, stream, knn_step, args.steps, args.warmup, flush, barrier)
+    knn_ms = max_over_ranks(knn_ms_mine)
+    knn_ms_ranks = [v / args.steps for v in c["per_rank"](knn_ms_mine)]
+    # the exhaustive scan of the same workload (knn_brute_kernel: the FP32-pipe-bound kernel of north_star (3)):
+    # 3 timed steps of ~16 ms, results compared with the grid search's
+    brute = None
+    if args.method != "brute" and not args.skip_brute:
+        nns_t.set_method(B.METHOD_BRUTE)
+        b_idx, b_d2 = torch.empty_like(d_idx), torch.empty_like(d_d2)
+
+        def brute_step():
+            nns_t.knn(d_q, K_NN, indices=b_idx, dists2=b_d2)
+
+        brute_ms = max_over_ranks(timed_steps(torch, stream, brute_step, 3, 3, flush, barrier, 0.05)) / 3
+        nns_t.set_method(method)
+        knn_step()
+        stream.synchronize()
+        fp32_peak_b = 148 * FP32_NOFMA_LANES * pk["sm_max_mhz"] * 1e6 / 1e12
+        ach_b = 8.0 * N_NODES * N_QUERIES / (brute_ms * 1e-3) / 1e12
+        brute = {"value": world * N_QUERIES / (brute_ms * 1e-3), "unit": "queries/s", "ms_per_step": brute_ms, "steps": 3,
+                 "identical_to_grid_search": bool(torch.equal(b_idx, d_idx) and torch.equal(b_d2.view(torch.int32), d_d2.view(torch.int32))),
+                 "roofline": {"bound": "fp32", "kernel": "knn_brute_kernel", "achieved": ach_b, "peak": fp32_peak_b, "unit": "TFLOP/s",
+                              "frac": ach_b / fp32_peak_b, "flops_per_pair": 8, "pairs_per_step": float(N_NODES) * N_QUERIES,
+                              "note": "8 non-FMA FP32 operations per (query, node) pair is the algorithmic work of the exact distance "
+                                      "(SURVEY 8(d)); the kernel spends most pairs on a 3-FFMA2 conservative filter (two pairs per issue "
+                                      "slot) and the exact arithmetic on the survivors, so the fraction is against the non-FMA peak of "
+                                      "148 SM x 128 lanes x sm_max_mhz"}}
     l1 = L.bgr_launch_count()                       # launches per step, counted on one isolated step
     knn_step()
     stream.synchronize()
@@ -319,14 +354,17 @@ def knn_section(c, out):
     kname = "grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel"
     d2h_bytes = int(8 * K_NN * N_QUERIES)
     out.update({
-        "value": value, "ms_per_step": ms_per_step,
+        "value": value, "ms_per_step": ms_per_step, "ms_per_step_per_rank": knn_ms_ranks, "brute_scan": brute,
         "config": {"workload": "configs[1]: batched kNN, 1,000,000-node 3-D tree (U[0,25.6)^3, MT19937 seed 2), "
                                "65,536 queries/GPU (seed 3+rank), k=16, eps=0, exact, method=%s" % args.method,
                    "nodes": N_NODES, "queries_per_gpu": N_QUERIES, "k": K_NN,
                    "l2": "flushed between steps (256 MiB fill on the same stream, untimed)",
                    "prewarm": "0.25 s untimed clock ramp before the W warm-up steps; the K timed steps are enqueued "
                               "behind a 1.5 ms spin kernel (no host launch gap inside an event pair)",
-                   "index_build_ms": build_ms, "parallelism": "replicas x%d" % world},
+                   "index_build_ms": build_ms, "parallelism": "replicas x%d" % world,
+                   "per_rank_note": "every rank searches its own query batch (seed 3 + rank); the kernel time depends on the batch by "
+                                    "+-4 % (profiles/r2_knn_query_order_and_bounds.txt: seeds 3..6 on one GPU), so the max over ranks "
+                                    "at N > 1 sits a few % above the N = 1 figure with no collective in the path"},
         "e2e": {"value": world * N_QUERIES / (e2e_ms / args.steps * 1e-3), "unit": "queries/s",
                 "ms_per_step": e2e_ms / args.steps,
                 "h2d_bytes_per_step": int(12 * N_QUERIES), "d2h_bytes_per_step": d2h_bytes,
@@ -589,7 +627,8 @@ def planner_bench(c):
         return {"nodes": len(pl), "seconds": el, "nodes_per_s": world * (len(pl) - n0) / el,
                 "candidates_per_s": world * st["candidates"] / el, "batches": st["batches"], "batch": batch, "k": k,
                 "rejected_state": st["rejected_state"], "rejected_edge": st["rejected_edge"], "rewired": st["rewired"],
-                "in_band": st["in_band"], "map": "%d^3 @0.05 m, %d leaf boxes" % (n_map, len(boxes))}
+                "in_band": st["in_band"], "map": "%d^3 @0.05 m, %d leaf boxes" % (n_map, len(boxes)),
+                "steps_in_persistent_kernel": pl.persist_stats()["steps"], "us_per_step": 1e6 * el / max(st["batches"], 1)}
 
     g64 = (3.0, 3.0, 3.0)
     res["config0_rrtstar_64_batch1"] = grow(64, 1, 3, 6, B.PLAN_MODE_RS, 10, 1, B.PLAN_QUIRKS, 5000, None, g64)
@@ -676,7 +715,9 @@ def planner_bench(c):
         "workload": "configs[4](i): %d independent (start, goal) pairs per GPU (random free points, sphere r = 0.1), planner seeds "
                     "100 + 512 rank + q, MS sampler with the 3 door-centre milestones, edge checks + rewiring + BGR_PLAN_DEDUP; bgr_planner_run_many, "
                     "%d queries in flight (one stream + map handle each)" % (QUERIES_PER_GPU, nconc)}
-    res["note"] = ("wall clock of bgr_planner_run (host loop + device kernels, one sync per batch); nodes_per_s is the "
+    res["note"] = ("wall clock of bgr_planner_run; batches of <= 8 candidates without edge checks run whole steps inside one "
+                   "launch (plan_persist_kernel, steps_in_persistent_kernel), the others are host-driven (~30 launches and one "
+                   "sync per batch); nodes_per_s is the "
                    "aggregate over %d independent planning queries (one per GPU)" % world)
     return res
 
@@ -849,6 +890,7 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-sharded", action="store_true")
     ap.add_argument("--skip-planner", action="store_true")
+    ap.add_argument("--skip-brute", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

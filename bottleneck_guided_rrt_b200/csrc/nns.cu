@@ -384,7 +384,7 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
     const bool want_stats = (h->create_flags & BGR_TOUCH_STATISTICS) && touched;
     int chunks = 1;
     if ((method == BGR_METHOD_GRID || method == BGR_METHOD_GRID_GENERAL) && !want_stats && !pipe_disabled())
-        chunks = (int)std::min<int64_t>(4, nq / 8192);
+        chunks = (int)std::min<int64_t>(d2 ? 4 : 2, nq / 8192);   // measured (profiles/r2_e2e_chunks.txt): 4 with both result arrays, 2 with indices only
     if (const char* e = getenv("BGR_KNN_CHUNKS")) chunks = std::max(1, std::min(atoi(e), (int)CopyPipe::kMaxChunks));   // measurement aid
     if (chunks <= 1) {
         BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
