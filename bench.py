@@ -670,34 +670,28 @@ def planner_bench(c):
     assert len(free) >= 2 * QUERIES_PER_GPU
     table = synth.points(9 + rank, 200_000, 12.8)
 
-    def run_queries(q0, q1, seq=False):
-        """queries [q0, q1) in groups of nconc through bgr_planner_run_many (or one after the other)"""
-        reached, nodes = [], []
-        for g0 in range(q0, q1, nconc):
-            pls = []
-            for j, qi in enumerate(range(g0, min(q1, g0 + nconc))):
-                P = B.PlannerParams(tuple(free[2 * qi]), tuple(free[2 * qi + 1]), mode=B.PLAN_MODE_MS, k=16, batch=1024,
-                                    flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | B.PLAN_DEDUP, seed=100 + rank * QUERIES_PER_GPU + qi)
-                pls.append(B.Planner(P, qmaps[j], table, msq, stream=qstreams[j].cuda_stream))
-            if seq:
-                fl = [p.run(QUERY_MAX_NODES) for p in pls]
-            else:
-                fl = B.Planner.run_many(pls, QUERY_MAX_NODES)
-            torch.cuda.synchronize()
-            reached += [bool(f) for f in fl]
-            nodes += [len(p) for p in pls]
-            del pls
-        return reached, nodes
+    # one planner per worker (map handle + stream each), re-armed for every query (bgr_planner_reset): a worker takes
+    # the next (start, goal, seed) as soon as its query ends (bgr_planner_run_queue) — no query waits for the slowest
+    # of a group, no buffer is allocated or freed while queries run
+    P0 = B.PlannerParams(tuple(free[0]), tuple(free[1]), mode=B.PLAN_MODE_MS, k=16, batch=1024,
+                         flags=B.PLAN_EDGE_CHECK | B.PLAN_REWIRE | B.PLAN_DEDUP, seed=100)
+    workers = [B.Planner(P0, qmaps[j], table, msq, stream=qstreams[j].cuda_stream) for j in range(nconc)]
+    starts, goals = free[0:2 * QUERIES_PER_GPU:2], free[1:2 * QUERIES_PER_GPU:2]
+    seeds = np.arange(QUERIES_PER_GPU, dtype=np.uint32) + np.uint32(100 + rank * QUERIES_PER_GPU)
 
-    run_queries(0, nconc)                                   # warm-up: allocations, first launches
-    torch.cuda.synchronize()
+    def run_queries(q0, q1, nworkers):
+        r_, n_ = B.Planner.run_queue(workers[:nworkers], starts[q0:q1], goals[q0:q1], seeds[q0:q1], QUERY_MAX_NODES)
+        torch.cuda.synchronize()
+        return [bool(v) for v in r_], [int(v) for v in n_]
+
+    run_queries(0, 2 * nconc, nconc)                        # warm-up: allocations, first launches
     barrier()
     t0 = time.perf_counter()
-    reached, nodes = run_queries(0, QUERIES_PER_GPU)
+    reached, nodes = run_queries(0, QUERIES_PER_GPU, nconc)
     el = max_over_ranks(time.perf_counter() - t0)
     barrier()
     t0 = time.perf_counter()
-    run_queries(0, 2 * nconc, seq=True)
+    run_queries(0, 2 * nconc, 1)
     el_seq = max_over_ranks(time.perf_counter() - t0)
     ok_nodes = [n for n, r in zip(nodes, reached) if r]
     n_ok = int(max_over_ranks(float(sum(reached))))        # max over ranks would overstate: report rank 0 and say so
@@ -713,8 +707,8 @@ def planner_bench(c):
         "map": "256^3 @0.05 m, 3 walls with one %.2f m door each, %.1f%% occupied, %d leaf boxes, map seed 5 + rank"
                % (0.05 * QUERY_DOOR_CELLS, 100 * occq.mean(), len(boxesq)),
         "workload": "configs[4](i): %d independent (start, goal) pairs per GPU (random free points, sphere r = 0.1), planner seeds "
-                    "100 + 512 rank + q, MS sampler with the 3 door-centre milestones, edge checks + rewiring + BGR_PLAN_DEDUP; bgr_planner_run_many, "
-                    "%d queries in flight (one stream + map handle each)" % (QUERIES_PER_GPU, nconc)}
+                    "100 + 512 rank + q, MS sampler with the 3 door-centre milestones, edge checks + rewiring + BGR_PLAN_DEDUP; "
+                    "bgr_planner_run_queue, %d worker planners (one host thread, stream and map handle each), re-armed per query" % (QUERIES_PER_GPU, nconc)}
     res["note"] = ("wall clock of bgr_planner_run; batches of <= 8 candidates without edge checks run whole steps inside one "
                    "launch (plan_persist_kernel, steps_in_persistent_kernel), the others are host-driven (~30 launches and one "
                    "sync per batch); nodes_per_s is the "

@@ -115,6 +115,8 @@ def lib():
     L.bgr_planner_get_path.argtypes = [vp, vp, vp]
     L.bgr_planner_stats.argtypes = [vp, vp]
     L.bgr_planner_persist_stats.argtypes = [vp, vp]
+    L.bgr_planner_reset.argtypes = [vp, vp, vp, u32]
+    L.bgr_planner_run_queue.argtypes = [vp, i32, vp, vp, vp, i64, i64, i64, vp, vp]
     L.bgr_planner_nns.argtypes = [vp, vp]
     L.bgr_planner_destroy.argtypes = [vp]
     _LIB = L
@@ -643,6 +645,27 @@ class Planner:
         flags = (C.c_int * n)()
         _check(lib().bgr_planner_run_many(arr, n, max_nodes, max_batches, flags))
         return [bool(f) for f in flags]
+
+    def reset(self, start, goal, seed):
+        """bgr_planner_reset: same map / table / milestones, new query"""
+        a = np.ascontiguousarray(start, dtype=np.float32)
+        b = np.ascontiguousarray(goal, dtype=np.float32)
+        _check(lib().bgr_planner_reset(self._h, _ptr(a), _ptr(b), int(seed)))
+
+    @staticmethod
+    def run_queue(planners, starts, goals, seeds, max_nodes, max_batches=1 << 40):
+        """bgr_planner_run_queue: len(starts) queries through the given planners (one worker thread each).
+        Returns (reached (Q,) bool, nodes (Q,) int64)."""
+        n = len(planners)
+        arr = (C.c_void_p * n)(*[p._h for p in planners])
+        st = np.ascontiguousarray(starts, dtype=np.float32).reshape(-1, 3)
+        gl = np.ascontiguousarray(goals, dtype=np.float32).reshape(-1, 3)
+        sd = np.ascontiguousarray(seeds, dtype=np.uint32)
+        nq = st.shape[0]
+        reached = np.zeros(nq, dtype=np.int32)
+        nodes = np.zeros(nq, dtype=np.int64)
+        _check(lib().bgr_planner_run_queue(arr, n, _ptr(st), _ptr(gl), _ptr(sd), nq, max_nodes, max_batches, _ptr(reached), _ptr(nodes)))
+        return reached.astype(bool), nodes
 
     def tree(self):
         n = len(self)

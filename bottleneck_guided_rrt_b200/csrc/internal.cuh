@@ -7,6 +7,7 @@ namespace bgr {
 int nns_reserve(bgr_nns* h, int64_t n);                       // capacity only, NaN padded, size unchanged
 void nns_soa(bgr_nns* h, float** x, float** y, float** z, float4** f4);   // current arrays (valid until the next reserve)
 void nns_set_size(bgr_nns* h, int64_t n);                     // after a device-side append
+int nns_reset(bgr_nns* h);                                    // empty store again (buffers kept, NaN padding restored, index dropped)
 cudaStream_t nns_stream(bgr_nns* h);
 // Nearest over a query array whose valid length (count_base + *d_count <= nq_cap) is known only on the device
 int nns_nearest_counted(bgr_nns* h, const float* d_q, int64_t nq_cap, int64_t nq_hint, const long long* d_count,

@@ -195,6 +195,21 @@ void nns_soa(bgr_nns* h, float** x, float** y, float** z, float4** f4) {
     if (f4) *f4 = h->f4.p;
 }
 void nns_set_size(bgr_nns* h, int64_t n) { h->n = n; }
+int nns_reset(bgr_nns* h) {
+    // back to an empty store: the scans read whole 1,024-node tiles and rely on NaN padding past the last node
+    const int64_t used = std::min<int64_t>(h->x.cap, round_up(h->n > 0 ? h->n : 1, kTile));
+    if (h->x.p && used > 0) {
+        BGR_CUDA(cudaMemsetAsync(h->x.p, 0xFF, (size_t)used * sizeof(float), h->stream));
+        BGR_CUDA(cudaMemsetAsync(h->y.p, 0xFF, (size_t)used * sizeof(float), h->stream));
+        BGR_CUDA(cudaMemsetAsync(h->z.p, 0xFF, (size_t)used * sizeof(float), h->stream));
+        BGR_CUDA(cudaMemsetAsync(h->f4.p, 0xFF, (size_t)used * sizeof(float4), h->stream));
+    }
+    h->n = 0;
+    h->grid.n_indexed = 0;
+    h->grid.crowd = 0.0;
+    h->tail_work = 0.0;
+    return BGR_OK;
+}
 cudaStream_t nns_stream(bgr_nns* h) { return h->stream; }
 }  // namespace bgr
 

@@ -1071,6 +1071,78 @@ int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t ma
     return BGR_OK;
 }
 
+int bgr_planner_reset(bgr_planner* pl, const float start[3], const float goal[3], uint32_t seed) {
+    BGR_ARG(pl != nullptr && start != nullptr && goal != nullptr, "bad arguments");
+    cudaStream_t st = pl->stream;
+    BGR_CUDA(cudaStreamSynchronize(st));
+    for (int a = 0; a < 3; ++a) { pl->p.start[a] = start[a]; pl->p.goal[a] = goal[a]; }
+    pl->p.seed = seed;
+    BGR_CHECK(nns_reset(pl->nns));
+    BGR_CHECK(bgr_nns_append(pl->nns, start, 1));                               // V = [[xs,ys,zs,-1]] MS:1152-1156
+    uint32_t s[kMtN + 1];
+    mt_seed_host(s, seed);
+    const int32_t root_parent = -1;
+    BGR_CUDA(cudaMemcpyAsync(pl->mt_state.p, s, sizeof(s), cudaMemcpyHostToDevice, st));
+    BGR_CUDA(cudaMemcpyAsync(pl->par.p, &root_parent, sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    BGR_CUDA(cudaStreamSynchronize(st));                                        // s / root_parent are stack temporaries
+    pl->goal_reached = 0;
+    for (int i = 0; i < 7; ++i) pl->stats[i] = 0;
+    pl->stats[7] = -1;
+    pl->words_cur = 0;
+    pl->words_ahead = false;
+    pl->pending_n = 0;
+    pl->unique_hint = 0;
+    return BGR_OK;
+}
+
+int bgr_planner_run_queue(bgr_planner** pls, int n_workers, const float* starts, const float* goals, const uint32_t* seeds,
+                          int64_t nq, int64_t max_nodes, int64_t max_batches, int* out_reached, int64_t* out_nodes) {
+    BGR_ARG(pls != nullptr && n_workers >= 1 && nq >= 0 && (nq == 0 || (starts && goals && seeds)), "bad arguments");
+    for (int i = 0; i < n_workers; ++i) {
+        BGR_ARG(pls[i] != nullptr, "null planner %d", i);
+        for (int j = 0; j < i; ++j)
+            BGR_ARG(pls[i] != pls[j] && pls[i]->map != pls[j]->map && pls[i]->stream != pls[j]->stream,
+                    "planners %d and %d share a handle, a map or a stream", j, i);
+    }
+    int dev = 0;
+    BGR_CUDA(cudaGetDevice(&dev));
+    std::atomic<int64_t> next{0};
+    std::vector<int> rcs((size_t)n_workers, BGR_OK);
+    std::vector<std::string> errs((size_t)n_workers);
+    auto worker = [&](int w) {
+        if (cudaSetDevice(dev) != cudaSuccess) return;
+        bgr_planner* pl = pls[w];
+        for (int64_t q = next.fetch_add(1); q < nq; q = next.fetch_add(1)) {
+            int rc = bgr_planner_reset(pl, starts + 3 * q, goals + 3 * q, seeds[q]);
+            for (int64_t b = 0; rc == BGR_OK && b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes;) {
+                int64_t done = 0;
+                rc = advance(pl, max_nodes, max_batches - b, &done);
+                b += done;
+            }
+            if (rc != BGR_OK) {
+                rcs[(size_t)w] = rc;
+                errs[(size_t)w] = get_error();
+                return;
+            }
+            if (out_reached) out_reached[q] = pl->goal_reached;
+            if (out_nodes) out_nodes[q] = bgr_nns_size(pl->nns);
+        }
+    };
+    if (n_workers == 1) {
+        worker(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < n_workers; ++t) th.emplace_back(worker, t);
+        for (auto& t : th) t.join();
+    }
+    for (int i = 0; i < n_workers; ++i)
+        if (rcs[(size_t)i] != BGR_OK) {
+            set_error("worker %d: %s", i, errs[(size_t)i].c_str());
+            return rcs[(size_t)i];
+        }
+    return BGR_OK;
+}
+
 int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int* goal_reached) {
     BGR_ARG(pl != nullptr, "null planner");
     for (int64_t b = 0; b < max_batches && !pl->goal_reached && bgr_nns_size(pl->nns) < max_nodes;) {

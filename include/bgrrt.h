@@ -340,6 +340,17 @@ int bgr_planner_run(bgr_planner* pl, int64_t max_nodes, int64_t max_batches, int
  * the one bgr_planner_run would grow.  The planners must not share a stream or a map handle.
  * goal_reached: n flags (may be NULL). */
 int bgr_planner_run_many(bgr_planner** pls, int n, int64_t max_nodes, int64_t max_batches, int* goal_reached);
+/* Re-arm a planner for another query on the same map / sample table / milestones: the tree becomes the single
+ * root `start`, the sample stream restarts from `seed`, the statistics are cleared; every buffer is kept.  The
+ * tree then grown is the one a freshly created planner with these parameters grows. */
+int bgr_planner_reset(bgr_planner* pl, const float start[3], const float goal[3], uint32_t seed);
+/* nq independent queries through n_workers planners (one host thread each; the planners must not share a map or a
+ * stream): a worker re-arms its planner with the next (start, goal, seed) of the list as soon as it finishes one,
+ * so no query waits for the slowest of a group.  starts / goals: 3 x Q column-major.  out_reached[q] / out_nodes[q]:
+ * goal flag and tree size of query q (either may be NULL). */
+int bgr_planner_run_queue(bgr_planner** pls, int n_workers, const float* starts_3xQ, const float* goals_3xQ,
+                          const uint32_t* seeds, int64_t nq, int64_t max_nodes, int64_t max_batches, int* out_reached,
+                          int64_t* out_nodes);
 int64_t bgr_planner_size(const bgr_planner* pl);
 /* tree download: xyz as 3 x N column-major (x0,y0,z0,...), parent[0] = -1 */
 int bgr_planner_get_tree(bgr_planner* pl, float* xyz_3xN, int32_t* parent);

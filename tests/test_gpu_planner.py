@@ -330,3 +330,45 @@ def test_persistent_steps_large_tree(bgr, oracle, world):
     b.run(24_000)
     _same_gpu_trees(a, b)
     assert a.persist_stats()["steps"] == a.stats()["batches"] and a.stats()["rewired"] > 0
+
+
+def test_reset_and_query_queue_equal_fresh_planners(bgr, oracle, world):
+    """bgr_planner_reset re-arms a planner for another query (same map / table / milestones): the tree it then grows
+    is the one a freshly created planner grows, bit for bit — host-driven batches, persistent small batches, and
+    through bgr_planner_run_queue (workers take the next query as they finish one)."""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    m, boxes, table, ms = world
+    starts = np.array([[0.2, 0.2, 0.2], [0.3, 2.9, 0.4], [0.25, 1.5, 2.8], [0.5, 0.5, 3.0], [0.3, 0.3, 1.5], [0.2, 3.0, 3.0]], dtype=np.float32)
+    goals = np.array([[3.0, 3.0, 3.0], [2.9, 0.3, 2.9], [3.0, 1.6, 0.3], [2.8, 2.8, 0.3], [3.0, 0.4, 1.4], [3.0, 0.2, 0.2]], dtype=np.float32)
+    seeds = np.array([11, 12, 13, 14, 15, 16], dtype=np.uint32)
+    for batch, k, flags, cap in ((64, 10, 3, 3000), (2, 8, 2, 600)):
+        fresh = []
+        for q in range(len(seeds)):
+            P = bgr.PlannerParams(tuple(starts[q]), tuple(goals[q]), mode=bgr.PLAN_MODE_MS, k=k, batch=batch, flags=flags, seed=int(seeds[q]))
+            pl = bgr.Planner(P, m, table, ms)
+            g = pl.run(cap, 200)
+            fresh.append((g, pl.tree(), pl.stats()))
+        # one planner, re-armed for every query (after a different query ran on it)
+        P0 = bgr.PlannerParams((1.0, 1.0, 1.0), (2.0, 2.0, 2.0), mode=bgr.PLAN_MODE_MS, k=k, batch=batch, flags=flags, seed=99)
+        pl = bgr.Planner(P0, m, table, ms)
+        pl.run(cap // 2, 50)
+        for q in range(len(seeds)):
+            pl.reset(starts[q], goals[q], seeds[q])
+            assert len(pl) == 1
+            g = pl.run(cap, 200)
+            x, par = pl.tree()
+            assert g == fresh[q][0] and np.array_equal(x.view(np.uint32), fresh[q][1][0].view(np.uint32)) and np.array_equal(par, fresh[q][1][1])
+            assert pl.stats() == fresh[q][2]
+        # the queue: 2 workers (own map handle + stream each), 6 queries
+        streams = [torch.cuda.Stream() for _ in range(2)]
+        maps = []
+        for s_ in streams:
+            mm = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64), stream=s_.cuda_stream)
+            mm.set_boxes(boxes)
+            maps.append(mm)
+        workers = [bgr.Planner(P0, maps[i], table, ms, stream=streams[i].cuda_stream) for i in range(2)]
+        reached, nodes = bgr.Planner.run_queue(workers, starts, goals, seeds, cap, 200)
+        torch.cuda.synchronize()
+        for q in range(len(seeds)):
+            assert bool(reached[q]) == fresh[q][0] and int(nodes[q]) == len(fresh[q][1][1]), (q, reached, nodes)
