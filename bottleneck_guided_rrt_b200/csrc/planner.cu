@@ -563,7 +563,7 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persist_kernel(PlanDev d
     __shared__ uint32_t sd[kPersistThreads / 32][32], si[kPersistThreads / 32][32];
     __shared__ float s_f[32];
     __shared__ int32_t s_i[32];
-    __shared__ int s_stop;
+    __shared__ int s_full, s_goal_hit;   // two flags: each is rewritten only many barriers after its last read
     __shared__ long long s_stats[5];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) {
@@ -582,12 +582,12 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persist_kernel(PlanDev d
     long long goal = -1, unique = 0;
     for (; steps < max_steps; ++steps) {
         if (tid == 0) {
-            s_stop = d.n >= max_nodes;
+            s_full = d.n >= max_nodes;
             d.have_knn = d.n > K;                                  // MS:1273
             for (int i = 0; i < 16; ++i) d.counters[i] = 0;
         }
         __syncthreads();
-        if (s_stop) break;
+        if (s_full) break;
         // sample-stream words of this step (the step the host had prepared ahead comes first)
         if (steps == 0 && first_words) {
             for (int i = tid; i < B * d.W; i += blockDim.x) words[i] = first_words[i];
@@ -627,10 +627,10 @@ __global__ void __launch_bounds__(kPersistThreads) plan_persist_kernel(PlanDev d
             unique = d.counters[10];
             d.n += d.counters[0] + (goal >= 0 ? 1 : 0);
             for (int i = 0; i < 5; ++i) s_stats[i] += d.counters[4 + i];
-            s_stop = goal >= 0;
+            s_goal_hit = goal >= 0;
         }
         __syncthreads();
-        if (s_stop) { ++steps; break; }
+        if (s_goal_hit) { ++steps; break; }
     }
     for (int i = tid; i < kMtN; i += blockDim.x) mt_state[i] = mts[i];
     if (tid == 0) {
