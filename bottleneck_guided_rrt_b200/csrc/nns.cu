@@ -406,6 +406,23 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
     if ((method == BGR_METHOD_GRID || method == BGR_METHOD_GRID_GENERAL) && !want_stats && !pipe_disabled())
         chunks = (int)std::min<int64_t>(d2 ? 4 : 2, nq / 8192);   // measured (profiles/r2_e2e_chunks.txt): 4 with both result arrays, 2 with indices only
     if (const char* e = getenv("BGR_KNN_CHUNKS")) chunks = std::max(1, std::min(atoi(e), (int)CopyPipe::kMaxChunks));   // measurement aid
+    // Page-locked result buffers are written by the search kernel itself, straight over the host link (UVA: a
+    // pinned host allocation has a device pointer), instead of being staged in HBM and copied back in chunks:
+    // measured on configs[1] 0.256 -> 0.234 ms (profiles/r2_e2e_chunks.txt).  BGR_KNN_ZEROCOPY=0 turns it off;
+    // pageable buffers take the staged path below.
+    static const bool zero_copy = !(getenv("BGR_KNN_ZEROCOPY") && getenv("BGR_KNN_ZEROCOPY")[0] == '0');
+    if (zero_copy && !want_stats) {
+        cudaPointerAttributes ai{}, ad{};
+        const bool ok_i = cudaPointerGetAttributes(&ai, idx) == cudaSuccess && ai.type == cudaMemoryTypeHost && ai.devicePointer;
+        const bool ok_d = !d2 || (cudaPointerGetAttributes(&ad, d2) == cudaSuccess && ad.type == cudaMemoryTypeHost && ad.devicePointer);
+        (void)cudaGetLastError();
+        if (ok_i && ok_d) {
+            BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, (int32_t*)ai.devicePointer,
+                                      d2 ? (float*)ad.devicePointer : h->d2_dev.p, nullptr));
+            BGR_CUDA(cudaStreamSynchronize(h->stream));
+            return BGR_OK;
+        }
+    }
     if (chunks <= 1) {
         BGR_CHECK(bgr_nns_knn_dev(h, h->q_dev.p, nq, k, eps, flags, max_radius, d_radii, h->idx_dev.p,
                                   h->d2_dev.p, touched));

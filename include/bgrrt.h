@@ -21,7 +21,8 @@
  * buffers and return synchronised.  Large batches are cut into chunks whose copies overlap
  * the kernels of their neighbours: that overlap needs page-locked caller buffers
  * (cudaHostAlloc / cudaHostRegister); pageable buffers give the same results with the
- * copies serialised by the driver.
+ * copies serialised by the driver.  bgr_nns_knn writes page-locked RESULT buffers from the search
+ * kernel itself (no staging copy).
  * Handles are not thread-safe (the reference caller is single-threaded) and belong to the
  * CUDA device that was current when they were created: calls made with another device
  * current return BGR_ERR_STATE.

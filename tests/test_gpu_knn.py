@@ -319,3 +319,25 @@ def test_knn_full_size_second_pass_self_match(bgr, oracle):
         di, dd, _ = nns.knn(torch.from_numpy(q).cuda(), k, optionFlags=flags)
         torch.cuda.synchronize()
         assert np.array_equal(di.cpu().numpy(), gi) and np.array_equal(dd.cpu().numpy().view(np.uint32), gd.view(np.uint32))
+
+
+def test_knn_pinned_result_buffers_written_by_the_kernel(bgr, oracle):
+    """host call with page-locked result buffers: the kernel writes them directly (no staging copy); same rows as
+    the pageable-buffer call and the oracle, with and without the distance array, grid and brute force"""
+    import torch
+    pts = oracle.points(2, 80_000, 10.0)
+    q = oracle.points(3, 20_000, 10.0)
+    oi, od = oracle.knn_brute(pts, q[:256], 16)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    for method in (bgr.METHOD_GRID, bgr.METHOD_BRUTE):
+        nns.set_method(method)
+        qp = q if method == bgr.METHOD_GRID else q[:2048]
+        ri, rd, _ = nns.knn(qp, 16)                                     # pageable numpy arrays: staged path
+        ih = torch.full((len(qp), 16), -9, dtype=torch.int32).pin_memory()
+        dh = torch.full((len(qp), 16), -9.0, dtype=torch.float32).pin_memory()
+        nns.knn(qp, 16, indices=ih.numpy(), dists2=dh.numpy())
+        assert canon_equal(ih.numpy(), dh.numpy(), ri, rd)
+        assert canon_equal(ih.numpy()[:256], dh.numpy()[:256], oi, od)
+        ih.fill_(-9)
+        nns.knn(qp, 16, indices=ih.numpy(), want_dists2=False)
+        assert np.array_equal(ih.numpy(), ri)
