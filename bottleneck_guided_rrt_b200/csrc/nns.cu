@@ -115,6 +115,7 @@ void plan_scan(int64_t nq, int64_t n, int* R, int* chunks, int64_t* chunk_nodes)
     // chunk restarts its running bound, the f32 filter passes more nodes to the fp64 path: cfg 3 0.40 -> 0.48 s)
     int r = 8;
     while (r > 1 && div_up(nq, (int64_t)kConsumerWarps * r) < 2 * sms) r >>= 1;
+    if (const char* e = getenv("BGR_SCAN_R")) { const int f = atoi(e); if (f == 1 || f == 2 || f == 4 || f == 8) r = f; }   // measurement aid
     const int64_t qblocks = div_up(nq, (int64_t)kConsumerWarps * r);
     const int64_t tiles = div_up(n > 0 ? n : 1, kTile);
     const int64_t resident = 3LL * sms;
