@@ -372,3 +372,43 @@ def test_reset_and_query_queue_equal_fresh_planners(bgr, oracle, world):
         torch.cuda.synchronize()
         for q in range(len(seeds)):
             assert bool(reached[q]) == fresh[q][0] and int(nodes[q]) == len(fresh[q][1][1]), (q, reached, nodes)
+
+
+def test_persistent_steps_respect_max_batches(bgr, oracle, world):
+    """run(max_nodes, max_batches) stops after exactly max_batches steps in the persistent kernel too, and a
+    sequence of short runs leaves the tree and the sample stream where the host-driven steps leave them"""
+    m, boxes, table, ms = world
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_MS, k=6, batch=3, flags=bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL, seed=17)
+    Q = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_MS, k=6, batch=3, flags=bgr.PLAN_REWIRE | bgr.PLAN_NO_GOAL | bgr.PLAN_NO_PERSIST, seed=17)
+    a, b = bgr.Planner(P, m, table, ms), bgr.Planner(Q, m, table, ms)
+    total = 0
+    for nb in (1, 2, 3, 5, 1, 7, 40, 1, 1, 13):
+        a.run(1 << 30, nb)
+        b.run(1 << 30, nb)
+        total += nb
+        assert a.stats()["batches"] == total == b.stats()["batches"]
+        assert len(a) == len(b)
+    _same_gpu_trees(a, b)
+    # node limit inside a launch: stops at the first step that reaches it
+    a.run(len(a) + 5, 1000)
+    b.run(len(b) + 5, 1000)
+    _same_gpu_trees(a, b)
+    assert a.persist_stats()["steps"] == a.stats()["batches"]
+
+
+def test_run_queue_corner_cases(bgr, oracle, world):
+    import torch
+    m, boxes, table, ms = world
+    P0 = bgr.PlannerParams((1.0, 1.0, 1.0), (2.0, 2.0, 2.0), mode=bgr.PLAN_MODE_RS, k=5, batch=1, flags=0, seed=1)
+    w = bgr.Planner(P0, m, table, ms)
+    reached, nodes = bgr.Planner.run_queue([w], np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32), np.zeros(0, np.uint32), 100)
+    assert len(reached) == 0 and len(nodes) == 0
+    starts = np.array([[0.2, 0.2, 0.2], [0.3, 0.3, 0.3]], np.float32)
+    goals = np.array([[0.5, 0.5, 0.5], [0.6, 0.4, 0.5]], np.float32)
+    reached, nodes = bgr.Planner.run_queue([w], starts, goals, np.array([5, 6], np.uint32), 2000, 5000)
+    for q in range(2):
+        P = bgr.PlannerParams(tuple(starts[q]), tuple(goals[q]), mode=bgr.PLAN_MODE_RS, k=5, batch=1, flags=0, seed=5 + q)
+        f = bgr.Planner(P, m, table, ms)
+        assert f.run(2000, 5000) == bool(reached[q]) and len(f) == int(nodes[q])
+    with pytest.raises(Exception):
+        bgr.Planner.run_queue([w, w], starts, goals, np.array([5, 6], np.uint32), 100)      # shared handle

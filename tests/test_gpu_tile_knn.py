@@ -182,3 +182,22 @@ def test_tile_knn_host_call_and_skip_flags(bgr, oracle):
         di, dd = di.cpu().numpy(), dd.cpu().numpy()
         assert (di[skip == 1] == -7).all() and (dd[skip == 1] == -7.0).all()
         assert canon_equal(di[skip == 0], dd[skip == 0], hi[skip == 0], hd[skip == 0])
+
+
+def test_tile_knn_falls_back_where_it_does_not_apply(bgr, oracle):
+    """k > 16, small batches and argument validation: the warp-per-query search answers, set_tile rejects bad sizes"""
+    import torch
+    pts = oracle.points(2, 60_000, 8.0)
+    q = oracle.points(3, 5_000, 8.0)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(bgr.METHOD_GRID)
+    nns.set_tile(0)
+    for k, nq in ((20, 5000), (16, 1000)):
+        i, d, _ = nns.knn(torch.from_numpy(q[:nq]).cuda(), k)
+        torch.cuda.synchronize()
+        oi, od = oracle.knn_brute(pts, q[:256], k)
+        assert canon_equal(i.cpu().numpy()[:256], d.cpu().numpy()[:256], oi, od)
+    assert nns.tile_stats()["tile_searches"] == 0
+    for bad in ((9, 1, 1, 1), (1, 7, 1, 1), (2, 2, 0, 1), (2, 2, 2, 5)):
+        with pytest.raises(Exception):
+            nns.set_tile(*bad)
