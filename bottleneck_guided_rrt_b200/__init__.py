@@ -36,6 +36,7 @@ from .capi import (  # noqa: F401
     PLAN_NO_GOAL,
     PLAN_DEDUP,
     PLAN_NO_PERSIST,
+    PLAN_NO_GRAPH,
     PLAN_MODE_RS,
     PLAN_MODE_MS,
     microbench_l2,

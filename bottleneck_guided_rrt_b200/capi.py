@@ -132,7 +132,7 @@ def microbench_l2(nbytes, mode, reps=10):
     return v.value
 
 
-PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP, PLAN_NO_PERSIST = 1, 2, 4, 8, 16, 32
+PLAN_EDGE_CHECK, PLAN_REWIRE, PLAN_QUIRKS, PLAN_NO_GOAL, PLAN_DEDUP, PLAN_NO_PERSIST, PLAN_NO_GRAPH = 1, 2, 4, 8, 16, 32, 64
 PLAN_MODE_RS, PLAN_MODE_MS = 0, 1
 
 
@@ -689,9 +689,9 @@ class Planner:
 
     def persist_stats(self):
         """bgr_planner_persist_stats: launches of the persistent small-batch kernel and the steps they ran"""
-        s = np.zeros(2, dtype=np.uint64)
+        s = np.zeros(3, dtype=np.uint64)
         _check(lib().bgr_planner_persist_stats(self._h, _ptr(s)))
-        return {"launches": int(s[0]), "steps": int(s[1])}
+        return {"launches": int(s[0]), "steps": int(s[1]), "graph_steps": int(s[2])}
 
     def stats(self):
         s = np.zeros(8, dtype=np.int64)

@@ -42,6 +42,7 @@ struct BruteArgs {
     int32_t* idx;         // [chunks][Q][k]
     float* d2;
     int64_t index_base;
+    const long long* n_dev;   // optional: the store's size lives on the device (CUDA-graph replays); n = its upper bound
 };
 
 __device__ __forceinline__ uint32_t radius_sentinel(float mr) {
@@ -107,7 +108,8 @@ __global__ void __launch_bounds__(kBruteThreads, 2) knn_brute_kernel(BruteArgs a
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t chunk_begin = (int64_t)blockIdx.y * a.chunk_nodes;
-    const int64_t n_pad = (a.n + kTile - 1) / kTile * kTile;
+    const int64_t n_now = a.n_dev ? (int64_t)*a.n_dev : a.n;
+    const int64_t n_pad = (n_now + kTile - 1) / kTile * kTile;
     const int64_t chunk_end = min(chunk_begin + a.chunk_nodes, n_pad);
     const int ntiles = (int)((chunk_end - chunk_begin) / kTile);
     const int tstride = tile_stride(ntiles);

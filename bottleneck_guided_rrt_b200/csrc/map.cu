@@ -1305,6 +1305,20 @@ void refresh_mask(bgr_map* h) {
 }  // namespace
 
 namespace bgr {
+// everything a captured planner step depends on inside the map: the scratch pointers of the collision calls, the
+// gate maps and their state, the gate / timing switches.  A different value = re-capture.
+uint64_t map_signature(const bgr_map* h) {
+    uint64_t v = 1469598103934665603ull;
+    auto mix = [&](uint64_t x) { v = (v ^ x) * 1099511628211ull; };
+    mix((uint64_t)(uintptr_t)h->eflags.p); mix((uint64_t)(uintptr_t)h->qctl.p); mix((uint64_t)(uintptr_t)h->queue.p);
+    mix((uint64_t)h->queue.cap); mix((uint64_t)(uintptr_t)h->stats.p);
+    mix((uint64_t)(uintptr_t)h->dil[0].p); mix((uint64_t)(uintptr_t)h->dil[1].p);
+    mix((uint64_t)h->dil_cells[0]); mix((uint64_t)h->dil_cells[1]); mix((uint64_t)h->n_dilate_full);
+    mix((uint64_t)h->gate_on); mix((uint64_t)h->timing); mix((uint64_t)h->level_mask);
+    for (int L = 0; L <= kMaxLevel; ++L) mix((uint64_t)(uintptr_t)h->bits[L].p);
+    mix((uint64_t)(uintptr_t)h->stream);
+    return v;
+}
 int map_sphere_gate(bgr_map* h, double radius, LevelGrid* dil) {
     dil->bits = nullptr;
     for (int a = 0; a < 3; ++a) dil->nb[a] = h->nb[0][a];

@@ -65,4 +65,5 @@ void** map_aux(bgr_map* h, void (*free_fn)(void*));
 // gate map of a sphere query of this radius (level 0 dilated; built / brought up to date if need be); bits = nullptr
 // when the gate does not apply
 int map_sphere_gate(bgr_map* h, double radius, LevelGrid* dil);
+uint64_t map_signature(const bgr_map* h);   // changes whenever a captured planner step would have to be re-captured
 }  // namespace bgr

@@ -25,6 +25,7 @@ struct NearestArgs {
     int64_t index_base;
     const long long* nq_dev;   // optional: only the first nq_base + *nq_dev queries are valid (<= nq)
     int64_t nq_base;
+    const long long* n_dev;    // optional: the store's size lives on the device (CUDA-graph replays); n = its upper bound
 };
 
 __device__ __forceinline__ int64_t valid_queries(const long long* nq_dev, int64_t nq_base, int64_t nq) {
@@ -47,7 +48,8 @@ __global__ void __launch_bounds__(kBruteThreads) nearest_kernel(NearestArgs a) {
     uint64_t* empty_bar = full_bar + kStages;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t chunk_begin = (int64_t)blockIdx.y * a.chunk_nodes;
-    const int64_t n_pad = (a.n + kTile - 1) / kTile * kTile;
+    const int64_t n_now = a.n_dev ? (int64_t)*a.n_dev : a.n;
+    const int64_t n_pad = (n_now + kTile - 1) / kTile * kTile;
     const int64_t chunk_end = min(chunk_begin + a.chunk_nodes, n_pad);
     const int ntiles = (int)((chunk_end - chunk_begin) / kTile);
     const int tstride = tile_stride(ntiles);   // scrambled tile order: see knn_brute.cuh

@@ -130,13 +130,16 @@ void plan_scan(int64_t nq, int64_t n, int* R, int* chunks, int64_t* chunk_nodes)
     *chunk_nodes = per;
 }
 
+// n_dev != nullptr: the kernels read the store's size from the device and the launch is laid out for n_plan nodes
+// (CUDA-graph replays of a planner step: the same launch parameters serve a growing tree)
 int knn_brute_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flags, float max_radius,
-                  const float* d_radii, int32_t* d_idx, float* d_d2) {
+                  const float* d_radii, int32_t* d_idx, float* d_d2, int64_t n_plan = -1, const long long* n_dev = nullptr) {
     int R, chunks;
     int64_t per;
-    plan_scan(nq, h->n, &R, &chunks, &per);
+    if (n_plan < 0) n_plan = h->n;
+    plan_scan(nq, n_plan, &R, &chunks, &per);
     BruteArgs a;
-    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.f4 = h->f4.p; a.n = h->n;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.f4 = h->f4.p; a.n = n_plan; a.n_dev = n_dev;
     a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
     a.max_radius = max_radius; a.max_radii = d_radii;
     a.chunk_nodes = per;
@@ -452,13 +455,17 @@ int bgr_nns_knn(bgr_nns* h, const float* q, int64_t nq, int k, float eps, unsign
 // nq = capacity of the query / result arrays; with d_count only the first count_base + *d_count
 // queries are valid (the rest of the rows is left undefined) and nq_hint (host guess of that
 // number, e.g. the previous batch's) sizes the scan.
+// n_dev != nullptr: plain scan laid out for n_plan nodes, the kernels read the store's size from the device
+// (CUDA-graph replays of a planner step)
 int nearest_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, float* d_dist,
-                            const long long* d_count, int64_t count_base, int64_t nq_hint) {
+                            const long long* d_count, int64_t count_base, int64_t nq_hint, int64_t n_plan = -1,
+                            const long long* n_dev = nullptr) {
     BGR_ARG(h != nullptr && nq >= 0, "bad nearest arguments");
     BGR_ARG(h->n >= 1, "Nearest on an empty tree");
     if (nq == 0) return BGR_OK;
     BGR_CHECK(check_device(h->device));
-    {
+    if (n_plan < 0) n_plan = h->n;
+    if (!n_dev) {
         // large trees: the grid index answers Nearest exactly (grid_nearest_kernel); the plain scan
         // below stays for small trees and for METHOD_BRUTE
         int method;
@@ -470,10 +477,10 @@ int nearest_dev_impl(bgr_nns* h, const float* d_q, int64_t nq, int32_t* d_idx, f
     }
     int R, chunks;
     int64_t per;
-    plan_scan(d_count ? std::max<int64_t>(1, std::min(nq, nq_hint)) : nq, h->n, &R, &chunks, &per);
+    plan_scan(d_count ? std::max<int64_t>(1, std::min(nq, nq_hint)) : nq, n_plan, &R, &chunks, &per);
     if (R > 4) R = 4;   // double-precision state: keep registers in check
     NearestArgs a;
-    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = h->n;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.n = n_plan; a.n_dev = n_dev;
     a.q = d_q; a.nq = nq; a.chunk_nodes = per; a.index_base = h->index_base;
     a.nq_dev = d_count; a.nq_base = count_base;
     BGR_CHECK(h->part_idx.reserve((int64_t)chunks * nq, h->stream, false));
@@ -581,4 +588,15 @@ int nns_nearest_counted(bgr_nns* h, const float* d_q, int64_t nq_cap, int64_t nq
                         int64_t count_base, int32_t* d_idx, float* d_dist) {
     return nearest_dev_impl(h, d_q, nq_cap, d_idx, d_dist, d_count, count_base, nq_hint);
 }
+int nns_nearest_scan_cap(bgr_nns* h, const float* d_q, int64_t nq_cap, const long long* d_count, int64_t count_base,
+                         int32_t* d_idx, float* d_dist, int64_t n_cap, const long long* n_dev) {
+    return nearest_dev_impl(h, d_q, nq_cap, d_idx, d_dist, d_count, count_base, nq_cap, n_cap, n_dev);
+}
+int nns_knn_brute_cap(bgr_nns* h, const float* d_q, int64_t nq, int k, int32_t* d_idx, float* d_d2, int64_t n_cap,
+                      const long long* n_dev) {
+    BGR_CHECK(check_device(h->device));
+    return knn_brute_dev(h, d_q, nq, k, 0u, INFINITY, nullptr, d_idx, d_d2, n_cap, n_dev);
+}
+void nns_scan_scratch(bgr_nns* h, const void** a, const void** b) { *a = h->part_idx.p; *b = h->part_d2.p; }
+int nns_method(const bgr_nns* h) { return h->method; }
 }  // namespace bgr

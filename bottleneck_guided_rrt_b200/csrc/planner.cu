@@ -31,6 +31,7 @@ struct PlanDev {                 // device view shared by the kernels
     const float *x, *y, *z;      // node store
     int32_t* par;
     int64_t n;                   // snapshot size
+    const long long* n_dev;      // optional: the snapshot size lives on the device (CUDA-graph replays of a step)
     int B, K, W;                 // candidates, neighbours, stream words per candidate
     int have_knn;
     const uint32_t* words;
@@ -59,6 +60,8 @@ struct PlanDev {                 // device view shared by the kernels
     const int32_t* u_near;
     int n_fixed;
 };
+
+__device__ __forceinline__ int64_t tree_n(const PlanDev& d) { return d.n_dev ? (int64_t)*d.n_dev : d.n; }
 
 // ------------------------------------------------------------------ MT19937 on the device
 __device__ __forceinline__ uint32_t mt_twist(uint32_t u, uint32_t v) {   // mtrand.h:77-82
@@ -274,7 +277,7 @@ __device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, flo
     float cost = __fadd_rn(0.f, norm_ref(px, py, pz, cx, cy, cz));
     int cur = d.par[P];
     float lx = px, ly = py, lz = pz;                           // previous node on the walk (P first)
-    int64_t guard = d.n + d.B + 2;                             // a tree walk visits every node at most once
+    int64_t guard = tree_n(d) + d.B + 2;                       // a tree walk visits every node at most once
     while (cur > 0 && guard-- > 0) {
         const float qx = d.x[cur], qy = d.y[cur], qz = d.z[cur];
         cost = __fadd_rn(cost, norm_ref(qx, qy, qz, lx, ly, lz));
@@ -375,9 +378,9 @@ __device__ __forceinline__ void plan_commit_body(const PlanDev& d, float* x, flo
         __syncthreads();
         const int base = s_base;
         const int rank = base + (warp ? warp_tot[warp - 1] : 0) + inc - take;
-        if (c < d.B) d.new_index[c] = take ? (int32_t)(d.n + rank) : -1;
+        if (c < d.B) d.new_index[c] = take ? (int32_t)(tree_n(d) + rank) : -1;
         if (take) {
-            const int64_t ni = d.n + rank;
+            const int64_t ni = tree_n(d) + rank;
             x[ni] = d.pnew[3 * c]; y[ni] = d.pnew[3 * c + 1]; z[ni] = d.pnew[3 * c + 2];
             f4[ni] = filter_image(d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2]);
             d.par[ni] = d.parent[c];
@@ -391,7 +394,7 @@ __device__ __forceinline__ void plan_commit_body(const PlanDev& d, float* x, flo
         d.counters[0] = acc;
         d.counters[1] = goal_c == 0x7fffffff ? -1 : goal_c;
         if (goal_c != 0x7fffffff) {
-            const int64_t gi = d.n + acc;
+            const int64_t gi = tree_n(d) + acc;
             x[gi] = d.p.goal[0]; y[gi] = d.p.goal[1]; z[gi] = d.p.goal[2];
             f4[gi] = filter_image(d.p.goal[0], d.p.goal[1], d.p.goal[2]);
             d.par[gi] = (int32_t)(gi - 1);                      // goal.push_back(V.size()-1)
@@ -441,7 +444,7 @@ __device__ __forceinline__ void plan_rewire_apply_body(const PlanDev& d, const i
     const int32_t ni = d.new_index[c];
     if (ni < 0) return;
     const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
-    if (ind <= 0 || ind >= d.n) return;
+    if (ind <= 0 || ind >= tree_n(d)) return;
     const unsigned long long key = d.rkey[ind];
     if (key == ~0ull || (unsigned)(key & 0xffffffffu) != (unsigned)ni) return;
     // several slots of the same candidate can name the same node only once (kNN lists are sets)
@@ -454,7 +457,7 @@ __global__ void plan_rewire_apply_kernel(PlanDev d, const int32_t* __restrict__ 
 __device__ __forceinline__ void plan_rewire_clear_body(const PlanDev& d, const int t) {
     if (t >= d.B * d.K) return;
     const int32_t ind = d.knn_idx[(size_t)t];
-    if (ind > 0 && ind < d.n) d.rkey[ind] = ~0ull;
+    if (ind > 0 && ind < tree_n(d)) d.rkey[ind] = ~0ull;
 }
 __global__ void plan_rewire_clear_kernel(PlanDev d) { plan_rewire_clear_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
@@ -676,10 +679,17 @@ struct bgr_planner {
     PinBuf host_counters;
     DevBuf<PersistCtl> pctl;     // control block of the persistent small-batch kernel
     PinBuf host_pctl;
+    PinBuf host_init;            // counters block a replayed step uploads: zeros + the tree size in word 15
+    cudaGraphExec_t gexec[2] = {nullptr, nullptr};   // the captured step, one per sample-word buffer
+    uint64_t g_sig = 0;          // what the captured launches depend on (graph_signature)
+    bool g_warm = false;
+    uint64_t n_graph_steps = 0;
     uint64_t n_persist_launches = 0, n_persist_steps = 0;
 };
 
 extern "C" {
+
+static void graph_drop(bgr_planner* pl);
 
 int bgr_planner_destroy(bgr_planner* pl) {
     if (!pl) return BGR_OK;
@@ -692,7 +702,9 @@ int bgr_planner_destroy(bgr_planner* pl) {
     pl->found.release(); pl->hit.release(); pl->kskip.release(); pl->band.release(); pl->ehit.release(); pl->eband.release();
     pl->ok.release(); pl->par.release(); pl->near.release(); pl->knn_idx.release(); pl->parent.release();
     pl->new_index.release(); pl->rkey.release(); pl->counters.release(); pl->host_counters.release();
-    pl->pctl.release(); pl->host_pctl.release();
+    pl->pctl.release(); pl->host_pctl.release(); pl->host_init.release();
+    for (int i = 0; i < 2; ++i)
+        if (pl->gexec[i]) cudaGraphExecDestroy(pl->gexec[i]);
     delete pl;
     return BGR_OK;
 }
@@ -707,7 +719,7 @@ int bgr_planner_create(const bgr_planner_params* p, bgr_map* map, const float* t
     BGR_ARG(p->batch >= 1 && p->batch <= 65536, "batch must be in 1..65536");
     BGR_ARG(p->mode == BGR_PLAN_MODE_RS || p->mode == BGR_PLAN_MODE_MS, "unknown sampler mode %d", p->mode);
     BGR_ARG(p->mode != BGR_PLAN_MODE_MS || (milestones != nullptr && nm >= 3), "mode MS needs >= 3 milestone points");
-    BGR_ARG((p->flags & ~63u) == 0, "unknown planner flags %u", p->flags);
+    BGR_ARG((p->flags & ~127u) == 0, "unknown planner flags %u", p->flags);
     BGR_ARG(p->eta > 0.f && p->state_radius >= 0 && p->edge_radius >= 0, "bad eta / radii");
     bgr_planner* pl = new bgr_planner;
     pl->p = *p;
@@ -742,6 +754,7 @@ int bgr_planner_create(const bgr_planner_params* p, bgr_map* map, const float* t
 int bgr_planner_set_stream(bgr_planner* pl, void* stream) {
     BGR_ARG(pl != nullptr, "null planner");
     BGR_CUDA(cudaStreamSynchronize(pl->stream));
+    graph_drop(pl);
     pl->stream = (cudaStream_t)stream;
     BGR_CHECK(bgr_nns_set_stream(pl->nns, stream));
     BGR_CHECK(bgr_map_set_stream(pl->map, stream));
@@ -821,7 +834,7 @@ static PlanDev step_view(bgr_planner* pl, int64_t N, uint32_t* words_now) {
     nns_soa(pl->nns, &x, &y, &z, &f4);
     d.x = x; d.y = y; d.z = z;
     d.par = pl->par.p;
-    d.n = N; d.B = P.batch; d.K = P.k; d.W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4; d.have_knn = N > P.k;   // MS:1273
+    d.n = N; d.n_dev = nullptr; d.B = P.batch; d.K = P.k; d.W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4; d.have_knn = N > P.k;   // MS:1273
     d.words = words_now; d.table = pl->table.p; d.nt = pl->nt; d.milestones = pl->milestones.p;
     d.prand = pl->prand.p; d.pnew = pl->pnew.p; d.found = pl->found.p; d.near = pl->near.p;
     d.hit = pl->hit.p; d.band = pl->band.p; d.knn_idx = pl->knn_idx.p;
@@ -832,34 +845,29 @@ static PlanDev step_view(bgr_planner* pl, int64_t N, uint32_t* words_now) {
     return d;
 }
 
-static int step_launch(bgr_planner* pl) {
+// The device work of one step, from the counters block to the counters copy, enqueued on the planner's stream.
+// capped = false: host-driven form (launch parameters from the exact tree size N).
+// capped = true : the form a CUDA graph replays — the counters block is uploaded from a pinned host block whose last
+// word carries N (d.n_dev points at it), and Nearest / kNN are the plain scans laid out for kGraphCap nodes.
+constexpr int64_t kGraphCap = 16384;     // below this size the AUTO method is the plain scan anyway
+static int step_enqueue(bgr_planner* pl, const PlanDev& d, float* x, float* y, float* z, float4* f4, bool capped) {
     const bgr_planner_params& P = pl->p;
     const int B = P.batch, K = P.k, K1 = K + 1;
-    const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
-    const int64_t N = bgr_nns_size(pl->nns);
     const bool edge_check = P.flags & BGR_PLAN_EDGE_CHECK, rewire = P.flags & BGR_PLAN_REWIRE;
-    const bool have_knn = N > K;                                               // MS:1273
-    const int n_fixed = P.mode == BGR_PLAN_MODE_MS ? 4 : 1;
+    const bool have_knn = d.have_knn;
+    const int n_fixed = d.n_fixed;
     cudaStream_t st = pl->stream;
-    // capacity for this step's appends (+ the goal node)
-    BGR_CHECK(step_reserve(pl, N + B + 1));
-    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
-    uint32_t* words_next = pl->words_cur ? pl->words.p : pl->words2.p;
-    const PlanDev d = step_view(pl, N, words_now);
-    float *x, *y, *z;
-    float4* f4;
-    nns_soa(pl->nns, &x, &y, &z, &f4);
-
     const unsigned gb = (unsigned)div_up(B, 256), gbk1 = (unsigned)div_up((int64_t)B * K1, 256), gbk = (unsigned)div_up((int64_t)B * K, 256);
-    BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
-    if (!pl->words_ahead) {
-        mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, words_now, B * W);
-        BGR_LAUNCH_CHECK();
-    }
+    if (capped) BGR_CUDA(cudaMemcpyAsync(pl->counters.p, pl->host_init.p, 16 * sizeof(long long), cudaMemcpyHostToDevice, st));
+    else BGR_CUDA(cudaMemsetAsync(pl->counters.p, 0, 16 * sizeof(long long), st));
     plan_sample_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
-    BGR_CHECK(nns_nearest_counted(pl->nns, pl->uq.p, B + n_fixed, pl->unique_hint > 0 ? pl->unique_hint + pl->unique_hint / 4 + 8 : B + n_fixed,
-                                  pl->counters.p + 10, n_fixed, pl->u_near.p, pl->u_dist.p));
+    if (capped)
+        BGR_CHECK(nns_nearest_scan_cap(pl->nns, pl->uq.p, B + n_fixed, pl->counters.p + 10, n_fixed, pl->u_near.p, pl->u_dist.p,
+                                       kGraphCap, pl->counters.p + 15));
+    else
+        BGR_CHECK(nns_nearest_counted(pl->nns, pl->uq.p, B + n_fixed, pl->unique_hint > 0 ? pl->unique_hint + pl->unique_hint / 4 + 8 : B + n_fixed,
+                                      pl->counters.p + 10, n_fixed, pl->u_near.p, pl->u_dist.p));
     plan_steer_kernel<<<gb, 256, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
     BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
@@ -872,7 +880,8 @@ static int step_launch(bgr_planner* pl) {
         // milestone candidate have the rows of the first one: skip their searches
         plan_knn_rep_kernel<<<gb, 256, 0, st>>>(d, pl->kskip.p);
         BGR_LAUNCH_CHECK();
-        BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->kskip.p, pl->knn_idx.p, pl->knn_d2.p));
+        if (capped) BGR_CHECK(nns_knn_brute_cap(pl->nns, pl->pnew.p, B, K, pl->knn_idx.p, pl->knn_d2.p, kGraphCap, pl->counters.p + 15));
+        else BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->kskip.p, pl->knn_idx.p, pl->knn_d2.p));
         plan_knn_spread_kernel<<<gbk, 256, 0, st>>>(d, pl->knn_d2.p);
         BGR_LAUNCH_CHECK();
     }
@@ -896,8 +905,109 @@ static int step_launch(bgr_planner* pl) {
         plan_rewire_clear_kernel<<<gbk, 256, 0, st>>>(d);
         BGR_LAUNCH_CHECK();
     }
-    long long* hc = (long long*)pl->host_counters.p;
-    BGR_CUDA(cudaMemcpyAsync(hc, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    BGR_CUDA(cudaMemcpyAsync(pl->host_counters.p, pl->counters.p, 16 * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    return BGR_OK;
+}
+
+// A step of a small tree is ~20-30 tiny dependent launches; on a stream of its own the whole sequence is captured
+// once (per sample-word buffer) and replayed as ONE graph launch per step while the tree stays below kGraphCap nodes:
+// nothing in the captured launches depends on the tree size any more (it is read from the counters block).
+static bool graph_ok(const bgr_planner* pl) {
+    const bgr_planner_params& P = pl->p;
+    const int64_t N = bgr_nns_size(pl->nns);
+    static const bool off = getenv("BGR_PLAN_NO_GRAPH") != nullptr;
+    return !off && pl->stream != nullptr && !(P.flags & BGR_PLAN_NO_GRAPH) && nns_method(pl->nns) == BGR_METHOD_AUTO &&
+           N > P.k && N + P.batch + 1 <= kGraphCap;
+}
+
+static void graph_drop(bgr_planner* pl) {
+    for (int i = 0; i < 2; ++i)
+        if (pl->gexec[i]) { cudaGraphExecDestroy(pl->gexec[i]); pl->gexec[i] = nullptr; }
+    pl->g_warm = false;
+}
+
+static uint64_t graph_signature(bgr_planner* pl) {
+    float *x, *y, *z;
+    float4* f4;
+    nns_soa(pl->nns, &x, &y, &z, &f4);
+    const void *sa, *sb;
+    nns_scan_scratch(pl->nns, &sa, &sb);
+    uint64_t v = map_signature(pl->map);
+    auto mix = [&](const void* p) { v = (v ^ (uint64_t)(uintptr_t)p) * 1099511628211ull; };
+    mix(x); mix(y); mix(z); mix(f4); mix(sa); mix(sb); mix(pl->par.p); mix(pl->rkey.p); mix(pl->counters.p);
+    mix(pl->words.p); mix(pl->words2.p); mix(pl->knn_idx.p); mix(pl->e1.p); mix(pl->ehit.p); mix(pl->pnew.p);
+    mix(pl->uq.p); mix(pl->costs.p); mix(pl->stream); mix(pl->host_counters.p); mix(pl->host_init.p);
+    // the kernels take the parameters by value (goal, eta, radii, flags ...): a re-armed planner re-captures
+    const unsigned char* pb = reinterpret_cast<const unsigned char*>(&pl->p);
+    for (size_t i = 0; i < sizeof(pl->p); ++i) v = (v ^ pb[i]) * 1099511628211ull;
+    v = (v ^ (uint64_t)pl->nt) * 1099511628211ull;
+    mix(pl->table.p); mix(pl->milestones.p);
+    return v;
+}
+
+static int step_launch(bgr_planner* pl) {
+    const bgr_planner_params& P = pl->p;
+    const int B = P.batch;
+    const int W = P.mode == BGR_PLAN_MODE_MS ? 6 : 4;
+    const int64_t N = bgr_nns_size(pl->nns);
+    cudaStream_t st = pl->stream;
+    const bool capped = graph_ok(pl);
+    // capacity for this step's appends (+ the goal node); the graph form reserves the whole regime at once so that
+    // no pointer moves between replays
+    BGR_CHECK(step_reserve(pl, capped ? kGraphCap + B + 1 : N + B + 1));
+    uint32_t* words_now = pl->words_cur ? pl->words2.p : pl->words.p;
+    uint32_t* words_next = pl->words_cur ? pl->words.p : pl->words2.p;
+    PlanDev d = step_view(pl, N, words_now);
+    float *x, *y, *z;
+    float4* f4;
+    nns_soa(pl->nns, &x, &y, &z, &f4);
+    if (!pl->words_ahead) {
+        mt_fill_kernel<<<1, 256, 0, st>>>(pl->mt_state.p, words_now, B * W);
+        BGR_LAUNCH_CHECK();
+    }
+    if (!capped) {
+        BGR_CHECK(step_enqueue(pl, d, x, y, z, f4, false));
+    } else {
+        BGR_CHECK(pl->host_init.reserve(16 * sizeof(long long)));
+        long long* hi = (long long*)pl->host_init.p;
+        for (int i = 0; i < 15; ++i) hi[i] = 0;
+        hi[15] = N;                                   // read by the replayed upload: the host has synchronised the previous step
+        d.n_dev = pl->counters.p + 15;
+        d.have_knn = 1;
+        const int par = pl->words_cur;
+        const uint64_t sig = graph_signature(pl);
+        if (!pl->g_warm || sig != pl->g_sig) {
+            // first step of the regime (or something moved): run the sequence directly — allocations, function
+            // attributes and the gate maps settle — and capture from the next step on
+            graph_drop(pl);
+            BGR_CHECK(step_enqueue(pl, d, x, y, z, f4, true));
+            pl->g_sig = graph_signature(pl);
+            pl->g_warm = true;
+        } else {
+            if (!pl->gexec[par]) {
+                cudaGraph_t g = nullptr;
+                BGR_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+                const int rc = step_enqueue(pl, d, x, y, z, f4, true);
+                const cudaError_t ce = cudaStreamEndCapture(st, &g);
+                if (rc != BGR_OK || ce != cudaSuccess || !g) {
+                    if (g) cudaGraphDestroy(g);
+                    (void)cudaGetLastError();
+                    if (rc != BGR_OK) return rc;
+                    set_error("planner step capture failed: %s", cudaGetErrorString(ce));
+                    return BGR_ERR_CUDA;
+                }
+                const cudaError_t ie = cudaGraphInstantiate(&pl->gexec[par], g, 0);
+                cudaGraphDestroy(g);
+                if (ie != cudaSuccess) {
+                    pl->gexec[par] = nullptr;
+                    set_error("planner step graph instantiation failed: %s", cudaGetErrorString(ie));
+                    return BGR_ERR_CUDA;
+                }
+            }
+            BGR_CUDA(cudaGraphLaunch(pl->gexec[par], st));
+            pl->n_graph_steps++;
+        }
+    }
     if (!pl->ev_step) BGR_CUDA(cudaEventCreateWithFlags(&pl->ev_step, cudaEventDisableTiming));
     BGR_CUDA(cudaEventRecord(pl->ev_step, st));
     // the sample stream does not depend on the tree: the next step's words (a single-CTA, serial MT19937
@@ -1192,10 +1302,11 @@ int bgr_planner_get_path(bgr_planner* pl, int32_t* path, int64_t* n_out) {   // 
     return BGR_OK;
 }
 
-int bgr_planner_persist_stats(bgr_planner* pl, uint64_t out[2]) {
+int bgr_planner_persist_stats(bgr_planner* pl, uint64_t out[3]) {
     BGR_ARG(pl != nullptr && out != nullptr, "bad arguments");
     out[0] = pl->n_persist_launches;
     out[1] = pl->n_persist_steps;
+    out[2] = pl->n_graph_steps;
     return BGR_OK;
 }
 

@@ -304,6 +304,8 @@ int bgr_map_find_labels(bgr_map* map, const double* path_3xP, int64_t p, double 
                                  * reject the copies (counted in rejected_state) instead of appending coincident nodes */
 #define BGR_PLAN_NO_PERSIST 32u  /* measurement / test aid: never run steps in the persistent small-batch kernel (batch <= 8,
                                  * no edge checks, tree < 65,536 nodes: whole steps inside one launch, same tree bit for bit) */
+#define BGR_PLAN_NO_GRAPH 64u    /* measurement / test aid: never replay a step as a CUDA graph (planner on its own stream, tree below
+                                 * 16,384 nodes: the step's ~25 launches are captured once and replayed; same tree bit for bit) */
 #define BGR_PLAN_MODE_RS 0      /* rrt_star.cpp sampler: rand_chance > goal_chance ? table : goal */
 #define BGR_PLAN_MODE_MS 1      /* rrt_star_milestones.cpp sampler: >0.8 table, (0.5,0.8) goal, else milestone[int z] */
 
@@ -361,8 +363,9 @@ int bgr_planner_get_path(bgr_planner* pl, int32_t* path, int64_t* n);
 /* [0] batches [1] candidates [2] rejected by the state check [3] rejected by the edge check
  * [4] improved parents [5] rewired nodes [6] in-band collision results [7] goal candidate */
 int bgr_planner_stats(bgr_planner* pl, int64_t out[8]);
-/* test / measurement aid: [0] launches of the persistent small-batch kernel so far, [1] steps they ran */
-int bgr_planner_persist_stats(bgr_planner* pl, uint64_t out[2]);
+/* test / measurement aid: [0] launches of the persistent small-batch kernel so far, [1] steps they ran,
+ * [2] steps replayed as a CUDA graph */
+int bgr_planner_persist_stats(bgr_planner* pl, uint64_t out[3]);
 /* the planner's node store (borrowed): knn / nearest queries against the growing tree */
 int bgr_planner_nns(bgr_planner* pl, bgr_nns** out);
 int bgr_planner_destroy(bgr_planner* pl);

@@ -144,7 +144,7 @@ def test_planner_argument_errors(bgr, world):
     with pytest.raises(bgr.BgrError):
         bgr.Planner(bgr.PlannerParams((0, 0, 0), (1, 1, 1), mode=bgr.PLAN_MODE_MS), m, table, None)
     with pytest.raises(bgr.BgrError):
-        bgr.Planner(bgr.PlannerParams((0, 0, 0), (1, 1, 1), flags=64), m, table, ms)
+        bgr.Planner(bgr.PlannerParams((0, 0, 0), (1, 1, 1), flags=128), m, table, ms)
 
 
 def test_run_many_equals_run(bgr, oracle):
@@ -412,3 +412,69 @@ def test_run_queue_corner_cases(bgr, oracle, world):
         assert f.run(2000, 5000) == bool(reached[q]) and len(f) == int(nodes[q])
     with pytest.raises(Exception):
         bgr.Planner.run_queue([w, w], starts, goals, np.array([5, 6], np.uint32), 100)      # shared handle
+
+
+@pytest.mark.parametrize("mode,k,batch,flags,seed", [(0, 10, 256, 0, 11), (1, 10, 256, 3, 3), (1, 16, 1024, 3 | 16, 5), (1, 8, 64, 1, 9),
+                                                     (0, 5, 16, 2 | 4, 2), (1, 10, 300, 3 | 8, 4)])
+def test_graph_replayed_steps_equal_host_driven_steps(bgr, oracle, mode, k, batch, flags, seed):
+    """a planner on a stream of its own replays its step as one CUDA graph launch while the tree is below 16,384 nodes
+    (the tree size is read from the counters block, Nearest / kNN are the plain scans laid out for the cap): same
+    tree, statistics and sample-stream position as the launch-by-launch steps (BGR_PLAN_NO_GRAPH) and the oracle,
+    across the switch to host-driven steps at the cap, with run() and step() mixed, and after a map update"""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    occ = synth.make_map(64, 1, occupancy=0.0)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 2)
+    table = synth.points(9, 50000, 3.2)
+    ms = np.load(os.path.join(GOLD, "milestones.npz"))["milestones"][3].reshape(3, 3).astype(np.float32) * np.float32(1.5)
+    planners = []
+    for extra in (0, bgr.PLAN_NO_GRAPH):
+        st = torch.cuda.Stream()
+        m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64), stream=st.cuda_stream)
+        m.set_boxes(boxes)
+        P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=mode, k=k, batch=batch, flags=flags | extra | bgr.PLAN_NO_PERSIST, seed=seed)
+        planners.append((bgr.Planner(P, m, table, ms, stream=st.cuda_stream), m, st))
+    (a, ma, _), (b, mb, _) = planners
+    P0 = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=mode, k=k, batch=batch, flags=flags, seed=seed)
+    op = oracle.Planner(P0, boxes, table, ms)
+    ga, gb, go = a.run(3000, 12), b.run(3000, 12), op.run(3000, 12)
+    torch.cuda.synchronize()
+    assert a.persist_stats()["graph_steps"] >= 5 and b.persist_stats()["graph_steps"] == 0
+    assert ga == gb
+    _same_gpu_trees(a, b)
+    if a.stats()["in_band"] == 0:
+        _assert_same_tree(a, op, ga, go)
+    for _ in range(3):
+        if not ga:
+            ga, gb = a.step()[1], b.step()[1]
+    # a map update between steps: the captured step must not keep using what it captured
+    add = np.array([[1.025 + 0.05 * i, 1.025, 1.025, 0.05, 1.0, 0.5] for i in range(6)])
+    ma.update_boxes(add, boxes[:200])
+    mb.update_boxes(add, boxes[:200])
+    if not ga:
+        ga, gb = a.run(20_000, 40), b.run(20_000, 40)       # across the 16,384-node cap for the large batches
+    torch.cuda.synchronize()
+    assert ga == gb
+    _same_gpu_trees(a, b)
+
+
+def test_graph_replay_with_rearmed_planner(bgr, oracle, world):
+    """bgr_planner_reset changes the goal the captured kernels carry by value: the step is captured again"""
+    import torch
+    m0, boxes, table, ms = world
+    st = torch.cuda.Stream()
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (64, 64, 64), stream=st.cuda_stream)
+    m.set_boxes(boxes)
+    P = bgr.PlannerParams((0.2, 0.2, 0.2), (3.0, 3.0, 3.0), mode=bgr.PLAN_MODE_MS, k=10, batch=128, flags=3, seed=1)
+    w = bgr.Planner(P, m, table, ms, stream=st.cuda_stream)
+    w.run(2000, 10)
+    for q, (s_, g_, seed) in enumerate([((0.3, 2.9, 0.4), (2.9, 0.3, 2.9), 12), ((0.25, 1.5, 2.8), (3.0, 1.6, 0.3), 13)]):
+        w.reset(s_, g_, seed)
+        gw = w.run(2500, 30)
+        Pq = bgr.PlannerParams(s_, g_, mode=bgr.PLAN_MODE_MS, k=10, batch=128, flags=3 | bgr.PLAN_NO_GRAPH, seed=seed)
+        f = bgr.Planner(Pq, m0, table, ms)
+        gf = f.run(2500, 30)
+        torch.cuda.synchronize()
+        assert gw == gf
+        _same_gpu_trees(w, f)
+    assert w.persist_stats()["graph_steps"] > 10
