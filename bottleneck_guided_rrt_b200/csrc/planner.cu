@@ -340,6 +340,32 @@ __device__ __forceinline__ void plan_select_body(const PlanDev& d, const int c) 
 }
 __global__ void plan_select_kernel(PlanDev d) { plan_select_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
 
+// Fused forms of the host-driven step (a small step costs ~5 us per DEPENDENT kernel, whatever the kernel does):
+// one warp per candidate.  plan_state_kernel = steer, sphere state check, dedup and the kNN skip flag;
+// plan_cost_select_kernel = the K+1 chain costs of the candidate on K+1 lanes, then its parent choice.
+__global__ void __launch_bounds__(128) plan_state_kernel(PlanDev d, MapView m, LevelGrid dil, uint8_t* kskip) {
+    const int c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (c >= d.B) return;
+    if (lane == 0) plan_steer_body(d, c);
+    __syncwarp();
+    collide_spheres_warp<1>(m, d.pnew, d.B, d.p.state_radius, d.hit, d.band, dil, c, lane);
+    __syncwarp();
+    if (lane == 0) {
+        if (d.p.flags & BGR_PLAN_DEDUP) plan_dedup_body(d, c);
+        if (d.have_knn) {
+            const int slot = d.qslot[c];
+            kskip[c] = (d.hit[c] || (slot < d.n_fixed && (long long)(d.B - c) != d.counters[11 + slot])) ? 1 : 0;
+        }
+    }
+}
+__global__ void __launch_bounds__(128) plan_cost_select_kernel(PlanDev d) {
+    const int c = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (c >= d.B) return;
+    for (int j = lane; j < d.K + 1; j += 32) plan_cost_body(d, c * (d.K + 1) + j);
+    __syncwarp();
+    if (lane == 0) plan_select_body(d, c);
+}
+
 // One CTA: goal cut (first accepted candidate within goal_tol, MS:1340), ordered compaction,
 // append to the store (MS:1325-1327) and the goal node (MS:1346-1347).
 // every thread of ONE CTA calls this (barriers inside)
@@ -868,18 +894,16 @@ static int step_enqueue(bgr_planner* pl, const PlanDev& d, float* x, float* y, f
     else
         BGR_CHECK(nns_nearest_counted(pl->nns, pl->uq.p, B + n_fixed, pl->unique_hint > 0 ? pl->unique_hint + pl->unique_hint / 4 + 8 : B + n_fixed,
                                       pl->counters.p + 10, n_fixed, pl->u_near.p, pl->u_dist.p));
-    plan_steer_kernel<<<gb, 256, 0, st>>>(d);
-    BGR_LAUNCH_CHECK();
-    BGR_CHECK(bgr_map_collide_spheres_dev(pl->map, pl->pnew.p, B, P.state_radius, pl->hit.p, pl->band.p));
-    if (P.flags & BGR_PLAN_DEDUP) {
-        plan_dedup_kernel<<<gb, 256, 0, st>>>(d);
+    {
+        // steer + state check + dedup + kNN skip flags, a warp per candidate (candidates the state check rejected
+        // never read their neighbour rows, and the copies of a goal / milestone candidate have the rows of the
+        // first one: their searches are skipped)
+        LevelGrid dil;
+        BGR_CHECK(map_sphere_gate(pl->map, P.state_radius, &dil));
+        plan_state_kernel<<<(unsigned)div_up(B, 4), 128, 0, st>>>(d, map_view(pl->map), dil, pl->kskip.p);
         BGR_LAUNCH_CHECK();
     }
     if (have_knn) {
-        // candidates the state check rejected never read their neighbour rows, and the copies of a goal /
-        // milestone candidate have the rows of the first one: skip their searches
-        plan_knn_rep_kernel<<<gb, 256, 0, st>>>(d, pl->kskip.p);
-        BGR_LAUNCH_CHECK();
         if (capped) BGR_CHECK(nns_knn_brute_cap(pl->nns, pl->pnew.p, B, K, pl->knn_idx.p, pl->knn_d2.p, kGraphCap, pl->counters.p + 15));
         else BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->kskip.p, pl->knn_idx.p, pl->knn_d2.p));
         plan_knn_spread_kernel<<<gbk, 256, 0, st>>>(d, pl->knn_d2.p);
@@ -891,9 +915,7 @@ static int step_enqueue(bgr_planner* pl, const PlanDev& d, float* x, float* y, f
         BGR_CHECK(bgr_map_collide_edges_dev(pl->map, pl->e1.p, pl->e2.p, (int64_t)B * K1, P.edge_radius, P.edge_shape,
                                             pl->ehit.p, pl->eband.p));
     }
-    plan_cost_kernel<<<gbk1, 256, 0, st>>>(d);
-    BGR_LAUNCH_CHECK();
-    plan_select_kernel<<<gb, 256, 0, st>>>(d);
+    plan_cost_select_kernel<<<(unsigned)div_up(B, 4), 128, 0, st>>>(d);
     BGR_LAUNCH_CHECK();
     plan_commit_kernel<<<1, 1024, 0, st>>>(d, x, y, z, f4);
     BGR_LAUNCH_CHECK();
