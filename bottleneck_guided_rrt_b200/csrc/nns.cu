@@ -121,7 +121,8 @@ void plan_scan(int64_t nq, int64_t n, int* R, int* chunks, int64_t* chunk_nodes)
     const int64_t resident = 3LL * sms;
     int64_t c = 1;
     if (qblocks < 2 * resident) c = div_up(2 * resident, qblocks);
-    c = std::min<int64_t>(c, std::max<int64_t>(1, tiles / 4));
+    static const int min_tiles = getenv("BGR_SCAN_MIN_TILES") ? std::max(1, atoi(getenv("BGR_SCAN_MIN_TILES"))) : 4;   // measurement aid
+    c = std::min<int64_t>(c, std::max<int64_t>(1, tiles / min_tiles));
     c = std::min<int64_t>(c, 64);
     int64_t per = div_up(tiles, c) * kTile;
     c = div_up(tiles * kTile, per);
