@@ -251,11 +251,20 @@ __device__ __forceinline__ int32_t slot_node(const PlanDev& d, int c, int j) {
     return d.have_knn ? d.knn_idx[(size_t)c * d.K + j] : -1;
 }
 
+// The goal / milestone samples of a batch are the same point, hence — against one snapshot — the same candidate:
+// same nearest node, steered point, state check, neighbour rows, candidate edges and chain costs.  rep_of(c) = the
+// first candidate of c's sample slot; the edge checks and the parent-chain walks run for it only and its copies
+// read its rows (in MS mode 80 % of a batch are such copies: 5x fewer walks and edges, identical results).
+__device__ __forceinline__ int rep_of(const PlanDev& d, int c) {
+    const int slot = d.qslot[c];
+    return slot < d.n_fixed ? d.B - (int)d.counters[11 + slot] : c;
+}
+
 __global__ void plan_edges_kernel(PlanDev d) {                 // edge list for isLineValid geometry
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= d.B * (d.K + 1)) return;
     const int c = t / (d.K + 1), j = t % (d.K + 1);
-    const int32_t ind = d.hit[c] ? -1 : slot_node(d, c, j);
+    const int32_t ind = (d.hit[c] || rep_of(d, c) != c) ? -1 : slot_node(d, c, j);
     float a[3], b[3];
     if (ind >= 0) {
         a[0] = d.x[ind]; a[1] = d.y[ind]; a[2] = d.z[ind];
@@ -291,7 +300,7 @@ __device__ float chain_cost(const PlanDev& d, int32_t P, float cx, float cy, flo
 __device__ __forceinline__ void plan_cost_body(const PlanDev& d, const int t) {
     if (t >= d.B * (d.K + 1)) return;
     const int c = t / (d.K + 1), j = t % (d.K + 1);
-    if (d.hit[c]) return;
+    if (d.hit[c] || rep_of(d, c) != c) return;
     const int32_t ind = slot_node(d, c, j);
     if (ind < 0) return;
     d.costs[t] = chain_cost(d, ind, d.pnew[3 * c], d.pnew[3 * c + 1], d.pnew[3 * c + 2], &d.psis[t]);
@@ -302,16 +311,17 @@ __device__ __forceinline__ void plan_select_body(const PlanDev& d, const int c) 
     if (c >= d.B) return;
     const bool edge_check = d.p.flags & BGR_PLAN_EDGE_CHECK, quirks = d.p.flags & BGR_PLAN_QUIRKS;
     const int K1 = d.K + 1;
+    const size_t r1 = (size_t)rep_of(d, c) * K1, rk = (size_t)rep_of(d, c) * d.K;   // rows of the slot's first candidate
     d.ok[c] = 0;
     long long band = d.band[c];
     if (edge_check && !d.hit[c])
         for (int j = 0; j < K1; ++j)
-            if (slot_node(d, c, j) >= 0) band += d.eband[(size_t)c * K1 + j];
+            if ((j == d.K ? d.near[c] : (d.have_knn ? d.knn_idx[rk + j] : -1)) >= 0) band += d.eband[r1 + j];
     if (band) atomicAdd((unsigned long long*)&d.counters[8], (unsigned long long)band);
     if (d.hit[c]) { atomicAdd((unsigned long long*)&d.counters[4], 1ull); return; }
-    if (edge_check && d.ehit[(size_t)c * K1 + d.K]) { atomicAdd((unsigned long long*)&d.counters[5], 1ull); return; }
+    if (edge_check && d.ehit[r1 + d.K]) { atomicAdd((unsigned long long*)&d.counters[5], 1ull); return; }
     int32_t parent_index = d.near[c];
-    float lowest = d.costs[(size_t)c * K1 + d.K];             // current_cost MS:1316
+    float lowest = d.costs[r1 + d.K];                         // current_cost MS:1316
     float mycost = lowest;
     int slot = d.K, pslot = d.K;
     if (d.have_knn) {
@@ -319,10 +329,10 @@ __device__ __forceinline__ void plan_select_body(const PlanDev& d, const int c) 
         for (int j = 0; j < d.K; ++j) {
             // an unfilled slot (fewer than K admissible nodes: the self-match rule drops the copies that
             // coincide with the candidate) has no cost: plan_cost_kernel left costs[] untouched for it
-            const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
+            const int32_t ind = d.knn_idx[rk + j];
             if (ind < 0) continue;
-            if (edge_check && d.ehit[(size_t)c * K1 + j]) continue;
-            const float temp = d.costs[(size_t)c * K1 + j];
+            if (edge_check && d.ehit[r1 + j]) continue;
+            const float temp = d.costs[r1 + j];
             if (temp < lowest) { pc = ind; lowest = temp; pslot = j; }
         }
         if (pc > 0) {
@@ -335,7 +345,7 @@ __device__ __forceinline__ void plan_select_body(const PlanDev& d, const int c) 
     const bool keep_near = quirks && d.found[c];
     d.parent[c] = keep_near ? d.near[c] : parent_index;
     d.cost[c] = mycost;
-    d.psi[c] = d.psis[(size_t)c * K1 + (keep_near ? d.K : slot)];   // follows the pointer actually committed
+    d.psi[c] = d.psis[r1 + (keep_near ? d.K : slot)];          // follows the pointer actually committed
     d.ok[c] = 1;
 }
 __global__ void plan_select_kernel(PlanDev d) { plan_select_body(d, blockIdx.x * blockDim.x + threadIdx.x); }
@@ -444,6 +454,9 @@ __device__ __forceinline__ bool rewire_proposal(const PlanDev& d, int t, int32_t
     const int c = t / d.K, j = t % d.K;
     const int32_t ni = d.new_index[c];
     if (ni < 0) return false;
+    // a copy of a goal / milestone candidate proposes the same new cost with a larger new index than the slot's first
+    // candidate (accepted whenever a copy is): its key can never be the minimum
+    if (rep_of(d, c) != c) return false;
     const int32_t ind = d.knn_idx[(size_t)c * d.K + j];
     if (ind <= 0 || ind == d.par[ni]) return false;
     if ((d.p.flags & BGR_PLAN_EDGE_CHECK) && d.ehit[(size_t)c * (d.K + 1) + j]) return false;
@@ -906,8 +919,7 @@ static int step_enqueue(bgr_planner* pl, const PlanDev& d, float* x, float* y, f
     if (have_knn) {
         if (capped) BGR_CHECK(nns_knn_brute_cap(pl->nns, pl->pnew.p, B, K, pl->knn_idx.p, pl->knn_d2.p, kGraphCap, pl->counters.p + 15));
         else BGR_CHECK(bgr_nns_knn_skip_dev(pl->nns, pl->pnew.p, B, K, 0u, pl->kskip.p, pl->knn_idx.p, pl->knn_d2.p));
-        plan_knn_spread_kernel<<<gbk, 256, 0, st>>>(d, pl->knn_d2.p);
-        BGR_LAUNCH_CHECK();
+        // (the copies' rows are never read: edges, costs, parent choice and rewire proposals go through rep_of)
     }
     if (edge_check) {
         plan_edges_kernel<<<gbk1, 256, 0, st>>>(d);
@@ -915,8 +927,17 @@ static int step_enqueue(bgr_planner* pl, const PlanDev& d, float* x, float* y, f
         BGR_CHECK(bgr_map_collide_edges_dev(pl->map, pl->e1.p, pl->e2.p, (int64_t)B * K1, P.edge_radius, P.edge_shape,
                                             pl->ehit.p, pl->eband.p));
     }
-    plan_cost_select_kernel<<<(unsigned)div_up(B, 4), 128, 0, st>>>(d);
-    BGR_LAUNCH_CHECK();
+    if (P.flags & BGR_PLAN_DEDUP) {
+        // no live copies (dedup rejected them): costs and parent choice of a candidate in one warp
+        plan_cost_select_kernel<<<(unsigned)div_up(B, 4), 128, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+    } else {
+        // copies read the rows of their slot's first candidate: all costs first, then the choices
+        plan_cost_kernel<<<gbk1, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+        plan_select_kernel<<<gb, 256, 0, st>>>(d);
+        BGR_LAUNCH_CHECK();
+    }
     plan_commit_kernel<<<1, 1024, 0, st>>>(d, x, y, z, f4);
     BGR_LAUNCH_CHECK();
     if (rewire && have_knn) {
