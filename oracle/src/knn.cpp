@@ -84,7 +84,8 @@ int orc_knn_brute(const float* cloud, int64_t n, const float* q, int64_t nq, int
 static std::atomic<long long> g_pow_sqrt_mismatch{0};
 float orc_pow_root(double s) {
     const float r = (float)std::pow(s, 0.5);
-    if (r != (float)std::sqrt(s)) g_pow_sqrt_mismatch.fetch_add(1, std::memory_order_relaxed);
+    const float q = (float)std::sqrt(s);
+    if (r != q && !(r != r && q != q)) g_pow_sqrt_mismatch.fetch_add(1, std::memory_order_relaxed);   // NaN == NaN here
     return r;
 }
 float orc_norm(const float* a, const float* b) {

@@ -341,3 +341,27 @@ def test_knn_pinned_result_buffers_written_by_the_kernel(bgr, oracle):
         ih.fill_(-9)
         nns.knn(qp, 16, indices=ih.numpy(), want_dists2=False)
         assert np.array_equal(ih.numpy(), ri)
+
+
+def test_nearest_scan_edge_cases(bgr, oracle):
+    """the plain Nearest scan runs an f32 filter before the reference's mixed
+    f32 / f64 arithmetic: it must never lose the reference's answer — large coordinates (coarse filter), queries on
+    nodes, a hair away from them, far, astronomically far, infinite and NaN; duplicated nodes (last index wins)"""
+    rng = np.random.default_rng(13)
+    base = oracle.points(2, 40_000, 6.4)
+    pts = np.concatenate([base + np.float32(500.0), base[:5000] + np.float32(500.0), base[:3000] * np.float32(1e-3)]).astype(np.float32)
+    q = np.concatenate([
+        pts[rng.integers(0, len(pts), 600)],
+        pts[rng.integers(0, len(pts), 600)] + rng.normal(0, 1e-4, (600, 3)).astype(np.float32),
+        oracle.points(3, 600, 6.4) + np.float32(500.0),
+        rng.uniform(-2000, 2000, (300, 3)).astype(np.float32),
+        np.array([[1e6, -1e6, 3], [1e12, 0, 0], [1e18, 1e18, -1e18], [3e25, 0, 1], [np.inf, 0, 0], [0, -np.inf, 5], [np.nan, 1, 1],
+                  [0, 0, 0], [500, 500, 500]], dtype=np.float32)]).astype(np.float32)
+    nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
+    nns.set_method(bgr.METHOD_BRUTE)
+    gi, gd = nns.nearest(q)
+    oi, od = oracle.nearest(pts, q)
+    ok = ~np.isnan(q).any(axis=1)       # a NaN query compares false with everything: the library reports "no node" (-1)
+    assert np.array_equal(gi[ok], oi[ok]), np.nonzero(gi != oi)[0][:10]
+    assert np.array_equal(gd[ok].view(np.uint32), od[ok].view(np.uint32))
+    assert (gi[~ok] == -1).all()
