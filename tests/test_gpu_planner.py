@@ -480,3 +480,46 @@ def test_graph_replay_with_rearmed_planner(bgr, oracle, world):
         assert gw == gf
         _same_gpu_trees(w, f)
     assert w.persist_stats()["graph_steps"] > 10
+
+
+def test_config4_query_shape_parity(bgr, oracle):
+    """BASELINE configs[4](i) shape: one start/goal query on the 256^3 query map of bench.py (0.4 m doors, light
+    clutter), MS sampler with the door-centre milestones, batch 1024, K = 16, edge checks + rewiring +
+    BGR_PLAN_DEDUP, the planner on a stream of its own (so its steps are replayed as a CUDA graph while the tree is
+    small, then host-driven): tree bit for bit against oracle/src/planner.cpp on every batch before the first
+    in-band collision event, goal flag included."""
+    import torch
+    from bottleneck_guided_rrt_b200 import synth
+    import bench
+    occ = synth.make_map(256, 5, n_walls=3, wall_thick=4, door_cells=bench.QUERY_DOOR_CELLS, occupancy=bench.QUERY_OCCUPANCY)
+    boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
+    ms = bench.door_milestones(occ, 256)
+    table = synth.points(9, 200_000, 12.8)
+    st = torch.cuda.Stream()
+    m = bgr.OccupancyMap(0.05, (0, 0, 0), (256,) * 3, stream=st.cuda_stream)
+    m.set_boxes(boxes)
+    cand = synth.points(77, 4000, 12.8)
+    hit, _ = m.collide_spheres(cand, 0.1)
+    free = cand[np.asarray(hit) == 0]
+    flags = bgr.PLAN_EDGE_CHECK | bgr.PLAN_REWIRE | bgr.PLAN_DEDUP
+    compared = 0
+    for qi in (0, 3):
+        P = bgr.PlannerParams(tuple(free[2 * qi]), tuple(free[2 * qi + 1]), mode=bgr.PLAN_MODE_MS, k=16, batch=1024, flags=flags, seed=100 + qi)
+        n_batches = 40
+        first = _first_band_batch(bgr.Planner(P, m, table, ms, stream=st.cuda_stream), 1 << 30, n_batches)
+        if first is not None:
+            n_batches = first
+        if n_batches < 5:
+            continue
+        gp = bgr.Planner(P, m, table, ms, stream=st.cuda_stream)
+        op = oracle.Planner(P, boxes, table, ms, collision_mode=2)
+        before = oracle.pow_sqrt_mismatches()
+        g_goal, o_goal = gp.run(1 << 30, n_batches), op.run(1 << 30, n_batches)
+        torch.cuda.synchronize()
+        assert gp.stats()["in_band"] == 0
+        gs = _assert_same_tree(gp, op, g_goal, o_goal)
+        assert gs["rejected_state"] > 0 and len(gp) > 1000
+        assert gp.persist_stats()["graph_steps"] > 0
+        assert oracle.pow_sqrt_mismatches() == before
+        compared += 1
+    assert compared >= 1
