@@ -1630,6 +1630,23 @@ int bgr_map_collide_edges(bgr_map* h, const float* p1, const float* p2, int64_t 
                           uint8_t* hit, uint8_t* band) {
     BGR_ARG(h != nullptr && n >= 0 && (n == 0 || (p1 && p2 && hit)), "bad collide_edges arguments");
     if (n == 0) return BGR_OK;
+    // experiment (BGR_EDGES_ZEROCOPY=1): page-locked caller buffers are read and written by the kernels themselves over
+    // the host link (UVA device pointers), instead of staged copies
+    static const bool zero_copy = getenv("BGR_EDGES_ZEROCOPY") && getenv("BGR_EDGES_ZEROCOPY")[0] == '1';
+    if (zero_copy) {
+        cudaPointerAttributes a1{}, a2{}, ah{}, ab{};
+        const bool ok = cudaPointerGetAttributes(&a1, p1) == cudaSuccess && a1.type == cudaMemoryTypeHost && a1.devicePointer &&
+                        cudaPointerGetAttributes(&a2, p2) == cudaSuccess && a2.type == cudaMemoryTypeHost && a2.devicePointer &&
+                        cudaPointerGetAttributes(&ah, hit) == cudaSuccess && ah.type == cudaMemoryTypeHost && ah.devicePointer &&
+                        (!band || (cudaPointerGetAttributes(&ab, band) == cudaSuccess && ab.type == cudaMemoryTypeHost && ab.devicePointer));
+        (void)cudaGetLastError();
+        if (ok) {
+            BGR_CHECK(bgr_map_collide_edges_dev(h, (const float*)a1.devicePointer, (const float*)a2.devicePointer, n, radius, shape,
+                                                (uint8_t*)ah.devicePointer, band ? (uint8_t*)ab.devicePointer : nullptr));
+            BGR_CUDA(cudaStreamSynchronize(h->stream));
+            return BGR_OK;
+        }
+    }
     BGR_CHECK(h->p1_dev.reserve(3 * n, h->stream, false));
     BGR_CHECK(h->p2_dev.reserve(3 * n, h->stream, false));
     BGR_CHECK(h->hit_dev.reserve(n, h->stream, false));
