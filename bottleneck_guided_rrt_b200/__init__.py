@@ -9,6 +9,7 @@ has not been built — there is no CPU fallback anywhere in the product path.
 from .capi import (  # noqa: F401
     ALLOW_SELF_MATCH,
     SORT_RESULTS,
+    KNN_STATIC_MAX_RESULTS,
     TOUCH_STATISTICS,
     METHOD_AUTO,
     METHOD_BRUTE,

@@ -14,6 +14,7 @@ import numpy as np
 
 ALLOW_SELF_MATCH = 1
 SORT_RESULTS = 2
+KNN_STATIC_MAX_RESULTS = 32768   # BGR_KNN_STATIC_MAX_RESULTS (bgr_nns_knn_scan_static_dev)
 TOUCH_STATISTICS = 1
 METHOD_AUTO, METHOD_BRUTE, METHOD_GRID, METHOD_GRID_GENERAL = 0, 1, 2, 3
 SHAPE_CYLINDER, SHAPE_CAPSULE = 0, 1
@@ -66,6 +67,7 @@ def lib():
     L.bgr_nns_nearest_dev.argtypes = [vp, vp, i64, vp, vp]
     L.bgr_nns_debug_stats.argtypes = [vp, vp]
     L.bgr_nns_knn_skip_dev.argtypes = [vp, vp, i64, i32, C.c_uint, vp, vp, vp]
+    L.bgr_nns_knn_scan_static_dev.argtypes = [vp, vp, i64, i32, C.c_uint, f32, vp, vp, vp]
     L.bgr_nns_set_tile.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int]
     L.bgr_nns_tile_stats.argtypes = [vp, vp]
     L.bgr_nns_destroy.argtypes = [vp]
@@ -250,6 +252,15 @@ class NNSearchF:
         """bgr_nns_knn_skip_dev: CUDA tensors only; rows of queries with a non-zero skip byte are left untouched"""
         _check(lib().bgr_nns_knn_skip_dev(self._h, _ptr(d_query), d_query.shape[0], k, optionFlags, _ptr(d_skip),
                                           _ptr(d_indices), _ptr(d_dists2)))
+
+    def knn_scan_static(self, d_query, k, d_indices, d_dists2, optionFlags=0, maxRadius=float("inf")):
+        """bgr_nns_knn_scan_static_dev: the allocation-free plain scan (CUDA tensors only; nq * k <=
+        KNN_STATIC_MAX_RESULTS; partial lists in the library's static device array).  Returns the number of
+        node chunks the scan used (1 = the static scratch was not needed)."""
+        chunks = C.c_int(0)
+        _check(lib().bgr_nns_knn_scan_static_dev(self._h, _ptr(d_query), d_query.shape[0], k, optionFlags, maxRadius,
+                                                 _ptr(d_indices), _ptr(d_dists2), C.byref(chunks)))
+        return chunks.value
 
     def set_tile(self, tx=0, ty=0, tz=0, warps=0):
         """tile kNN tuning (bgr_nns_set_tile): all 0 = automatic, tx < 0 = tile search off"""

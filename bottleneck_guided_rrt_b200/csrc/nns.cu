@@ -601,3 +601,96 @@ int nns_knn_brute_cap(bgr_nns* h, const float* d_q, int64_t nq, int k, int32_t* 
 void nns_scan_scratch(bgr_nns* h, const void** a, const void** b) { *a = h->part_idx.p; *b = h->part_d2.p; }
 int nns_method(const bgr_nns* h) { return h->method; }
 }  // namespace bgr
+
+// ---------------------------------------------------------------------------------------------------------
+// bgr_nns_knn_scan_static_dev — the brute-force kNN scan for callers that may not allocate (no counterpart in
+// the reference).  knn_brute_dev above keeps the per-chunk
+// partial lists of a chunked scan in the handle's part_idx / part_d2 buffers, which grow with cudaMalloc.  Here
+// the same kernels (knn_brute_kernel, knn_merge_kernel) write / read those partial lists in ONE file-scope
+// device array of fixed size, so the call allocates nothing: no cudaMalloc / cudaFree, no allocating library call.
+//   * limit  : nq * k <= BGR_KNN_STATIC_MAX_RESULTS (32,768 results, e.g. 2,048 queries x k = 16) and at most
+//              kStaticMaxChunks (16) node chunks -> 16 * 32,768 * (4 + 4) bytes = 4 MiB, held by every GPU that
+//              loads the library until the process exits;
+//   * address: in host code the array's NAME is a host-side stand-in, not a device address; the device address
+//              comes from cudaGetSymbolAddress, asked once per device with that device current (below);
+//   * sharing: every call (all handles, all streams) uses the same array, and it keeps the last call's contents.
+//              Nothing in it has to start at zero: every chunk's CTAs write each of their nq * k slots (lists
+//              padded with idx = -1, d2 = +inf) before the merge kernel, ordered behind them on the handle's
+//              stream, reads exactly those slots.  Two calls that overlap on the GPU (different streams, or
+//              different host threads on different streams) RACE on the array: serialize them.
+namespace {
+constexpr int64_t kStaticMaxResults = BGR_KNN_STATIC_MAX_RESULTS;
+constexpr int kStaticMaxChunks = 16;
+constexpr size_t kStaticHalf = (size_t)kStaticMaxChunks * kStaticMaxResults * sizeof(int32_t);   // idx half, then d2 half
+static_assert(sizeof(int32_t) == sizeof(float), "the two halves have equal size");
+}  // namespace
+static __device__ __align__(256) unsigned char g_knn_static_scratch[2 * kStaticHalf];
+
+namespace {
+// device address of g_knn_static_scratch on the CURRENT device (== device, checked by the caller)
+int knn_static_scratch(int device, unsigned char** out) {
+    static std::atomic<unsigned char*> addr[kMaxDevices];
+    BGR_ARG(device >= 0 && device < kMaxDevices, "device %d outside the static scratch table (%d devices)", device, kMaxDevices);
+    unsigned char* p = addr[device].load(std::memory_order_acquire);
+    if (!p) {
+        void* sym = nullptr;
+        BGR_CUDA(cudaGetSymbolAddress(&sym, g_knn_static_scratch));
+        if (!sym) {
+            set_error("cudaGetSymbolAddress returned a null address for the static kNN scratch");
+            return BGR_ERR_CUDA;
+        }
+        p = static_cast<unsigned char*>(sym);
+        addr[device].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return BGR_OK;
+}
+}  // namespace
+
+extern "C" int bgr_nns_knn_scan_static_dev(bgr_nns* h, const float* d_q, int64_t nq, int k, unsigned flags,
+                                           float max_radius, int32_t* d_idx, float* d_d2, int* chunks_used) {
+    BGR_CHECK(check_knn_args(h, nq, k, 0.f, flags, max_radius));
+    BGR_ARG(nq == 0 || (d_q && d_idx && d_d2), "null query/result buffer");
+    BGR_ARG(nq * (int64_t)k <= kStaticMaxResults,
+            "nq * k = %lld results exceed the static scratch limit of %lld (BGR_KNN_STATIC_MAX_RESULTS): split the "
+            "batch or use bgr_nns_knn_dev", (long long)(nq * (int64_t)k), (long long)kStaticMaxResults);
+    BGR_CHECK(check_device(h->device));
+    if (chunks_used) *chunks_used = 0;
+    if (nq == 0) return BGR_OK;
+    unsigned char* scratch = nullptr;
+    BGR_CHECK(knn_static_scratch(h->device, &scratch));
+    int R, chunks;
+    int64_t per;
+    plan_scan(nq, h->n, &R, &chunks, &per);
+    if (chunks > kStaticMaxChunks) {
+        const int64_t tiles = div_up(h->n, kTile);
+        per = div_up(tiles, (int64_t)kStaticMaxChunks) * kTile;
+        chunks = (int)div_up(tiles * kTile, per);
+    }
+    BruteArgs a;
+    a.x = h->x.p; a.y = h->y.p; a.z = h->z.p; a.f4 = h->f4.p; a.n = h->n; a.n_dev = nullptr;
+    a.q = d_q; a.nq = nq; a.k = k; a.flags = flags;
+    a.max_radius = max_radius; a.max_radii = nullptr;
+    a.chunk_nodes = per;
+    a.index_base = h->index_base;
+    int32_t* part_idx = reinterpret_cast<int32_t*>(scratch);
+    float* part_d2 = reinterpret_cast<float*>(scratch + kStaticHalf);
+    if (chunks == 1) {
+        a.idx = d_idx; a.d2 = d_d2;          // a single chunk has no partial lists: straight into the caller's rows
+    } else {
+        a.idx = part_idx; a.d2 = part_d2;
+    }
+    switch (R) {
+        case 8: BGR_CHECK(launch_brute<8>(h, a, chunks)); break;
+        case 4: BGR_CHECK(launch_brute<4>(h, a, chunks)); break;
+        case 2: BGR_CHECK(launch_brute<2>(h, a, chunks)); break;
+        default: BGR_CHECK(launch_brute<1>(h, a, chunks)); break;
+    }
+    h->n_brute++;
+    if (chunks > 1) {
+        knn_merge_kernel<<<(unsigned)div_up(nq, 8), 256, 0, h->stream>>>(part_idx, part_d2, chunks, nq * k, nq, k, d_idx, d_d2);
+        BGR_LAUNCH_CHECK();
+    }
+    if (chunks_used) *chunks_used = chunks;
+    return BGR_OK;
+}

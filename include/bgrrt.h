@@ -113,6 +113,22 @@ int bgr_nns_knn_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, float
  * (isStateValid MS:1270 comes before the knn MS:1312: rejected candidates never search). */
 int bgr_nns_knn_skip_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, unsigned flags,
                          const uint8_t* d_skip, int32_t* d_idx_kxQ, float* d_d2_kxQ);
+/* Allocation-free form of the brute-force kNN scan.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same search and same results as
+ * bgr_nns_knn_dev with eps = 0 and no per-query radii (exact (d2, index) order, rows padded with
+ * idx = -1, d2 = +inf), always by the plain scan; device pointers only; runs on the handle's stream.
+ * The per-chunk partial lists of the scan live in ONE fixed 4 MiB `static __device__` array of the
+ * library (held by every GPU that loads it until exit) instead of the handle's growable scratch, so
+ * the call makes no cudaMalloc / cudaFree and no allocating library call.
+ * Limit: nq * k <= BGR_KNN_STATIC_MAX_RESULTS; larger batches return BGR_ERR_ARG (split the batch,
+ * or use bgr_nns_knn_dev).  Every call of the process shares the array and it keeps the last
+ * call's contents (nothing in it has to start at zero: each call writes every slot it later reads):
+ * calls that overlap on the GPU — different streams — race on it and must be serialized.
+ * chunks_used (may be NULL) receives the number of node chunks, 1 = the scratch was not needed. */
+#define BGR_KNN_STATIC_MAX_RESULTS 32768
+int bgr_nns_knn_scan_static_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int k, unsigned flags,
+                                float max_radius, int32_t* d_idx_kxQ, float* d_d2_kxQ, int* chunks_used);
 
 /* Replaces Nearest(V, x) (MS:138-154) for a batch of x: Norm in the reference's mixed
  * precision (f32 differences, f64 squares/sum/sqrt, f32 result), `<=` so the LAST index
