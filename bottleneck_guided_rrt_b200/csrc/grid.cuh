@@ -344,7 +344,8 @@ constexpr int kFastTries = 3;
 // and the long scans (unsorted tail, rows longer than a warp) keep 3 x 32 nodes in flight; the lean
 // instantiation serves uniform clouds, where neither occurs and the extra registers would spill.
 template <bool PILED>
-__device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64_t qi, unsigned long long* cand_w, const int lane) {
+__device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64_t qi, unsigned long long* cand_w, const int lane,
+                                               const bool allow_fast = true) {
     const float qx = __ldg(a.q + 3 * qi), qy = __ldg(a.q + 3 * qi + 1), qz = __ldg(a.q + 3 * qi + 2);
     const bool self = (a.flags & BGR_ALLOW_SELF_MATCH) != 0;
     const uint32_t sent = radius_sentinel_g(a.max_radii ? __ldg(a.max_radii + qi) : a.max_radius);
@@ -378,7 +379,7 @@ __device__ __forceinline__ void grid_knn_query(const GridKnnArgs& a, const int64
     };
 
     // ------------------------------------------------------------------ fast path
-    if (a.n_indexed > 0 && a.fast) {
+    if (a.n_indexed > 0 && a.fast && allow_fast) {
         // the 9 x-rows of ring 1: lane t < 9 owns row (dy,dz)
         int rs = 0, re = 0;
         if (lane < 9) {

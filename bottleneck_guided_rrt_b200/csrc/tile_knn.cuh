@@ -32,6 +32,7 @@
 #include <atomic>
 #include <cstdio>
 #include "grid.cuh"
+#include "grid_pair.cuh"
 
 namespace bgr {
 
@@ -534,7 +535,12 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
         a.heavy = G.heavy.p; a.heavy_cap = kHeavyCap;
         a.heavy_min = std::max<int64_t>(2048, n / 128);
     }
+    // fully indexed, uncrowded cloud (no unsorted tail, no piles): two queries per warp (grid_pair.cuh);
+    // BGR_KNN_PAIR=0 keeps the warp-per-query kernel (measurement / test aid, read per call)
+    bool pair = fast == 1 && !a.heavy && G.n_indexed > 0 && G.n_indexed == n && nq >= 2;
+    if (pair) { const char* e = getenv("BGR_KNN_PAIR"); if (e && e[0] == '0') pair = false; }
     if (a.heavy) grid_knn_kernel<true><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
+    else if (pair) grid_knn_pair_kernel<<<(unsigned)div_up(nq, 2 * kPairWarps), kPairWarps * 32, 0, st>>>(a);
     else grid_knn_kernel<false><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
     if (a.heavy) G.n_piled++; else G.n_lean++;

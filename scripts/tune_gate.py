@@ -21,7 +21,8 @@ hit = torch.empty(len(p1), dtype=torch.uint8, device=dev)
 band = torch.empty(len(p1), dtype=torch.uint8, device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 ref = None
-for cfg in ["8,0", "4,4", "4,2", "4,3", "4,6", "4,8", "8,1", "8,2", "8,3", "2,4", "2,8", "16,1", "4,32", "8,16"]:
+CFGS = os.environ.get("BGR_TUNE_CFGS", "8,0 4,4 4,2 4,3 4,6 4,8 8,1 8,2 8,3 2,4 2,8 16,1 4,32 8,16").split()
+for cfg in CFGS:
     os.environ["BGR_GATE"] = cfg
     for _ in range(3):
         m.collide_edges(d1, d2, 0.03, 0, hit=hit, band=band)
