@@ -351,7 +351,7 @@ def knn_section(c, out):
     fp32_peak = 148 * FP32_NOFMA_LANES * pk["sm_max_mhz"] * 1e6 / 1e12     # TFLOP/s, non-FMA
     achieved = 8.0 * pairs_per_step / (ms_per_step * 1e-3) / 1e12
     alg_bytes = 12.0 * N_NODES + 12.0 * N_QUERIES + 8.0 * K_NN * N_QUERIES
-    kname = "grid_knn_kernel" if args.method != "brute" else "knn_brute_kernel"
+    kname = "grid_knn_group_kernel" if args.method != "brute" else "knn_brute_kernel"
     d2h_bytes = int(8 * K_NN * N_QUERIES)
     out.update({
         "value": value, "ms_per_step": ms_per_step, "ms_per_step_per_rank": knn_ms_ranks, "brute_scan": brute,

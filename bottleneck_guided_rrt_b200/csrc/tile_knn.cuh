@@ -32,7 +32,7 @@
 #include <atomic>
 #include <cstdio>
 #include "grid.cuh"
-#include "grid_pair.cuh"
+#include "grid_group.cuh"
 
 namespace bgr {
 
@@ -520,6 +520,7 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
     a.fast = fast;
     a.skip = d_skip;
     a.fast_target = (float)k + 2.5f * sqrtf((float)k) + 1.f;
+    if (const char* e = getenv("BGR_FAST_TARGET")) { const float f = (float)atof(e); if (f > 0.f) a.fast_target = (float)k + f * sqrtf((float)k) + 1.f; }   // measurement aid
     a.heavy = nullptr; a.heavy_cap = 0; a.heavy_min = 0;
     const bool crowded = G.crowd > 64.0;
     // large batches over a fully indexed, uncrowded cloud: one lane per query out of staged tiles
@@ -535,12 +536,13 @@ inline int grid_knn(GridIndex& G, const float* x, const float* y, const float* z
         a.heavy = G.heavy.p; a.heavy_cap = kHeavyCap;
         a.heavy_min = std::max<int64_t>(2048, n / 128);
     }
-    // fully indexed, uncrowded cloud (no unsorted tail, no piles): two queries per warp (grid_pair.cuh);
-    // BGR_KNN_PAIR=0 keeps the warp-per-query kernel (measurement / test aid, read per call)
-    bool pair = fast == 1 && !a.heavy && G.n_indexed > 0 && G.n_indexed == n && nq >= 2;
-    if (pair) { const char* e = getenv("BGR_KNN_PAIR"); if (e && e[0] == '0') pair = false; }
+    // fully indexed, uncrowded cloud (no unsorted tail, no piles): several queries per warp (grid_group.cuh);
+    // BGR_KNN_GROUP=0 keeps the warp-per-query kernel, 16 / 8 picks the lanes per query (measurement / test aid, read per call)
+    int group = (fast == 1 && !a.heavy && G.n_indexed > 0 && G.n_indexed == n && nq >= 2) ? kGroupLanesDefault : 0;
+    if (group) { const char* e = getenv("BGR_KNN_GROUP"); if (e) { const int v = atoi(e); if (v == 0 || v == 8 || v == 16) group = v; } }
     if (a.heavy) grid_knn_kernel<true><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
-    else if (pair) grid_knn_pair_kernel<<<(unsigned)div_up(nq, 2 * kPairWarps), kPairWarps * 32, 0, st>>>(a);
+    else if (group == 16) grid_knn_group_kernel<16><<<(unsigned)div_up(nq, 2 * kGroupWarps), kGroupWarps * 32, 0, st>>>(a);
+    else if (group == 8) grid_knn_group_kernel<8><<<(unsigned)div_up(nq, 4 * kGroupWarps), kGroupWarps * 32, 0, st>>>(a);
     else grid_knn_kernel<false><<<(unsigned)div_up(nq, 8), 256, 0, st>>>(a);
     BGR_LAUNCH_CHECK();
     if (a.heavy) G.n_piled++; else G.n_lean++;

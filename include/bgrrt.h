@@ -137,7 +137,7 @@ int bgr_nns_nearest(bgr_nns* nns, const float* q_3xQ, int64_t nq, int32_t* idx, 
 int bgr_nns_nearest_dev(bgr_nns* nns, const float* d_q_3xQ, int64_t nq, int32_t* d_idx,
                         float* d_dist);
 /* test / measurement aid — which code paths this handle has run so far: [0] grid index builds,
- * [1] grid_knn_kernel launches (uniform clouds), [2] launches of its crowded-index instantiation,
+ * [1] grid_knn_kernel / grid_knn_group_kernel launches (uniform clouds), [2] launches of the crowded-index instantiation,
  * [3] queries the LAST crowded launch handed to grid_knn_heavy_kernel (may exceed its 256 slots: the
  * rest ran the ring search), [4] grid_nearest_kernel launches, [5] nearest_kernel (plain scan)
  * launches, [6] knn_brute_kernel launches, [7] nodes covered by the current index */

@@ -1,4 +1,4 @@
-"""grid_knn_pair_kernel (two queries per warp) against grid_knn_kernel (BGR_KNN_PAIR=0) on configs[1]
+"""grid_knn_group_kernel<16 | 8> (a query per 16 / 8 lanes) against grid_knn_kernel (BGR_KNN_GROUP=0) on configs[1]
 (1 M uniform nodes, 65,536 queries, k = 16): kernel ms by CUDA events with an L2 flush between iterations, rows
 compared bit for bit.  usage: python scripts/exp_pair_knn.py [n] [nq] [k]"""
 import os
@@ -25,8 +25,8 @@ d2 = torch.empty((nq, k), dtype=torch.float32, device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 res = {}
 for rnd in range(2):
-    for pair in ("0", "1"):
-        os.environ["BGR_KNN_PAIR"] = pair
+    for pair in ("0", "16", "8"):
+        os.environ["BGR_KNN_GROUP"] = pair
         for _ in range(3):
             nns.knn(dq, k, 0.0, 0, indices=idx, dists2=d2)
         torch.cuda.synchronize()
@@ -40,6 +40,6 @@ for rnd in range(2):
             torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
         res[pair] = (idx.cpu().numpy().copy(), d2.cpu().numpy().copy())
-        print("pair=%s  n %d nq %d k %d: mean %.4f ms  min %.4f ms  (%.3g queries/s at the mean)" % (pair, n, nq, k, np.mean(ts), np.min(ts), nq / np.mean(ts) * 1e3))
-same = np.array_equal(res["0"][0], res["1"][0]) and np.array_equal(res["0"][1].view(np.uint32), res["1"][1].view(np.uint32))
+        print("lanes per query=%s  n %d nq %d k %d: mean %.4f ms  min %.4f ms  (%.3g queries/s at the mean)" % (pair, n, nq, k, np.mean(ts), np.min(ts), nq / np.mean(ts) * 1e3))
+same = all(np.array_equal(res["0"][0], res[v][0]) and np.array_equal(res["0"][1].view(np.uint32), res[v][1].view(np.uint32)) for v in ("16", "8"))
 print("rows identical:", same)

@@ -1,5 +1,5 @@
-"""GPU parity: grid_knn_pair_kernel (two queries per warp, grid_pair.cuh) against the CPU oracle and against
-the warp-per-query kernel (BGR_KNN_PAIR=0), bit-exact.  Reference surface: Nabo::NNSearchF::knn
+"""GPU parity: grid_knn_group_kernel<LQ> (a query per group of 16 / 8 lanes, grid_group.cuh) against the CPU oracle
+and against the warp-per-query kernel (BGR_KNN_GROUP=0), bit-exact.  Reference surface: Nabo::NNSearchF::knn
 (rrt_star_milestones.cpp:1309-1312)."""
 import os
 
@@ -9,17 +9,17 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _knn(bgr, nns, q, k, flags=0, max_radius=np.inf, max_radii=None, pair=True):
-    old = os.environ.get("BGR_KNN_PAIR")
-    os.environ["BGR_KNN_PAIR"] = "1" if pair else "0"
+def _knn(bgr, nns, q, k, flags=0, max_radius=np.inf, max_radii=None, lanes=16):
+    old = os.environ.get("BGR_KNN_GROUP")
+    os.environ["BGR_KNN_GROUP"] = str(lanes)
     try:
         nns.set_method(bgr.METHOD_GRID)
         idx, d2, _ = nns.knn(q, k, 0.0, flags, max_radius, max_radii)
     finally:
         if old is None:
-            del os.environ["BGR_KNN_PAIR"]
+            del os.environ["BGR_KNN_GROUP"]
         else:
-            os.environ["BGR_KNN_PAIR"] = old
+            os.environ["BGR_KNN_GROUP"] = old
     return idx, d2
 
 
@@ -29,21 +29,23 @@ def _same(a, b):
 
 @pytest.mark.parametrize("n,nq,k", [(200000, 4097, 16), (60000, 1001, 8), (30000, 3, 16), (30000, 2, 1), (90000, 555, 32),
                                     (120000, 2048, 24)])
-def test_pair_matches_oracle_and_warp_kernel(bgr, oracle, n, nq, k):
+@pytest.mark.parametrize("lanes", [16, 8])
+def test_group_matches_oracle_and_warp_kernel(bgr, oracle, lanes, n, nq, k):
     pts = oracle.points(31, n, 25.6)
     q = oracle.points(32, nq, 25.6)
     nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
     try:
-        pair = _knn(bgr, nns, q, k)
-        warp = _knn(bgr, nns, q, k, pair=False)
-        assert _same(pair, warp), "pair kernel differs from the warp-per-query kernel"
+        pair = _knn(bgr, nns, q, k, lanes=lanes)
+        warp = _knn(bgr, nns, q, k, lanes=0)
+        assert _same(pair, warp), "group kernel differs from the warp-per-query kernel"
         oi, od = oracle.knn_brute(pts, q, k, 0, np.inf, None)
-        assert _same(pair, (oi, od)), "pair kernel differs from the oracle"
+        assert _same(pair, (oi, od)), "group kernel differs from the oracle"
     finally:
         nns.close()
 
 
-def test_pair_self_match_radius_and_ties(bgr, oracle):
+@pytest.mark.parametrize("lanes", [16, 8])
+def test_group_self_match_radius_and_ties(bgr, oracle, lanes):
     # queries = nodes (self-match rule), a radius limit that leaves rows partly empty, per-query radii
     pts = oracle.points(33, 80000, 25.6)
     q = np.concatenate([pts[1000:2001], oracle.points(34, 700, 25.6)]).astype(np.float32)
@@ -51,11 +53,11 @@ def test_pair_self_match_radius_and_ties(bgr, oracle):
     try:
         for flags in (0, bgr.ALLOW_SELF_MATCH | bgr.SORT_RESULTS):
             for mr in (np.inf, 0.45, 0.05):
-                pair = _knn(bgr, nns, q, 12, flags, mr)
+                pair = _knn(bgr, nns, q, 12, flags, mr, lanes=lanes)
                 oi, od = oracle.knn_brute(pts, q, 12, flags, mr, None)
                 assert _same(pair, (oi, od)), (flags, mr)
         radii = np.abs(oracle.points(35, len(q), 1.0)[:, 0]).astype(np.float32) * np.float32(0.6)
-        pair = _knn(bgr, nns, q, 10, 0, np.inf, radii)
+        pair = _knn(bgr, nns, q, 10, 0, np.inf, radii, lanes=lanes)
         oi, od = oracle.knn_brute(pts, q, 10, 0, np.inf, radii)
         assert _same(pair, (oi, od))
     finally:
@@ -69,14 +71,15 @@ def test_pair_self_match_radius_and_ties(bgr, oracle):
     try:
         for k in (6, 16, 27):
             for flags in (0, bgr.ALLOW_SELF_MATCH):
-                pair = _knn(bgr, nns, ql, k, flags)
+                pair = _knn(bgr, nns, ql, k, flags, lanes=lanes)
                 oi, od = oracle.knn_brute(lat, ql, k, flags, np.inf, None)
                 assert _same(pair, (oi, od)), (k, flags)
     finally:
         nns.close()
 
 
-def test_pair_sparse_queries_far_outside_and_skip(bgr, oracle):
+@pytest.mark.parametrize("lanes", [16, 8])
+def test_group_sparse_queries_far_outside_and_skip(bgr, oracle, lanes, monkeypatch):
     import torch
     # a cloud in one corner: most queries find an empty ring-1 block or need ring 2 (general search per half)
     pts = (oracle.points(36, 50000, 6.4)).astype(np.float32)
@@ -84,7 +87,7 @@ def test_pair_sparse_queries_far_outside_and_skip(bgr, oracle):
     q[::7] = np.float32(1e6)                         # far outside the grid
     nns = bgr.NNSearchF.createKDTreeLinearHeap(pts)
     try:
-        pair = _knn(bgr, nns, q, 16)
+        pair = _knn(bgr, nns, q, 16, lanes=lanes)
         oi, od = oracle.knn_brute(pts, q, 16, 0, np.inf, None)
         assert _same(pair, (oi, od))
         # skip flags: rows of skipped queries stay untouched, whichever half they sit in
@@ -92,6 +95,7 @@ def test_pair_sparse_queries_far_outside_and_skip(bgr, oracle):
         di = torch.full((len(q), 16), -9, dtype=torch.int32, device="cuda")
         dd = torch.full((len(q), 16), -2.0, dtype=torch.float32, device="cuda")
         nns.set_method(bgr.METHOD_GRID)
+        monkeypatch.setenv("BGR_KNN_GROUP", str(lanes))
         nns.knn_skip(torch.from_numpy(q).cuda(), 16, torch.from_numpy(skip).cuda(), di, dd)
         ri, rd = di.cpu().numpy(), dd.cpu().numpy()
         keep = skip == 0
