@@ -42,6 +42,40 @@ __device__ __forceinline__ void count_below(int& rank, const uint32_t v, const u
     asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(rank) : "r"(v), "r"(key));
 }
 
+// Ascending bitonic sort of the 32 keys a group of LQ lanes holds in 32 / LQ registers each: position
+// P = s LQ + l (register s of lane l) ends up holding rank P.  Strides >= LQ exchange registers of one lane,
+// smaller strides are xor shuffles, which stay inside the group.
+template <int LQ>
+__device__ __forceinline__ void group_sort32(uint32_t (&v)[32 / LQ], const int l) {
+    constexpr int KS = 32 / LQ;
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (stride >= LQ) {
+#pragma unroll
+                for (int s = 0; s < KS; ++s) {
+                    const int s2 = s ^ (stride / LQ);
+                    if (s2 > s) {
+                        const bool asc = ((s * LQ) & size) == 0;            // size >= 2 LQ: the bit lies in s
+                        const uint32_t lo = min(v[s], v[s2]), hi = max(v[s], v[s2]);
+                        v[s] = asc ? lo : hi;
+                        v[s2] = asc ? hi : lo;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int s = 0; s < KS; ++s) {
+                    const uint32_t o = __shfl_xor_sync(kFull, v[s], stride);
+                    const bool asc = ((s * LQ + l) & size) == 0;
+                    const bool lower = (l & stride) == 0;
+                    v[s] = (lower == asc) ? min(v[s], o) : max(v[s], o);
+                }
+            }
+        }
+    }
+}
+
 #ifndef BGR_GROUP_WARPS
 #define BGR_GROUP_WARPS 4
 #endif
@@ -189,80 +223,131 @@ __global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_g
         const bool ok = active && c <= kFastCap && (c >= a.k || (tau >= tmax && tmax >= lim));
         __syncwarp();
         if (__any_sync(kFull, ok)) {
-            // ---- selection: rank by counting.  Lane l owns the survivors l + LQ s of the first 32 (slots 0 .. KS-1) and
-            // of the next 32 (slots KS .. 2 KS - 1, only when some group holds more than 32); d2 alone orders them
-            // unless two of the first k share a d2.  No warp-wide operation inside the loops: the groups run their
-            // own trip counts.
-            const int cm = ok ? c : 0;
             const uint32_t* cd = reinterpret_cast<const uint32_t*>(cand_w) + 1;
-            const bool wide = __any_sync(kFull, cm > 32);
-            uint32_t kd[2 * KS];
-            int rk[2 * KS];
+            const bool wide = __any_sync(kFull, ok && c > 32);
+            bool by_count = ok;                            // this group's survivors still have to be ranked by counting
+            if (!wide) {
+                // ---- selection, common case (every group holds <= 32 survivors): sort 32-bit keys = d2 bits with the low
+                // 6 bits replaced by the survivor's slot, bitonic network across the group's lanes x KS registers
+                // (min / max and xor shuffles only).  Afterwards register s of lane l holds rank s LQ + l: the row is
+                // written in rank order (coalesced), the full key fetched by slot.  The 6 dropped bits can only misorder
+                // two survivors whose d2 agree in the upper 26 bits: such a pair among the first k + 1 ranks sends the
+                // group to the exact ranking below.
+                const int cm = ok ? c : 0;
+                uint32_t v[KS];
 #pragma unroll
-            for (int s = 0; s < 2 * KS; ++s) { kd[s] = 0xFFFFFFFFu; rk[s] = 0; }
+                for (int s = 0; s < KS; ++s) {
+                    const int pos = l + LQ * s;
+                    v[s] = pos < cm ? ((cd[2 * pos] & ~63u) | (uint32_t)pos) : 0xFFFFFFFFu;
+                }
+                group_sort32<LQ>(v, l);
+                bool tie = false;
 #pragma unroll
-            for (int s = 0; s < KS; ++s)
-                if (l + LQ * s < cm) kd[s] = cd[2 * (l + LQ * s)];
-#pragma unroll 4
-            for (int j = 0; j < cm; ++j) {
-                const uint32_t v = cd[2 * j];
+                for (int s = 0; s < KS; ++s) {
+                    if (s * LQ < a.k) {
+                        uint32_t nx = __shfl_sync(kFull, v[s], l + 1, LQ);
+                        const uint32_t wrap = __shfl_sync(kFull, v[s + 1 < KS ? s + 1 : s], 0, LQ);
+                        if (l == LQ - 1) nx = s + 1 < KS ? wrap : 0xFFFFFFFFu;
+                        const int r = s * LQ + l;
+                        tie |= (r < a.k) && (r + 1 < cm) && ((v[s] >> 6) == (nx >> 6));
+                    }
+                }
+                const bool group_tie = (__ballot_sync(kFull, tie) & gmask) != 0u;
+                by_count = ok && group_tie;
+                if (ok && !group_tie) {
 #pragma unroll
-                for (int s = 0; s < KS; ++s) count_below(rk[s], v, kd[s]);
+                    for (int s = 0; s < KS; ++s) {
+                        const int r = s * LQ + l;
+                        if (r < a.k) {
+                            if (r < cm) {
+                                const unsigned long long key = cand_w[v[s] & 63u];
+                                a.idx[qi * a.k + r] = (int32_t)((int64_t)(uint32_t)key + a.index_base);
+                                a.d2[qi * a.k + r] = __uint_as_float((uint32_t)(key >> 32));
+                            } else {                                   // fewer than k inside the radius limit
+                                a.idx[qi * a.k + r] = -1;
+                                a.d2[qi * a.k + r] = __uint_as_float(kInfBits);
+                            }
+                        }
+                    }
+                    if (a.counter && l == 0) atomicAdd(a.counter, touched);
+                    active = false;
+                }
             }
-            if (wide) {
+            if (__any_sync(kFull, by_count)) {
+                // ---- selection, exact ranking by counting (more than 32 survivors in some group, or a possible tie).
+                // Lane l owns the survivors l + LQ s of the first 32 (slots 0 .. KS-1) and of the next 32 (slots
+                // KS .. 2 KS - 1, only when some group holds more than 32); d2 alone orders them unless two of the first k
+                // share a d2.  No warp-wide operation inside the loops: the groups run their own trip counts.
+                const int cm = by_count ? c : 0;
+                const bool wide2 = __any_sync(kFull, cm > 32);
+                uint32_t kd[2 * KS];
+                int rk[2 * KS];
 #pragma unroll
-                for (int s = KS; s < 2 * KS; ++s)
+                for (int s = 0; s < 2 * KS; ++s) { kd[s] = 0xFFFFFFFFu; rk[s] = 0; }
+#pragma unroll
+                for (int s = 0; s < KS; ++s)
                     if (l + LQ * s < cm) kd[s] = cd[2 * (l + LQ * s)];
 #pragma unroll 4
                 for (int j = 0; j < cm; ++j) {
                     const uint32_t v = cd[2 * j];
 #pragma unroll
-                    for (int s = KS; s < 2 * KS; ++s) count_below(rk[s], v, kd[s]);
+                    for (int s = 0; s < KS; ++s) count_below(rk[s], v, kd[s]);
                 }
-            }
-            // the first k ranks are a permutation of 0 .. min(c, k) - 1 exactly when no two of them tie
-            unsigned bits = 0;
-            int below = 0;
+                if (wide2) {
 #pragma unroll
-            for (int s = 0; s < 2 * KS; ++s) {
-                if (s >= KS && !wide) break;
-                const bool in = (l + LQ * s < cm) && rk[s] < a.k;
-                bits |= in ? 1u << rk[s] : 0u;
-                below += in ? 1 : 0;
-            }
-            const int want = min(cm, a.k);
-            const unsigned all_bits = __reduce_or_sync(gmask, bits);
-            const int all_below = (int)__reduce_add_sync(gmask, (unsigned)below);
-            const bool tie = ok && (__popc(all_bits) != want || all_below != want);
-            if (tie) {
-                // re-rank by the full (d2, index) key
+                    for (int s = KS; s < 2 * KS; ++s)
+                        if (l + LQ * s < cm) kd[s] = cd[2 * (l + LQ * s)];
+#pragma unroll 4
+                    for (int j = 0; j < cm; ++j) {
+                        const uint32_t v = cd[2 * j];
+#pragma unroll
+                        for (int s = KS; s < 2 * KS; ++s) count_below(rk[s], v, kd[s]);
+                    }
+                }
+                // the first k ranks are a permutation of 0 .. min(c, k) - 1 exactly when no two of them tie
+                unsigned bits = 0;
+                int below = 0;
 #pragma unroll
                 for (int s = 0; s < 2 * KS; ++s) {
-                    rk[s] = 0;
-                    if (l + LQ * s < cm) {
-                        const unsigned long long key = cand_w[l + LQ * s];
-                        for (int j = 0; j < cm; ++j) rk[s] += cand_w[j] < key ? 1 : 0;
-                    }
+                    if (s >= KS && !wide2) break;
+                    const bool in = (l + LQ * s < cm) && rk[s] < a.k;
+                    bits |= in ? 1u << rk[s] : 0u;
+                    below += in ? 1 : 0;
                 }
-            }
-            if (ok) {
+                const int want = min(cm, a.k);
+                const unsigned all_bits = __reduce_or_sync(gmask, bits);
+                const int all_below = (int)__reduce_add_sync(gmask, (unsigned)below);
+                const bool tie = by_count && (__popc(all_bits) != want || all_below != want);
+                if (tie) {
+                    // re-rank by the full (d2, index) key
 #pragma unroll
-                for (int s = 0; s < 2 * KS; ++s) {
-                    if (s >= KS && !wide) break;
-                    const int t = l + LQ * s;
-                    if (t < cm && rk[s] < a.k) {
-                        a.idx[qi * a.k + rk[s]] = (int32_t)((int64_t)(uint32_t)cand_w[t] + a.index_base);
-                        a.d2[qi * a.k + rk[s]] = __uint_as_float(kd[s]);
+                    for (int s = 0; s < 2 * KS; ++s) {
+                        rk[s] = 0;
+                        if (l + LQ * s < cm) {
+                            const unsigned long long key = cand_w[l + LQ * s];
+                            for (int j = 0; j < cm; ++j) rk[s] += cand_w[j] < key ? 1 : 0;
+                        }
                     }
                 }
-                if (cm < a.k) {                                    // fewer than k inside the radius limit
-                    for (int t = cm + l; t < a.k; t += LQ) {
-                        a.idx[qi * a.k + t] = -1;
-                        a.d2[qi * a.k + t] = __uint_as_float(kInfBits);
+                if (by_count) {
+#pragma unroll
+                    for (int s = 0; s < 2 * KS; ++s) {
+                        if (s >= KS && !wide2) break;
+                        const int t = l + LQ * s;
+                        if (t < cm && rk[s] < a.k) {
+                            a.idx[qi * a.k + rk[s]] = (int32_t)((int64_t)(uint32_t)cand_w[t] + a.index_base);
+                            a.d2[qi * a.k + rk[s]] = __uint_as_float(kd[s]);
+                        }
                     }
+                    if (cm < a.k) {                                    // fewer than k inside the radius limit
+                        for (int t = cm + l; t < a.k; t += LQ) {
+                            a.idx[qi * a.k + t] = -1;
+                            a.d2[qi * a.k + t] = __uint_as_float(kInfBits);
+                        }
+                    }
+                    if (a.counter && l == 0) atomicAdd(a.counter, touched);
+                    active = false;
                 }
-                if (a.counter && l == 0) atomicAdd(a.counter, touched);
-                active = false;
             }
         }
         __syncwarp();
