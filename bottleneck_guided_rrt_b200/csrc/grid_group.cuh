@@ -19,6 +19,7 @@
 //
 // Used for fully indexed, uncrowded clouds (no unsorted tail, no piles): grid_knn() in tile_knn.cuh.
 #pragma once
+#include <type_traits>
 #include "grid.cuh"
 
 namespace bgr {
@@ -42,14 +43,14 @@ __device__ __forceinline__ void count_below(int& rank, const uint32_t v, const u
     asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\t@p add.s32 %0, %0, 1;\n\t}" : "+r"(rank) : "r"(v), "r"(key));
 }
 
-// Ascending bitonic sort of the 32 keys a group of LQ lanes holds in 32 / LQ registers each: position
+// Ascending bitonic sort of the N (32 or 64) keys a group of LQ lanes holds in N / LQ registers each: position
 // P = s LQ + l (register s of lane l) ends up holding rank P.  Strides >= LQ exchange registers of one lane,
 // smaller strides are xor shuffles, which stay inside the group.
-template <int LQ>
-__device__ __forceinline__ void group_sort32(uint32_t (&v)[32 / LQ], const int l) {
-    constexpr int KS = 32 / LQ;
+template <int LQ, int N>
+__device__ __forceinline__ void group_sort(uint32_t (&v)[N / LQ], const int l) {
+    constexpr int KS = N / LQ;
 #pragma unroll
-    for (int size = 2; size <= 32; size <<= 1) {
+    for (int size = 2; size <= N; size <<= 1) {
 #pragma unroll
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
             if (stride >= LQ) {
@@ -225,29 +226,30 @@ __global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_g
         if (__any_sync(kFull, ok)) {
             const uint32_t* cd = reinterpret_cast<const uint32_t*>(cand_w) + 1;
             const bool wide = __any_sync(kFull, ok && c > 32);
-            bool by_count = ok;                            // this group's survivors still have to be ranked by counting
-            if (!wide) {
-                // ---- selection, common case (every group holds <= 32 survivors): sort 32-bit keys = d2 bits with the low
-                // 6 bits replaced by the survivor's slot, bitonic network across the group's lanes x KS registers
-                // (min / max and xor shuffles only).  Afterwards register s of lane l holds rank s LQ + l: the row is
-                // written in rank order (coalesced), the full key fetched by slot.  The 6 dropped bits can only misorder
-                // two survivors whose d2 agree in the upper 26 bits: such a pair among the first k + 1 ranks sends the
-                // group to the exact ranking below.
+            bool by_count = false;                         // this group's survivors have to be ranked exactly, by counting
+            // ---- selection: sort 32-bit keys = d2 bits with the low 6 bits replaced by the survivor's slot, bitonic
+            // network across the group's lanes x N / LQ registers (min / max and xor shuffles only; N = 32, or 64 when
+            // some group of the warp holds more than 32 survivors).  Afterwards register s of lane l holds rank
+            // s LQ + l: the row is written in rank order (coalesced), the full key fetched by slot.  The 6 dropped
+            // bits can only misorder two survivors whose d2 agree in the upper 26 bits: such a pair among the first
+            // k + 1 ranks sends the group to the exact ranking below.
+            auto select = [&](auto n_tag) {
+                constexpr int N = decltype(n_tag)::value, NS = N / LQ;
                 const int cm = ok ? c : 0;
-                uint32_t v[KS];
+                uint32_t v[NS];
 #pragma unroll
-                for (int s = 0; s < KS; ++s) {
+                for (int s = 0; s < NS; ++s) {
                     const int pos = l + LQ * s;
                     v[s] = pos < cm ? ((cd[2 * pos] & ~63u) | (uint32_t)pos) : 0xFFFFFFFFu;
                 }
-                group_sort32<LQ>(v, l);
+                group_sort<LQ, N>(v, l);
                 bool tie = false;
 #pragma unroll
-                for (int s = 0; s < KS; ++s) {
+                for (int s = 0; s < NS; ++s) {
                     if (s * LQ < a.k) {
                         uint32_t nx = __shfl_sync(kFull, v[s], l + 1, LQ);
-                        const uint32_t wrap = __shfl_sync(kFull, v[s + 1 < KS ? s + 1 : s], 0, LQ);
-                        if (l == LQ - 1) nx = s + 1 < KS ? wrap : 0xFFFFFFFFu;
+                        const uint32_t wrap = __shfl_sync(kFull, v[s + 1 < NS ? s + 1 : s], 0, LQ);
+                        if (l == LQ - 1) nx = s + 1 < NS ? wrap : 0xFFFFFFFFu;
                         const int r = s * LQ + l;
                         tie |= (r < a.k) && (r + 1 < cm) && ((v[s] >> 6) == (nx >> 6));
                     }
@@ -256,7 +258,7 @@ __global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_g
                 by_count = ok && group_tie;
                 if (ok && !group_tie) {
 #pragma unroll
-                    for (int s = 0; s < KS; ++s) {
+                    for (int s = 0; s < NS; ++s) {
                         const int r = s * LQ + l;
                         if (r < a.k) {
                             if (r < cm) {
@@ -272,7 +274,9 @@ __global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_g
                     if (a.counter && l == 0) atomicAdd(a.counter, touched);
                     active = false;
                 }
-            }
+            };
+            if (wide) select(std::integral_constant<int, 64>());
+            else select(std::integral_constant<int, 32>());
             if (__any_sync(kFull, by_count)) {
                 // ---- selection, exact ranking by counting (more than 32 survivors in some group, or a possible tie).
                 // Lane l owns the survivors l + LQ s of the first 32 (slots 0 .. KS-1) and of the next 32 (slots
