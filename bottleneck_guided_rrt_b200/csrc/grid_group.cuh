@@ -77,6 +77,13 @@ __device__ __forceinline__ void group_sort(uint32_t (&v)[N / LQ], const int l) {
     }
 }
 
+#ifndef BGR_GROUP_ROWS
+#define BGR_GROUP_ROWS 3
+#endif
+#ifndef BGR_GROUP_SM_WARPS
+#define BGR_GROUP_SM_WARPS 32
+#endif
+constexpr int kGroupRows = BGR_GROUP_ROWS;     // ring-1 rows whose loads are in flight together (divides 9)
 #ifndef BGR_GROUP_WARPS
 #define BGR_GROUP_WARPS 4
 #endif
@@ -85,7 +92,7 @@ constexpr int kGroupWarps = BGR_GROUP_WARPS;   // 64 registers, 8 CTAs of 4 warp
 
 // requires: a.n_indexed == a.n > 0, a.fast, a.heavy == nullptr
 template <int LQ>
-__global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_group_kernel(GridKnnArgs a) {
+__global__ void __launch_bounds__(kGroupWarps * 32, BGR_GROUP_SM_WARPS / kGroupWarps) grid_knn_group_kernel(GridKnnArgs a) {
     static_assert(LQ == 16 || LQ == 8, "lanes per query");
     constexpr int NG = 32 / LQ;               // queries per warp
     constexpr int RS = (9 + LQ - 1) / LQ;     // ring-1 rows a lane owns
@@ -175,24 +182,24 @@ __global__ void __launch_bounds__(kGroupWarps * 32, 32 / kGroupWarps) grid_knn_g
         };
         // rows in groups of three, two LQ-lane passes at a time: six LDG.128 in flight together
 #pragma unroll 1
-        for (int g = 0; g < 9; g += 3) {
-            int s0[3], e0[3];
+        for (int g = 0; g < 9; g += kGroupRows) {
+            int s0[kGroupRows], e0[kGroupRows];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
+            for (int i = 0; i < kGroupRows; ++i) {
                 int e;
                 row_bounds(g + i, s0[i], e);
                 e0[i] = active ? e : s0[i];                                           // a finished group admits nothing
             }
 #pragma unroll
             for (int pp = 0; pp < PASSES; pp += 2) {
-                float4 p[3][2];
+                float4 p[kGroupRows][2];
 #pragma unroll
-                for (int i = 0; i < 3; ++i) {
+                for (int i = 0; i < kGroupRows; ++i) {
                     p[i][0] = __ldg(a.pts + min(s0[i] + pp * LQ + l, last));          // lanes past the row's end load a node they ignore
                     p[i][1] = __ldg(a.pts + min(s0[i] + (pp + 1) * LQ + l, last));
                 }
 #pragma unroll
-                for (int i = 0; i < 3; ++i) {
+                for (int i = 0; i < kGroupRows; ++i) {
                     consider(p[i][0], s0[i] + pp * LQ + l < e0[i]);
                     consider(p[i][1], s0[i] + (pp + 1) * LQ + l < e0[i]);
                 }
