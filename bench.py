@@ -572,7 +572,7 @@ def sharded_section(c):
         # the local search is the grid kNN over a 6.25 M-node index (100 MB: L2 resident at the edge); its HBM-contract
         # roofline on SURVEY 8(d) bytes per GPU
         alg = 12.0 * SHARD_NODES + 12.0 * N_QUERIES + 8.0 * K_NN * N_QUERIES
-        sh["roofline"] = {"bound": "hbm", "kernel": "grid_knn_kernel (local search)", "achieved": alg / (best["local_ms"] * 1e-3) / 1e9,
+        sh["roofline"] = {"bound": "hbm", "kernel": "grid_knn_group_kernel (local search)", "achieved": alg / (best["local_ms"] * 1e-3) / 1e9,
                           "peak": c["pk"]["hbm_gbs"], "unit": "GB/s", "frac": alg / (best["local_ms"] * 1e-3) / 1e9 / c["pk"]["hbm_gbs"],
                           "algorithmic_bytes": alg, "exchange_bytes_per_rank": int(8 * K_NN * N_QUERIES * (world - 1) // max(world, 1))}
     sh["exchange"] = {"nccl": "ONE all_gather_into_tensor of the packed (idx,d2) slabs (%d B per rank) + bgr_knn_merge_strided_dev" % (8 * K_NN * N_QUERIES),
