@@ -1482,7 +1482,16 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
     BGR_CHECK(map_sphere_gate(h, radius, &dil));
     // large batches: 32 spheres per warp (lane-per-sphere gate, then the warp walks the undecided ones);
     // small ones: a warp per sphere so the walks overlap
-    if (n >= (int64_t)num_sms() * 1024)
+    // BGR_SPHERES=lane|warp32|warp1 forces one form (test / measurement aid, read per call)
+    int form = n >= (int64_t)num_sms() * 1024 ? (spheres_lane_ok(radius, h->view().inv_res) ? 2 : 1) : 0;
+    if (const char* e = getenv("BGR_SPHERES")) {
+        if (!strcmp(e, "lane") && spheres_lane_ok(radius, h->view().inv_res)) form = 2;
+        else if (!strcmp(e, "warp32")) form = 1;
+        else if (!strcmp(e, "warp1")) form = 0;
+    }
+    if (form == 2)
+        collide_spheres_lane_kernel<<<(unsigned)div_up(n, kLaneThreads), kLaneThreads, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
+    else if (form == 1)
         collide_spheres_kernel<32><<<(unsigned)div_up(n, 128), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);
     else
         collide_spheres_kernel<1><<<(unsigned)div_up(n, 4), 128, 0, h->stream>>>(h->view(), d_c, n, radius, d_hit, d_band, dil);

@@ -166,4 +166,114 @@ __device__ __forceinline__ void collide_spheres_warp(const MapView& m, const flo
     }   // while (pending)
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Lane-per-sphere form for LARGE batches of small spheres (box of radius + margin spans <= kLaneSpan cells per
+// axis, i.e. <= 3x3x3 bricks).  collide_spheres_warp<32> walks every undecided sphere with the whole warp: ~250
+// warp instructions per sphere, most of them the warp-wide bookkeeping of spreading ~13 occupied cells over 32
+// lanes (prefix scan, binary search, n-th set bit), at 80 % of the issue slots (profiles/r2_ncu_full_s_edges_spheres.txt).
+// With a dilation of 3 cells the gate decides only the ~10 % of spheres whose own cell is occupied, so nearly every
+// sphere is walked.  Here a lane keeps its sphere: it reads the <= 27 brick words itself, masks them to the box and
+// walks their set bits; the squared per-axis distances of the <= 8 cell coordinates per axis are tabulated once
+// per sphere in shared memory (the same double operations, in the same order, as the warp form: identical bits),
+// so an occupied cell costs three LDS.64 and two DADD.  No shuffles, no ballots.
+constexpr int kLaneSpan = 8;
+constexpr int kLaneThreads = 128;
+
+// largest radius the lane form takes on a map of resolution res (the box spans floor(2 rc) + 2 cells at most)
+__host__ __device__ inline bool spheres_lane_ok(double radius, double inv_res) {
+    return 2.0 * (radius + kSweepMargin) * inv_res + 2.0 <= (double)kLaneSpan;
+}
+
+static __global__ void __launch_bounds__(kLaneThreads) collide_spheres_lane_kernel(MapView m, const float* __restrict__ c3, int64_t n,
+                                                                            double radius, uint8_t* __restrict__ hit,
+                                                                            uint8_t* __restrict__ band, LevelGrid dil) {
+    __shared__ double t2[3 * kLaneSpan][kLaneThreads];     // [axis * kLaneSpan + cell - lo][thread]
+    const int tid = threadIdx.x;
+    const int64_t i = (int64_t)blockIdx.x * kLaneThreads + tid;
+    if (i >= n) return;
+    const double c[3] = {(double)c3[3 * i], (double)c3[3 * i + 1], (double)c3[3 * i + 2]};
+    {
+        const int gx = (int)floor((c[0] - m.origin[0]) * m.inv_res), gy = (int)floor((c[1] - m.origin[1]) * m.inv_res),
+                  gz = (int)floor((c[2] - m.origin[2]) * m.inv_res);
+        if (gx >= 0 && gx < m.dims[0] && gy >= 0 && gy < m.dims[1] && gz >= 0 && gz < m.dims[2]) {
+            // the gate of collide_spheres_warp: centre cell clear in the dilated map => free; occupied => distance 0
+            const int64_t w = ((int64_t)(gz >> 2) * m.lv[0].nb[1] + (gy >> 2)) * m.lv[0].nb[0] + (gx >> 2);
+            const int b = ((gz & 3) << 4) | ((gy & 3) << 2) | (gx & 3);
+            const bool clear = dil.bits && !((__ldg(dil.bits + w) >> b) & 1ull);
+            if (clear || ((__ldg(m.lv[0].bits + w) >> b) & 1ull)) {
+                hit[i] = (!clear && radius > 0.0) ? 1 : 0;
+                if (band) band[i] = (!clear && radius <= kBandTol) ? 1 : 0;
+                return;
+            }
+        }
+    }
+    const double thr2 = radius > kBandTol ? (radius - kBandTol) * (radius - kBandTol) * (1.0 - 1e-12) : -1.0;
+    int lo[3], hi[3];
+    bool empty = false;
+    const double half = 0.5 * m.res;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const double r = radius + kSweepMargin;
+        const double g = (c[a] - m.origin[a]) * m.inv_res, rc = r * m.inv_res;
+        lo[a] = max(0, (int)floor(g - rc));
+        hi[a] = min(m.dims[a] - 1, (int)floor(g + rc));
+        empty |= lo[a] > hi[a];
+        // squared distance along this axis from the centre to each cell of the box
+#pragma unroll
+        for (int k = 0; k < kLaneSpan; ++k) {
+            if (lo[a] + k <= hi[a]) {
+                const double cc = m.origin[a] + ((double)(lo[a] + k) + 0.5) * m.res;
+                const double t = fmax(0.0, fabs(c[a] - cc) - half);
+                t2[a * kLaneSpan + k][tid] = t * t;
+            }
+        }
+    }
+    double d2min = 1e300;
+    if (!empty) {
+        const int bl[3] = {lo[0] >> 2, lo[1] >> 2, lo[2] >> 2};
+        const int bh[3] = {hi[0] >> 2, hi[1] >> 2, hi[2] >> 2};
+        for (int bz = bl[2]; bz <= bh[2]; ++bz) {
+            const int z0 = max(lo[2] - 4 * bz, 0), z1 = min(hi[2] - 4 * bz, 3);
+            const unsigned long long mz = (z1 == 3 ? ~0ull : ((1ull << (16 * z1 + 16)) - 1ull)) & ~((1ull << (16 * z0)) - 1ull);
+            const int kz = 2 * kLaneSpan + 4 * bz - lo[2];
+            for (int by = bl[1]; by <= bh[1]; ++by) {
+                const int y0 = max(lo[1] - 4 * by, 0), y1 = min(hi[1] - 4 * by, 3);
+                const unsigned long long myz =
+                    ((unsigned long long)(((1u << (4 * y1 + 4)) - (1u << (4 * y0))) & 0xFFFFu) * 0x0001000100010001ull) & mz;
+                const int ky = kLaneSpan + 4 * by - lo[1];
+                const uint64_t* row = m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0];
+                for (int bx = bl[0]; bx <= bh[0]; ++bx) {
+                    const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
+                    const unsigned long long mx = (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull;
+                    const unsigned long long W = __ldg(row + bx) & mx & myz;
+                    const int kx = 4 * bx - lo[0];
+                    // the set bits, 32 at a time (z planes 0-1, then 2-3).  A cell closer than radius - tolerance
+                    // decides the sphere (hit, not in the band): stop at once — the lanes next to a clump of
+                    // occupied cells would otherwise walk dozens of bits while the rest of the warp waits
+#pragma unroll
+                    for (int hw = 0; hw < 2; ++hw) {
+                        unsigned w = (unsigned)(W >> (32 * hw));
+                        while (w) {
+                            const int bit = __ffs((int)w) - 1;
+                            w &= w - 1u;
+                            double d2 = t2[kx + (bit & 3)][tid];
+                            d2 += t2[ky + ((bit >> 2) & 3)][tid];
+                            d2 += t2[kz + 2 * hw + (bit >> 4)][tid];
+                            if (d2 < thr2) {
+                                hit[i] = 1;
+                                if (band) band[i] = 0;
+                                return;
+                            }
+                            d2min = fmin(d2min, d2);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    const double gmin = d2min < 1e299 ? sqrt(d2min) - radius : 1e300;
+    hit[i] = gmin < 0.0 ? 1 : 0;
+    if (band) band[i] = fabs(gmin) <= kBandTol ? 1 : 0;
+}
+
 }  // namespace bgr
