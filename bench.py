@@ -487,11 +487,11 @@ def edge_section(c, out):
                    "in_band": int(d_sband.sum().item())},
         "e2e": {"value": world * N_EDGES / (sphere_e2e_ms * 1e-3), "unit": "sphere state checks/s", "ms_per_step": sphere_e2e_ms,
                 "h2d_bytes_per_step": int(12 * N_EDGES), "d2h_bytes_per_step": int(2 * N_EDGES)},
-        "roofline": {"bound": "hbm", "kernel": "collide_spheres_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
+        "roofline": {"bound": "hbm", "kernel": "collide_spheres_lane_kernel", "achieved": sbytes / (sphere_ms * 1e-3) / 1e9,
                      "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": sbytes / (sphere_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                      "algorithmic_bytes": sbytes, "algorithmic_bytes_def": "14 B/sphere + the 16 MiB bitmap once",
-                     "peak_src": pk["src"], "traffic": ncu_traffic("collide_spheres_kernel"),
-                     "l2": l2_roofline("collide_spheres_kernel", sphere_ms, c["l2_peak"]["sectors_32MiB"],
+                     "peak_src": pk["src"], "traffic": ncu_traffic("collide_spheres_lane_kernel"),
+                     "l2": l2_roofline("collide_spheres_lane_kernel", sphere_ms, c["l2_peak"]["sectors_32MiB"],
                                        "random 32 B sectors (one 8 B brick word per load), 32 MiB resident buffer (both maps)")}}
     return boxes, p1, p2
 

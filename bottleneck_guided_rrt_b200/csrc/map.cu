@@ -1480,10 +1480,12 @@ int bgr_map_collide_spheres_dev(bgr_map* h, const float* d_c, int64_t n, double 
     BGR_CHECK(check_device(h->device));
     LevelGrid dil;
     BGR_CHECK(map_sphere_gate(h, radius, &dil));
-    // large batches: 32 spheres per warp (lane-per-sphere gate, then the warp walks the undecided ones);
-    // small ones: a warp per sphere so the walks overlap
+    // large batches of small spheres: a lane per sphere (spheres.cuh); large batches of larger spheres: 32 spheres per
+    // warp (lane-per-sphere gate, then the warp walks the undecided ones); small batches: a warp per sphere so the
+    // walks overlap
     // BGR_SPHERES=lane|warp32|warp1 forces one form (test / measurement aid, read per call)
-    int form = n >= (int64_t)num_sms() * 1024 ? (spheres_lane_ok(radius, h->view().inv_res) ? 2 : 1) : 0;
+    // (measured crossover of the lane form against a warp per sphere: ~20 k spheres, profiles/r2_spheres_lane.txt)
+    int form = (n >= 24576 && spheres_lane_ok(radius, h->view().inv_res)) ? 2 : (n >= (int64_t)num_sms() * 1024 ? 1 : 0);
     if (const char* e = getenv("BGR_SPHERES")) {
         if (!strcmp(e, "lane") && spheres_lane_ok(radius, h->view().inv_res)) form = 2;
         else if (!strcmp(e, "warp32")) form = 1;

@@ -242,10 +242,16 @@ static __global__ void __launch_bounds__(kLaneThreads) collide_spheres_lane_kern
                     ((unsigned long long)(((1u << (4 * y1 + 4)) - (1u << (4 * y0))) & 0xFFFFu) * 0x0001000100010001ull) & mz;
                 const int ky = kLaneSpan + 4 * by - lo[1];
                 const uint64_t* row = m.lv[0].bits + ((int64_t)bz * m.lv[0].nb[1] + by) * m.lv[0].nb[0];
-                for (int bx = bl[0]; bx <= bh[0]; ++bx) {
+                // the (up to three) words of this brick row are loaded together, then walked one after the other
+                unsigned long long Wr[3];
+#pragma unroll
+                for (int j = 0; j < 3; ++j) Wr[j] = bl[0] + j <= bh[0] ? __ldg(row + bl[0] + j) : 0ull;
+#pragma unroll
+                for (int j = 0; j < 3; ++j) {
+                    const int bx = bl[0] + j;
                     const int x0 = max(lo[0] - 4 * bx, 0), x1 = min(hi[0] - 4 * bx, 3);
-                    const unsigned long long mx = (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull;
-                    const unsigned long long W = __ldg(row + bx) & mx & myz;
+                    const unsigned long long mx = x1 >= x0 ? (unsigned long long)(((2u << x1) - (1u << x0)) & 0xFu) * 0x1111111111111111ull : 0ull;
+                    const unsigned long long W = Wr[j] & mx & myz;
                     const int kx = 4 * bx - lo[0];
                     // the set bits, 32 at a time (z planes 0-1, then 2-3).  A cell closer than radius - tolerance
                     // decides the sphere (hit, not in the band): stop at once — the lanes next to a clump of

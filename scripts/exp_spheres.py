@@ -18,6 +18,7 @@ boxes = synth.grid_to_boxes(occ, 0.05, (0, 0, 0), 3)
 m = B.OccupancyMap(0.05, (0, 0, 0), (512,) * 3)
 m.set_boxes(boxes)
 p1, _ = synth.edges(4, 1_000_000, occ)
+p1 = p1[:int(os.environ.get('NSPH', '1000000'))]
 # a tenth of the centres moved outside / onto the border of the map
 p1 = p1.copy()
 p1[::10] = (p1[::10] - np.float32(12.8)) * np.float32(1.05) + np.float32(12.8)

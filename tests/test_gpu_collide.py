@@ -356,6 +356,42 @@ def test_spheres_gate_is_exact(bgr, oracle, radius):
     assert not np.array_equal(h0u, h0)
 
 
+@pytest.mark.parametrize("radius", [0.0, 0.03, 0.05, 0.1, 0.149, 0.2])
+def test_spheres_lane_form_equals_warp_forms(bgr, oracle, radius, monkeypatch):
+    """the lane-per-sphere kernel (large batches of small spheres) writes the same hit / in_band bytes as the two
+    warp forms — gate on and off, centres outside / on the border of the map, after an incremental update — and
+    agrees with the oracle's MPR loop outside the band.  r = 0.2 spans more cells than the lane form takes: the
+    request falls back to the warp form."""
+    occ, boxes, m = _map(bgr, oracle, 96, 5, 3, n_walls=2, wall_thick=3, door_cells=5)
+    mt = oracle.MT(77)
+    pts = np.concatenate([_points_near_obstacles(oracle, occ, 30000, 78, 0.6),
+                          (mt.real(3 * 20000).reshape(-1, 3) * 5.4 - 0.3).astype(np.float32),
+                          np.array([[0.0, 0.0, 0.0], [4.8, 4.8, 4.8], [-0.05, 2.0, 2.0], [4.85, 2.0, 2.0], [2.4, 2.4, 1e6]], dtype=np.float32)])
+    res = {}
+    for gate in (True, False):
+        m.set_gate(gate)
+        for form in ("lane", "warp32", "warp1"):
+            monkeypatch.setenv("BGR_SPHERES", form)
+            res[(gate, form)] = m.collide_spheres(pts, radius)
+    ref = res[(True, "warp32")]
+    for key, (h, b) in res.items():
+        assert np.array_equal(h, ref[0]) and np.array_equal(b, ref[1]), key
+    if radius > 0:
+        assert 0.02 < ref[0].mean() < 0.98
+    sub = np.arange(0, len(pts), 37)
+    oh, _ = oracle.collide_spheres(boxes, pts[sub], radius, mode=1, want_band=False)
+    assert not ((oh != ref[0][sub]) & (ref[1][sub] == 0)).any()
+    m.set_gate(True)
+    m.update_boxes(np.array([[2.425, 2.425, 2.425, 0.05, 1.0, 0.5]]), boxes[:3000])
+    upd = {}
+    for form in ("lane", "warp32"):
+        monkeypatch.setenv("BGR_SPHERES", form)
+        upd[form] = m.collide_spheres(pts, radius)
+    assert np.array_equal(upd["lane"][0], upd["warp32"][0]) and np.array_equal(upd["lane"][1], upd["warp32"][1])
+    if radius > 0:
+        assert not np.array_equal(upd["lane"][0], ref[0])
+
+
 def test_edges_chunked_host_call_equals_device_call(bgr, oracle):
     """a large host-pointer batch is cut into chunks whose H2D copies overlap the sweep of the
     previous chunk: same hit / in_band bytes and same counters as the one-launch device call."""
