@@ -453,9 +453,9 @@ def test_edges_full_size_properties(bgr, oracle):
     assert np.array_equal(ol, oh[sub])
 
 
-def test_spheres_full_size_properties(bgr, oracle):
-    """1,000,000 state checks (r = 0.1) against the 512^3 map: gate on == gate off, chunk /
-    permutation independence, and the oracle's MPR loop on a subsample."""
+def test_spheres_full_size_properties(bgr, oracle, monkeypatch):
+    """1,000,000 state checks (r = 0.1) against the 512^3 map: gate on == gate off, the lane-per-sphere form ==
+    the warp forms, chunk / permutation independence, and the oracle's MPR loop on a subsample."""
     import torch
     from bottleneck_guided_rrt_b200 import synth
     occ = synth.make_map(512, 4, n_walls=8, wall_thick=4, door_cells=5)
@@ -473,9 +473,16 @@ def test_spheres_full_size_properties(bgr, oracle):
     torch.cuda.synchronize()
     assert np.array_equal(h, h0.cpu().numpy()) and np.array_equal(b, b0.cpu().numpy())
     m.set_gate(True)
-    perm = np.random.default_rng(3).permutation(len(pts))[:100000]       # small batch: a warp per sphere
+    perm = np.random.default_rng(3).permutation(len(pts))[:100000]       # another batch size, another order
     hp, bp = m.collide_spheres(pts[perm], 0.1)
     assert np.array_equal(hp, h[perm]) and np.array_equal(bp, b[perm])
+    hs, bs = m.collide_spheres(pts[perm[:10000]], 0.1)                   # small batch: a warp per sphere
+    assert np.array_equal(hs, h[perm[:10000]]) and np.array_equal(bs, b[perm[:10000]])
+    monkeypatch.setenv("BGR_SPHERES", "warp32")                          # the 32-spheres-per-warp form on the full batch
+    hw, bw = m.collide_spheres(dp, 0.1)
+    torch.cuda.synchronize()
+    assert np.array_equal(hw.cpu().numpy(), h) and np.array_equal(bw.cpu().numpy(), b)
+    monkeypatch.delenv("BGR_SPHERES")
     hh, bh = m.collide_spheres(pts, 0.1)                                 # host buffers: chunked, copies overlapped
     assert np.array_equal(hh, h) and np.array_equal(bh, b)
     sub = np.arange(0, 1_000_000, 8000)
