@@ -7,14 +7,16 @@
 // all 32 lanes repeat: cell coordinates, the nine row bounds, the nearest unscanned face, the a-priori
 // threshold, the retry logic, the kernel prologue.  With a query per lane group every such instruction serves
 // 32 / LQ queries.  The per-NODE part: a ring-1 x-row holds ~24 nodes — one 32-lane pass at 75 % of the lanes
-// before, 32 / LQ passes of LQ lanes now (LQ = 8: three of the four passes are full).  The selection ranks the
-// survivors by counting as before, each lane owning 32 / LQ of its group's first 32 survivors (and as many of
-// the next 32 when a group holds more).
+// before, 32 / LQ passes of LQ lanes now (LQ = 8: three of the four passes are full).  The selection sorts the
+// group's <= 32 (or <= 64) survivors with a bitonic network on packed 32-bit keys (d2 bits, low 6 bits = the
+// survivor's slot), all groups of the warp at once; the counting pass of grid_knn_query stays as the exact
+// fallback for survivors whose d2 agree in the upper 26 bits.
 //
 // Exactness: the same argument as the fast path of grid_knn_query (every node of the 3x3x3 block with
 // d2 <= tau is in the group's buffer, tau is strictly below the nearest unscanned face, >= k survivors or tau at
-// the radius limit => the k smallest keys are the answer).  Equal d2 among the first k ranks are re-ranked by
-// the full (d2, index) key.  A group whose query cannot be finished here (empty block, needs ring 2, three
+// the radius limit => the k smallest keys are the answer).  The packed keys order the survivors exactly unless two
+// of the first k + 1 ranks agree in their upper 26 bits; those groups are ranked by counting on the full d2, and equal
+// d2 among the first k ranks by the full (d2, index) key.  A group whose query cannot be finished here (empty block, needs ring 2, three
 // attempts spent) hands it to the general ring search, run by the whole warp at the end of the kernel.
 //
 // Used for fully indexed, uncrowded clouds (no unsorted tail, no piles): grid_knn() in tile_knn.cuh.
