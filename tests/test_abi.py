@@ -40,6 +40,17 @@ def test_header_symbols_all_exported(bgr):
     assert L.bgr_version() == 100
 
 
+def test_header_constants_match_the_binding(bgr):
+    """the numeric constants of include/bgrrt.h and their mirrors in the ctypes binding agree"""
+    src = open(HDR).read()
+    defs = dict((k, v) for k, v in re.findall(r"#define\s+(BGR_[A-Z0-9_]+)\s+([0-9]+)u?\b", src))
+    assert int(defs["BGR_KNN_STATIC_MAX_RESULTS"]) == bgr.KNN_STATIC_MAX_RESULTS == 32768
+    assert int(defs["BGR_ALLOW_SELF_MATCH"]) == bgr.ALLOW_SELF_MATCH and int(defs["BGR_SORT_RESULTS"]) == bgr.SORT_RESULTS
+    assert (int(defs["BGR_METHOD_BRUTE"]), int(defs["BGR_METHOD_GRID"]), int(defs["BGR_METHOD_GRID_GENERAL"])) == \
+        (bgr.METHOD_BRUTE, bgr.METHOD_GRID, bgr.METHOD_GRID_GENERAL)
+    assert int(defs["BGR_VERSION"]) == bgr.lib().bgr_version()
+
+
 def test_header_is_plain_c(tmp_path):
     """the boundary is a C ABI: the header must compile as C99 with no C++/torch types."""
     src = tmp_path / "t.c"
